@@ -1,0 +1,746 @@
+// sb_abi.cu -- host side of libsbayes_b200.so: the C ABI declared in include/sbayes_b200.h.
+// Pure CUDA runtime (no torch types); built by __graft_entry__.build() with
+//   nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -Xcompiler -fPIC
+#include "../../include/sbayes_b200.h"
+#include "sb_common.cuh"
+#include "sb_eval.cuh"
+#include "sb_step.cuh"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+struct sb_ctx {
+    int device = 0;
+    sb_dims dims{};
+    DevData d{};
+    ChainArrays st{};
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    std::string err;
+    bool has_data = false, has_priors = false, has_ops = false;
+    std::vector<void*> allocs;
+    double* partial = nullptr;       // [n_chains][n_tiles]
+    int n_tiles = 0, sites_per_tile = 0;
+    int geo_cap = 0;                 // capacity (members) of the Prim scratch
+    int64_t launches = 0;
+    int64_t steps_done = 0;
+    StepParams sp{};                 // operator configuration of the persistent kernel
+    double* d_pgrow = nullptr;
+    int* d_maxsize = nullptr;
+    size_t step_smem = 0;
+    std::vector<int> h_zone_size;    // [chains][Z] host mirror kept by set_state (shape checks only)
+};
+
+#define CK(call)                                                                                  \
+    do {                                                                                          \
+        cudaError_t e_ = (call);                                                                  \
+        if (e_ != cudaSuccess) {                                                                  \
+            ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_);                        \
+            return SB_E_CUDA;                                                                     \
+        }                                                                                         \
+    } while (0)
+#define FAIL(code, msg)        \
+    do {                       \
+        ctx->err = (msg);      \
+        return (code);         \
+    } while (0)
+
+template <typename T>
+static int dalloc(sb_ctx* ctx, T** p, size_t n) {
+    if (n == 0) n = 1;
+    CK(cudaMalloc((void**)p, n * sizeof(T)));
+    ctx->allocs.push_back((void*)*p);
+    CK(cudaMemsetAsync(*p, 0, n * sizeof(T), ctx->stream));
+    return SB_OK;
+}
+#define DA(p, n)                                       \
+    do {                                               \
+        int r_ = dalloc(ctx, &(p), (size_t)(n));       \
+        if (r_ != SB_OK) return r_;                    \
+    } while (0)
+
+template <typename T>
+static int h2d(sb_ctx* ctx, T* dst, const T* src, size_t n) {
+    if (n == 0) return SB_OK;
+    CK(cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));   // host buffers are borrowed for the duration of the call only
+    return SB_OK;
+}
+template <typename T>
+static int d2h(sb_ctx* ctx, T* dst, const T* src, size_t n) {
+    if (n == 0) return SB_OK;
+    CK(cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SB_OK;
+}
+#define H2D(dst, src, n)                                 \
+    do {                                                 \
+        int r_ = h2d(ctx, (dst), (src), (size_t)(n));    \
+        if (r_ != SB_OK) return r_;                      \
+    } while (0)
+#define D2H(dst, src, n)                                 \
+    do {                                                 \
+        int r_ = d2h(ctx, (dst), (src), (size_t)(n));    \
+        if (r_ != SB_OK) return r_;                      \
+    } while (0)
+
+static inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+extern "C" {
+
+int sb_version(void) { return 100; }
+
+int sb_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+const char* sb_last_error(const sb_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int sb_create(sb_ctx** out, int device, const sb_dims* dims) {
+    if (!out || !dims) return SB_E_ARG;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return SB_E_NOGPU;
+    if (device < 0 || device >= ndev) return SB_E_ARG;
+    if (dims->n_sites < 1 || dims->n_features < 1 || dims->n_states < 1 || dims->n_states > SB_MAX_S ||
+        dims->n_zones < 0 || dims->n_zones > SB_MAX_Z || dims->n_families < 0 || dims->n_families > 32767 ||
+        dims->n_chains < 1)
+        return SB_E_ARG;
+    sb_ctx* ctx = new sb_ctx();
+    ctx->device = device;
+    ctx->dims = *dims;
+    *out = ctx;   // returned even on failure so that the caller can read sb_last_error, then sb_destroy
+    CK(cudaSetDevice(device));
+    CK(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
+    ctx->stream = ctx->own_stream;
+
+    DevData& d = ctx->d;
+    d.N = dims->n_sites; d.F = dims->n_features; d.S = dims->n_states; d.Z = dims->n_zones;
+    d.inheritance = (dims->flags & SB_F_INHERITANCE) ? 1 : 0;
+    d.sample_source = (dims->flags & SB_F_SAMPLE_SOURCE) ? 1 : 0;
+    d.warmup = (dims->flags & SB_F_WARMUP) ? 1 : 0;
+    d.Fam = d.inheritance ? dims->n_families : 0;
+    d.C = d.inheritance ? 3 : 2;
+    d.ldx = round_up(d.F, 16);
+    d.ldn = round_up(d.N, 16);
+    if (d.inheritance && d.Fam < 1) FAIL(SB_E_ARG, "inheritance needs n_families >= 1");
+
+    const size_t nc = (size_t)dims->n_chains;
+    ChainArrays& st = ctx->st;
+    const int N = d.N, F = d.F, S = d.S, Z = d.Z, Fam = d.Fam;
+    st.s_zone_id = (size_t)round_up(N, 16);        DA(st.zone_id, nc * st.s_zone_id);
+    st.s_zone_members = (size_t)Z * N;              DA(st.zone_members, nc * st.s_zone_members);
+    st.s_zone_size = (size_t)(Z > 0 ? Z : 1);       DA(st.zone_size, nc * st.s_zone_size);
+    st.s_weights = (size_t)F * 3;                   DA(st.weights, nc * st.s_weights);
+    st.s_wnorm = (size_t)F * 12;                    DA(st.wnorm, nc * st.s_wnorm);
+    st.s_p_global = (size_t)F * S;                  DA(st.p_global, nc * st.s_p_global);
+    st.s_p_zones = (size_t)Z * F * S;               DA(st.p_zones, nc * st.s_p_zones);
+    st.s_p_fam = (size_t)Fam * F * S;               DA(st.p_fam, nc * st.s_p_fam);
+    st.s_source = d.sample_source ? (size_t)N * d.ldx : 0;   DA(st.source, nc * st.s_source);
+    st.s_cnt_glob = (size_t)F * S;                  DA(st.cnt_glob, nc * st.s_cnt_glob);
+    st.s_cnt_zone = (size_t)Z * F * S;              DA(st.cnt_zone, nc * st.s_cnt_zone);
+    st.s_cnt_fam = (size_t)Fam * F * S;             DA(st.cnt_fam, nc * st.s_cnt_fam);
+    st.s_cnt_src = (size_t)F * 12;                  DA(st.cnt_src, nc * st.s_cnt_src);
+    DA(st.ll, nc); DA(st.prior, nc); DA(st.geo, nc);
+    st.s_prior_pg = (size_t)F;                      DA(st.prior_pg, nc * st.s_prior_pg);
+    st.s_prior_pf = (size_t)Fam * F;                DA(st.prior_pf, nc * st.s_prior_pf);
+    DA(st.acc, nc * SB_N_OPS); DA(st.rej, nc * SB_N_OPS); DA(st.step, nc); DA(st.err, nc);
+
+    // K1 tiling: tiles x chains CTAs; aim at >= 4 waves of 148 SMs x 8 resident CTAs when the shape allows
+    int spt = 64;
+    ctx->sites_per_tile = spt;
+    ctx->n_tiles = (N + spt - 1) / spt;
+    DA(ctx->partial, nc * ctx->n_tiles);
+    ctx->geo_cap = N < 4096 ? N : 4096;
+    ctx->h_zone_size.assign(nc * (size_t)(Z > 0 ? Z : 1), 0);
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SB_OK;
+}
+
+int sb_destroy(sb_ctx* ctx) {
+    if (!ctx) return SB_OK;
+    cudaSetDevice(ctx->device);
+    if (ctx->own_stream) cudaStreamSynchronize(ctx->own_stream);
+    for (void* p : ctx->allocs) cudaFree(p);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+    delete ctx;
+    return SB_OK;
+}
+
+int sb_set_stream(sb_ctx* ctx, void* cuda_stream) {
+    if (!ctx) return SB_E_ARG;
+    ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+    return SB_OK;
+}
+
+int sb_sync(sb_ctx* ctx) {
+    if (!ctx) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SB_OK;
+}
+
+int sb_upload_data(sb_ctx* ctx, const uint8_t* x, const uint8_t* applicable, const int16_t* family_id,
+                   const int32_t* adj_indptr, const int32_t* adj_indices, const double* cost) {
+    if (!ctx || !x || !applicable) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    DevData& d = ctx->d;
+    const int N = d.N, F = d.F, S = d.S;
+    if (d.inheritance && !family_id) FAIL(SB_E_ARG, "family_id required with inheritance");
+    if (d.geo_type == SB_GEO_COST_BASED && !cost) FAIL(SB_E_ARG, "cost matrix required by cost_based geo prior");
+
+    std::vector<uint8_t> hx((size_t)N * d.ldx, SB_PAD), hxT((size_t)F * d.ldn, SB_PAD);
+    for (int n = 0; n < N; ++n)
+        for (int f = 0; f < F; ++f) {
+            const uint8_t v = x[(size_t)n * F + f];
+            if (v != SB_NA && v >= S) FAIL(SB_E_ARG, "state index out of range");
+            hx[(size_t)n * d.ldx + f] = v;
+            hxT[(size_t)f * d.ldn + n] = v;
+        }
+    std::vector<uint32_t> mask(F, 0);
+    std::vector<int> napp(F, 0);
+    for (int f = 0; f < F; ++f)
+        for (int s = 0; s < S; ++s)
+            if (applicable[(size_t)f * S + s]) { mask[f] |= 1u << s; ++napp[f]; }
+    for (int f = 0; f < F; ++f)
+        if (napp[f] < 1) FAIL(SB_E_ARG, "feature without applicable state");
+
+    uint8_t *dx, *dxT; uint32_t* dmask; int* dnapp;
+    DA(dx, hx.size()); DA(dxT, hxT.size()); DA(dmask, F); DA(dnapp, F);
+    H2D(dx, hx.data(), hx.size()); H2D(dxT, hxT.data(), hxT.size());
+    H2D(dmask, mask.data(), F); H2D(dnapp, napp.data(), F);
+    d.x = dx; d.xT = dxT; d.app_mask = dmask; d.n_app = dnapp;
+
+    // families: id per site + CSR member lists (ascending site order)
+    std::vector<int16_t> fid(N, -1);
+    std::vector<int> fptr(d.Fam + 1, 0), fsites;
+    if (d.inheritance) {
+        for (int n = 0; n < N; ++n) {
+            fid[n] = family_id[n];
+            if (fid[n] >= d.Fam || fid[n] < -1) FAIL(SB_E_ARG, "family id out of range");
+            if (fid[n] >= 0) ++fptr[fid[n] + 1];
+        }
+        for (int k = 0; k < d.Fam; ++k) fptr[k + 1] += fptr[k];
+        fsites.resize(fptr[d.Fam] > 0 ? fptr[d.Fam] : 1);
+        std::vector<int> pos(fptr.begin(), fptr.end() - 1);
+        for (int n = 0; n < N; ++n)
+            if (fid[n] >= 0) fsites[pos[fid[n]]++] = n;
+    } else {
+        fsites.resize(1);
+    }
+    int16_t* dfid; int *dfptr, *dfs;
+    DA(dfid, N); DA(dfptr, fptr.size()); DA(dfs, fsites.size());
+    H2D(dfid, fid.data(), N); H2D(dfptr, fptr.data(), fptr.size()); H2D(dfs, fsites.data(), fsites.size());
+    d.fam_id = dfid; d.fam_ptr = dfptr; d.fam_sites = dfs;
+
+    // adjacency CSR
+    int *dptr = nullptr, *didx = nullptr;
+    if (adj_indptr && adj_indices) {
+        const int nnz = adj_indptr[N];
+        for (int i = 0; i < nnz; ++i)
+            if (adj_indices[i] < 0 || adj_indices[i] >= N) FAIL(SB_E_ARG, "adjacency index out of range");
+        DA(dptr, N + 1); DA(didx, nnz);
+        H2D(dptr, adj_indptr, N + 1); H2D(didx, adj_indices, nnz);
+    }
+    d.adj_ptr = dptr; d.adj_idx = didx;
+
+    double* dcost = nullptr;
+    if (cost) {
+        DA(dcost, (size_t)N * N);
+        H2D(dcost, cost, (size_t)N * N);
+    }
+    d.cost = dcost;
+    ctx->has_data = true;
+    return SB_OK;
+}
+
+int sb_set_priors(sb_ctx* ctx, const sb_prior_cfg* cfg, const double* gibbs_g, const double* alpha_g,
+                  const double* gibbs_f, const double* alpha_f) {
+    if (!ctx || !cfg) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    DevData& d = ctx->d;
+    if (!ctx->has_data) FAIL(SB_E_STATE, "sb_upload_data must precede sb_set_priors");
+    if (cfg->size_type < 0 || cfg->size_type > 2 || cfg->geo_type < 0 || cfg->geo_type > 1 ||
+        cfg->p_global_type < 0 || cfg->p_global_type > 1 || cfg->p_families_type < 0 || cfg->p_families_type > 1)
+        FAIL(SB_E_ARG, "unknown prior type");
+    if (cfg->geo_type == SB_GEO_COST_BASED && !d.cost) FAIL(SB_E_ARG, "cost_based geo prior needs a cost matrix");
+    if (cfg->geo_type == SB_GEO_COST_BASED && !(cfg->geo_scale > 0)) FAIL(SB_E_ARG, "geo scale must be > 0");
+    if (cfg->p_global_type == SB_DIR_COUNTS && !alpha_g) FAIL(SB_E_ARG, "alpha_global required");
+    if (d.inheritance && cfg->p_families_type == SB_DIR_COUNTS && !alpha_f) FAIL(SB_E_ARG, "alpha_fam required");
+    d.size_type = cfg->size_type; d.geo_type = cfg->geo_type; d.geo_scale = cfg->geo_scale;
+    d.pg_type = cfg->p_global_type; d.pf_type = d.inheritance ? cfg->p_families_type : 0;
+    const int F = d.F, S = d.S, Fam = d.Fam;
+    const size_t FS = (size_t)F * S;
+
+    auto upload_rows = [&](const double* gibbs, const double* alpha, size_t rows, const double** out_gibbs,
+                           const double** out_alpha, const double** out_lnorm) -> int {
+        std::vector<double> g(rows * S, 1.0), a(rows * S, 1.0), ln(rows, 0.0);
+        if (gibbs) memcpy(g.data(), gibbs, g.size() * sizeof(double));
+        if (alpha) {
+            memcpy(a.data(), alpha, a.size() * sizeof(double));
+            std::vector<uint32_t> mask(F);
+            CK(cudaMemcpy(mask.data(), d.app_mask, F * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+            for (size_t r = 0; r < rows; ++r) {
+                double sa = 0.0, sl = 0.0;
+                for (int s = 0; s < S; ++s)
+                    if (mask[r % F] >> s & 1u) { sa += a[r * S + s]; sl += std::lgamma(a[r * S + s]); }
+                ln[r] = std::lgamma(sa) - sl;
+            }
+        }
+        double *dg, *da, *dl;
+        DA(dg, g.size()); DA(da, a.size()); DA(dl, ln.size());
+        H2D(dg, g.data(), g.size()); H2D(da, a.data(), a.size()); H2D(dl, ln.data(), ln.size());
+        *out_gibbs = dg; *out_alpha = da; *out_lnorm = dl;
+        return SB_OK;
+    };
+    int r = upload_rows(gibbs_g, d.pg_type ? alpha_g : nullptr, F, &d.gibbs_g, &d.alpha_g, &d.lnorm_g);
+    if (r != SB_OK) return r;
+    if (d.inheritance) {
+        r = upload_rows(gibbs_f, d.pf_type ? alpha_f : nullptr, (size_t)Fam * F, &d.gibbs_f, &d.alpha_f, &d.lnorm_f);
+        if (r != SB_OK) return r;
+    }
+    (void)FS;
+    ctx->has_priors = true;
+    return SB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// per-chain state
+// ---------------------------------------------------------------------------------------------
+static int check_chain(sb_ctx* ctx, int chain) {
+    if (chain < 0 || chain >= ctx->dims.n_chains) FAIL(SB_E_ARG, "chain index out of range");
+    if (!ctx->has_data) FAIL(SB_E_STATE, "sb_upload_data has not been called");
+    return SB_OK;
+}
+
+static int recount_chain(sb_ctx* ctx, int chain) {
+    const DevData& d = ctx->d;
+    ChainArrays& st = ctx->st;
+    CK(cudaMemsetAsync(st.cnt_glob + chain * st.s_cnt_glob, 0, st.s_cnt_glob * sizeof(int), ctx->stream));
+    CK(cudaMemsetAsync(st.cnt_zone + chain * st.s_cnt_zone, 0, st.s_cnt_zone * sizeof(int), ctx->stream));
+    CK(cudaMemsetAsync(st.cnt_fam + chain * st.s_cnt_fam, 0, st.s_cnt_fam * sizeof(int), ctx->stream));
+    CK(cudaMemsetAsync(st.cnt_src + chain * st.s_cnt_src, 0, st.s_cnt_src * sizeof(int), ctx->stream));
+    if (!d.sample_source) return SB_OK;
+    dim3 grid(ctx->n_tiles, 1);
+    count_kernel<<<grid, 256, 0, ctx->stream>>>(d, st, chain, ctx->sites_per_tile);
+    ++ctx->launches;
+    CK(cudaGetLastError());
+    return SB_OK;
+}
+
+int sb_set_state(sb_ctx* ctx, int chain, const uint8_t* zones, const double* weights, const double* p_global,
+                 const double* p_zones, const double* p_families, const uint8_t* source) {
+    if (!ctx) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    int r = check_chain(ctx, chain);
+    if (r != SB_OK) return r;
+    const DevData& d = ctx->d;
+    ChainArrays& st = ctx->st;
+    const int N = d.N, F = d.F, S = d.S, Z = d.Z, C = d.C, Fam = d.Fam;
+    if (!weights || !p_global || (Z > 0 && (!zones || !p_zones)) || (d.inheritance && !p_families))
+        FAIL(SB_E_ARG, "sb_set_state: missing array");
+    if (d.sample_source && !source) FAIL(SB_E_ARG, "sb_set_state: SAMPLE_SOURCE context needs a source array");
+
+    std::vector<int8_t> zid(st.s_zone_id, -1);
+    std::vector<int> members((size_t)Z * N, 0), sizes(Z > 0 ? Z : 1, 0);
+    for (int z = 0; z < Z; ++z)
+        for (int n = 0; n < N; ++n)
+            if (zones[(size_t)z * N + n]) {
+                if (zid[n] >= 0) FAIL(SB_E_OVERLAP, "sb_set_state: zones overlap (a site belongs to two zones)");
+                zid[n] = (int8_t)z;
+                members[(size_t)z * N + sizes[z]++] = n;
+            }
+    H2D(st.zone_id + chain * st.s_zone_id, zid.data(), zid.size());
+    H2D(st.zone_members + chain * st.s_zone_members, members.data(), members.size());
+    H2D(st.zone_size + chain * st.s_zone_size, sizes.data(), sizes.size());
+    for (int z = 0; z < Z; ++z) ctx->h_zone_size[chain * st.s_zone_size + z] = sizes[z];
+
+    std::vector<double> w3((size_t)F * 3, 0.0);
+    for (int f = 0; f < F; ++f)
+        for (int c = 0; c < C; ++c) w3[(size_t)f * 3 + c] = weights[(size_t)f * C + c];
+    H2D(st.weights + chain * st.s_weights, w3.data(), w3.size());
+    H2D(st.p_global + chain * st.s_p_global, p_global, (size_t)F * S);
+    if (Z > 0) H2D(st.p_zones + chain * st.s_p_zones, p_zones, (size_t)Z * F * S);
+    if (d.inheritance) H2D(st.p_fam + chain * st.s_p_fam, p_families, (size_t)Fam * F * S);
+    if (d.sample_source) {
+        std::vector<uint8_t> hs((size_t)N * d.ldx, 0);
+        for (int n = 0; n < N; ++n)
+            for (int f = 0; f < F; ++f) {
+                const uint8_t s = source[(size_t)n * F + f];
+                if (s >= C) FAIL(SB_E_ARG, "sb_set_state: source component out of range");
+                hs[(size_t)n * d.ldx + f] = s;
+            }
+        H2D(st.source + chain * st.s_source, hs.data(), hs.size());
+    }
+    dim3 grid((F + 127) / 128, 1);
+    wnorm_kernel<<<grid, 128, 0, ctx->stream>>>(d, st, chain);
+    ++ctx->launches;
+    CK(cudaGetLastError());
+    return recount_chain(ctx, chain);
+}
+
+int sb_get_state(sb_ctx* ctx, int chain, uint8_t* zones, double* weights, double* p_global, double* p_zones,
+                 double* p_families, uint8_t* source) {
+    if (!ctx) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    int r = check_chain(ctx, chain);
+    if (r != SB_OK) return r;
+    const DevData& d = ctx->d;
+    ChainArrays& st = ctx->st;
+    const int N = d.N, F = d.F, S = d.S, Z = d.Z, C = d.C, Fam = d.Fam;
+    if (zones && Z > 0) {
+        std::vector<int8_t> zid(st.s_zone_id);
+        D2H(zid.data(), st.zone_id + chain * st.s_zone_id, zid.size());
+        memset(zones, 0, (size_t)Z * N);
+        for (int n = 0; n < N; ++n)
+            if (zid[n] >= 0) zones[(size_t)zid[n] * N + n] = 1;
+    }
+    if (weights) {
+        std::vector<double> w3((size_t)F * 3);
+        D2H(w3.data(), st.weights + chain * st.s_weights, w3.size());
+        for (int f = 0; f < F; ++f)
+            for (int c = 0; c < C; ++c) weights[(size_t)f * C + c] = w3[(size_t)f * 3 + c];
+    }
+    if (p_global) D2H(p_global, st.p_global + chain * st.s_p_global, (size_t)F * S);
+    if (p_zones && Z > 0) D2H(p_zones, st.p_zones + chain * st.s_p_zones, (size_t)Z * F * S);
+    if (p_families && d.inheritance) D2H(p_families, st.p_fam + chain * st.s_p_fam, (size_t)Fam * F * S);
+    if (source) {
+        if (!d.sample_source) FAIL(SB_E_STATE, "context has no source state");
+        std::vector<uint8_t> hs((size_t)N * d.ldx);
+        D2H(hs.data(), st.source + chain * st.s_source, hs.size());
+        for (int n = 0; n < N; ++n) memcpy(source + (size_t)n * F, hs.data() + (size_t)n * d.ldx, F);
+    }
+    return SB_OK;
+}
+
+int sb_copy_state(sb_ctx* ctx, int dst, int src) {
+    if (!ctx) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    int r = check_chain(ctx, dst);
+    if (r == SB_OK) r = check_chain(ctx, src);
+    if (r != SB_OK) return r;
+    if (dst == src) return SB_OK;
+    ChainArrays& st = ctx->st;
+#define CP(arr, stride, T) \
+    CK(cudaMemcpyAsync(st.arr + dst * (stride), st.arr + src * (stride), (stride) * sizeof(T), cudaMemcpyDeviceToDevice, ctx->stream))
+    CP(zone_id, st.s_zone_id, int8_t); CP(zone_members, st.s_zone_members, int); CP(zone_size, st.s_zone_size, int);
+    CP(weights, st.s_weights, double); CP(wnorm, st.s_wnorm, double); CP(p_global, st.s_p_global, double);
+    CP(p_zones, st.s_p_zones, double); CP(p_fam, st.s_p_fam, double); CP(source, st.s_source, uint8_t);
+    CP(cnt_glob, st.s_cnt_glob, int); CP(cnt_zone, st.s_cnt_zone, int); CP(cnt_fam, st.s_cnt_fam, int);
+    CP(cnt_src, st.s_cnt_src, int); CP(prior_pg, st.s_prior_pg, double); CP(prior_pf, st.s_prior_pf, double);
+    CP(ll, (size_t)1, double); CP(prior, (size_t)1, double); CP(geo, (size_t)1, double);
+#undef CP
+    for (size_t z = 0; z < st.s_zone_size; ++z)
+        ctx->h_zone_size[dst * st.s_zone_size + z] = ctx->h_zone_size[src * st.s_zone_size + z];
+    return SB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// stateless evaluation
+// ---------------------------------------------------------------------------------------------
+static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source) {
+    const DevData& d = ctx->d;
+    dim3 gw((d.F + 127) / 128, n);
+    wnorm_kernel<<<gw, 128, 0, ctx->stream>>>(d, ctx->st, chain_begin);
+    dim3 grid(ctx->n_tiles, n);
+    if (use_source)
+        lh_full_kernel<1><<<grid, LH_THREADS, 0, ctx->stream>>>(d, ctx->st, chain_begin, ctx->sites_per_tile,
+                                                               ctx->partial, ctx->n_tiles);
+    else
+        lh_full_kernel<0><<<grid, LH_THREADS, 0, ctx->stream>>>(d, ctx->st, chain_begin, ctx->sites_per_tile,
+                                                               ctx->partial, ctx->n_tiles);
+    lh_reduce_kernel<<<n, 32, 0, ctx->stream>>>(ctx->partial, ctx->n_tiles, ctx->st.ll, chain_begin);
+    ctx->launches += 3;
+    CK(cudaGetLastError());
+    return SB_OK;
+}
+
+static int check_range(sb_ctx* ctx, int chain_begin, int n, int use_source) {
+    if (!ctx->has_data) FAIL(SB_E_STATE, "sb_upload_data has not been called");
+    if (chain_begin < 0 || n < 1 || chain_begin + n > ctx->dims.n_chains) FAIL(SB_E_ARG, "chain range out of bounds");
+    if (use_source && !ctx->d.sample_source) FAIL(SB_E_STATE, "use_source on a context created without SB_F_SAMPLE_SOURCE");
+    return SB_OK;
+}
+
+int sb_eval_likelihood_async(sb_ctx* ctx, int chain_begin, int n, int use_source) {
+    if (!ctx) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    int r = check_range(ctx, chain_begin, n, use_source);
+    if (r != SB_OK) return r;
+    return launch_likelihood(ctx, chain_begin, n, use_source);
+}
+
+int sb_read_ll(sb_ctx* ctx, int chain_begin, int n, double* ll) {
+    if (!ctx || !ll) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    int r = check_range(ctx, chain_begin, n, 0);
+    if (r != SB_OK) return r;
+    D2H(ll, ctx->st.ll + chain_begin, n);
+    return SB_OK;
+}
+
+int sb_eval(sb_ctx* ctx, int chain_begin, int n, int use_source, double* ll, double* prior, double* geo) {
+    if (!ctx) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    int r = check_range(ctx, chain_begin, n, use_source);
+    if (r != SB_OK) return r;
+    if (!ctx->has_priors) FAIL(SB_E_STATE, "sb_set_priors has not been called");
+    const DevData& d = ctx->d;
+    if (d.geo_type == SB_GEO_COST_BASED && d.Z > 0) {
+        for (int c = chain_begin; c < chain_begin + n; ++c) {
+            const int m = ctx->h_zone_size[c * ctx->st.s_zone_size + d.Z - 1];
+            if (m > ctx->geo_cap) FAIL(SB_E_ARG, "geo prior: last zone larger than the Prim scratch (4096 members)");
+        }
+    }
+    r = launch_likelihood(ctx, chain_begin, n, use_source);
+    if (r != SB_OK) return r;
+    const size_t smem = d.geo_type == SB_GEO_COST_BASED ? (size_t)ctx->geo_cap * 9 + 16 : 16;
+    if (smem > 48 * 1024)
+        CK(cudaFuncSetAttribute(prior_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    prior_kernel<<<n, 256, smem, ctx->stream>>>(d, ctx->st, chain_begin, ctx->geo_cap);
+    ++ctx->launches;
+    CK(cudaGetLastError());
+    if (ll) D2H(ll, ctx->st.ll + chain_begin, n);
+    if (prior) D2H(prior, ctx->st.prior + chain_begin, n);
+    if (geo) D2H(geo, ctx->st.geo + chain_begin, n);
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SB_OK;
+}
+
+static int run_components(sb_ctx* ctx, int chain, double* all_lh, double* wnorm, double* post) {
+    const DevData& d = ctx->d;
+    const size_t cells = (size_t)d.N * d.F, n = cells * d.C;
+    double *dl = nullptr, *dw = nullptr, *dp = nullptr;
+    if (all_lh) CK(cudaMalloc((void**)&dl, n * sizeof(double)));
+    if (wnorm) CK(cudaMalloc((void**)&dw, n * sizeof(double)));
+    if (post) CK(cudaMalloc((void**)&dp, n * sizeof(double)));
+    dim3 gw((d.F + 127) / 128, 1);
+    wnorm_kernel<<<gw, 128, 0, ctx->stream>>>(d, ctx->st, chain);
+    components_kernel<<<(unsigned)((cells + 255) / 256), 256, 0, ctx->stream>>>(d, ctx->st, chain, dl, dw, dp);
+    ctx->launches += 2;
+    int r = SB_OK;
+    if (cudaGetLastError() != cudaSuccess) { ctx->err = "components_kernel launch failed"; r = SB_E_CUDA; }
+    if (r == SB_OK && all_lh) r = d2h(ctx, all_lh, dl, n);
+    if (r == SB_OK && wnorm) r = d2h(ctx, wnorm, dw, n);
+    if (r == SB_OK && post) r = d2h(ctx, post, dp, n);
+    cudaStreamSynchronize(ctx->stream);
+    if (dl) cudaFree(dl);
+    if (dw) cudaFree(dw);
+    if (dp) cudaFree(dp);
+    return r;
+}
+
+int sb_eval_components(sb_ctx* ctx, int chain, double* all_lh, double* wnorm) {
+    if (!ctx) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    int r = check_chain(ctx, chain);
+    if (r != SB_OK) return r;
+    return run_components(ctx, chain, all_lh, wnorm, nullptr);
+}
+
+int sb_source_posterior(sb_ctx* ctx, int chain, double* post) {
+    if (!ctx || !post) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    int r = check_chain(ctx, chain);
+    if (r != SB_OK) return r;
+    return run_components(ctx, chain, nullptr, nullptr, post);
+}
+
+int sb_counts(sb_ctx* ctx, int chain, int recount, int32_t* cnt_glob, int32_t* cnt_zone, int32_t* cnt_fam,
+              int32_t* cnt_src_zone, int32_t* cnt_src_fam) {
+    if (!ctx) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    int r = check_chain(ctx, chain);
+    if (r != SB_OK) return r;
+    const DevData& d = ctx->d;
+    ChainArrays& st = ctx->st;
+    if (!d.sample_source) FAIL(SB_E_STATE, "count tables need a SAMPLE_SOURCE context");
+    if (recount) {
+        r = recount_chain(ctx, chain);
+        if (r != SB_OK) return r;
+    }
+    if (cnt_glob) D2H(cnt_glob, st.cnt_glob + chain * st.s_cnt_glob, st.s_cnt_glob);
+    if (cnt_zone) D2H(cnt_zone, st.cnt_zone + chain * st.s_cnt_zone, st.s_cnt_zone);
+    if (cnt_fam && d.inheritance) D2H(cnt_fam, st.cnt_fam + chain * st.s_cnt_fam, st.s_cnt_fam);
+    if (cnt_src_zone || cnt_src_fam) {
+        std::vector<int> cs(st.s_cnt_src);
+        D2H(cs.data(), st.cnt_src + chain * st.s_cnt_src, cs.size());
+        for (int f = 0; f < d.F; ++f)
+            for (int c = 0; c < d.C; ++c) {
+                const int* row = cs.data() + (size_t)f * 12;
+                if (cnt_src_zone) cnt_src_zone[(size_t)f * d.C + c] = row[1 * 3 + c] + row[3 * 3 + c];
+                if (cnt_src_fam) cnt_src_fam[(size_t)f * d.C + c] = row[2 * 3 + c] + row[3 * 3 + c];
+            }
+    }
+    return SB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// sampler
+// ---------------------------------------------------------------------------------------------
+static size_t step_smem_bytes(const StepParams& sp) {
+    const size_t words = 2 * (size_t)sp.nwords + (sp.nwords & 1);
+    return words * sizeof(unsigned) + (size_t)sp.prim_cap * 9 + 16;
+}
+
+static int ensure_step_scratch(sb_ctx* ctx) {
+    StepParams& sp = ctx->sp;
+    const DevData& d = ctx->d;
+    if (!sp.scratch) {
+        sp.s_scratch = (size_t)d.F * d.S;
+        DA(sp.scratch, (size_t)ctx->dims.n_chains * sp.s_scratch);
+        sp.s_tmp = (size_t)d.N;
+        DA(sp.tmp_members, (size_t)ctx->dims.n_chains * sp.s_tmp);
+    }
+    sp.nwords = (d.N + 31) / 32;
+    sp.chain_offset = ctx->dims.chain_offset;
+    return SB_OK;
+}
+
+int sb_set_operators(sb_ctx* ctx, const sb_operator_cfg* cfg, const double* p_grow, const int32_t* max_size) {
+    if (!ctx || !cfg || !p_grow || !max_size) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    if (!ctx->has_data || !ctx->has_priors) FAIL(SB_E_STATE, "sb_upload_data / sb_set_priors must precede sb_set_operators");
+    const DevData& d = ctx->d;
+    if (cfg->n_ops < 1 || cfg->n_ops > SB_N_OPS) FAIL(SB_E_ARG, "n_ops out of range");
+    StepParams& sp = ctx->sp;
+    double total = 0.0;
+    for (int i = 0; i < cfg->n_ops; ++i) {
+        const int op = cfg->op_ids[i];
+        if (op < 0 || op >= SB_N_OPS) FAIL(SB_E_ARG, "unknown operator id");
+        if (!(cfg->op_prob[i] >= 0.0)) FAIL(SB_E_ARG, "negative operator probability");
+        if (cfg->op_prob[i] > 0.0) {
+            const bool gibbs = op >= SB_OP_GIBBS_SOURCES && op <= SB_OP_GIBBS_P_FAMILIES;
+            const bool alter = op >= SB_OP_ALTER_WEIGHTS;
+            if (gibbs && !d.sample_source) FAIL(SB_E_ARG, "gibbs_* operators need SAMPLE_SOURCE");
+            if (alter && d.sample_source) FAIL(SB_E_ARG, "alter_* operators are not defined with SAMPLE_SOURCE (mcmc_setup.py:80-94)");
+            if ((op == SB_OP_GIBBS_P_FAMILIES || op == SB_OP_ALTER_P_FAMILIES) && !d.inheritance)
+                FAIL(SB_E_ARG, "family operator without inheritance");
+            if ((op <= SB_OP_SWAP_ZONE || op == SB_OP_GIBBS_P_ZONES || op == SB_OP_ALTER_P_ZONES) && d.Z < 1)
+                FAIL(SB_E_ARG, "zone operator with zero zones");
+            if (op <= SB_OP_SWAP_ZONE && !d.adj_ptr) FAIL(SB_E_ARG, "zone moves need the adjacency CSR");
+        }
+        total += cfg->op_prob[i];
+    }
+    if (!(total > 0.0)) FAIL(SB_E_ARG, "operator probabilities sum to zero");
+    // keep operators with positive probability only; CDF normalised like np.random.choice(p=...)
+    int m = 0;
+    double run = 0.0;
+    for (int i = 0; i < cfg->n_ops; ++i) {
+        if (cfg->op_prob[i] <= 0.0) continue;
+        run += cfg->op_prob[i] / total;
+        sp.op_ids[m] = cfg->op_ids[i];
+        sp.op_cdf[m] = run;
+        ++m;
+    }
+    sp.n_ops = m;
+    sp.prec_w = cfg->precision_weights; sp.prec_g = cfg->precision_p_global;
+    sp.prec_z = cfg->precision_p_zones; sp.prec_f = cfg->precision_p_families;
+    sp.min_size = cfg->min_size;
+    sp.frac = cfg->gibbs_feature_fraction;
+    sp.seed_lo = (uint32_t)cfg->seed; sp.seed_hi = (uint32_t)(cfg->seed >> 32);
+    int r = ensure_step_scratch(ctx);
+    if (r != SB_OK) return r;
+    const int nc = ctx->dims.n_chains;
+    if (!ctx->d_pgrow) { DA(ctx->d_pgrow, nc); DA(ctx->d_maxsize, nc); }
+    int cap = 2;
+    for (int c = 0; c < nc; ++c) {
+        if (!(p_grow[c] >= 0.0 && p_grow[c] <= 1.0)) FAIL(SB_E_ARG, "p_grow_connected outside [0,1]");
+        if (max_size[c] < 1) FAIL(SB_E_ARG, "max_size < 1");
+        if (max_size[c] + 1 > cap) cap = max_size[c] + 1;
+    }
+    for (int v : ctx->h_zone_size) if (v + 1 > cap) cap = v + 1;
+    if (cap > d.N) cap = d.N;
+    H2D(ctx->d_pgrow, p_grow, nc);
+    H2D(ctx->d_maxsize, max_size, nc);
+    sp.p_grow = ctx->d_pgrow; sp.max_size = ctx->d_maxsize;
+    sp.prim_cap = d.geo_type == SB_GEO_COST_BASED ? cap : 0;
+    ctx->step_smem = step_smem_bytes(sp);
+    if (ctx->step_smem > 200 * 1024) FAIL(SB_E_ARG, "step kernel scratch exceeds shared memory (N or MAX_M too large)");
+    if (ctx->step_smem > 48 * 1024) {
+        CK(cudaFuncSetAttribute(mcmc_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->step_smem));
+        CK(cudaFuncSetAttribute(move_log_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->step_smem));
+    }
+    ctx->has_ops = true;
+    return SB_OK;
+}
+
+int sb_run(sb_ctx* ctx, int64_t n_steps) {
+    if (!ctx || n_steps < 0) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    if (!ctx->has_ops) FAIL(SB_E_STATE, "sb_set_operators has not been called");
+    if (n_steps == 0) return SB_OK;
+    mcmc_step_kernel<<<ctx->dims.n_chains, STEP_THREADS, ctx->step_smem, ctx->stream>>>(ctx->d, ctx->st, ctx->sp,
+                                                                                       (long long)n_steps);
+    ++ctx->launches;
+    ctx->steps_done += n_steps;
+    CK(cudaGetLastError());
+    return SB_OK;
+}
+
+int sb_read_chain_scalars(sb_ctx* ctx, double* ll, double* prior) {
+    if (!ctx) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    if (ll) D2H(ll, ctx->st.ll, ctx->dims.n_chains);
+    if (prior) D2H(prior, ctx->st.prior, ctx->dims.n_chains);
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SB_OK;
+}
+
+int sb_read_op_stats(sb_ctx* ctx, int64_t* accepted, int64_t* rejected) {
+    if (!ctx) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    const size_t n = (size_t)ctx->dims.n_chains * SB_N_OPS;
+    if (accepted) D2H((unsigned long long*)accepted, ctx->st.acc, n);
+    if (rejected) D2H((unsigned long long*)rejected, ctx->st.rej, n);
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SB_OK;
+}
+
+int sb_step_counter(sb_ctx* ctx, int64_t* steps_done) {
+    if (!ctx || !steps_done) return SB_E_ARG;
+    *steps_done = ctx->steps_done;
+    return SB_OK;
+}
+
+int sb_kernel_launches(sb_ctx* ctx, int64_t* launches) {
+    if (!ctx || !launches) return SB_E_ARG;
+    *launches = ctx->launches;
+    return SB_OK;
+}
+
+int sb_move_log_q(sb_ctx* ctx, int chain, int kind, int zone, int site_new, int site_removed, double rho,
+                  double* log_q, double* log_q_back) {
+    if (!ctx || !log_q || !log_q_back) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    int r = check_chain(ctx, chain);
+    if (r != SB_OK) return r;
+    const DevData& d = ctx->d;
+    if (!d.adj_ptr) FAIL(SB_E_STATE, "no adjacency uploaded");
+    if (zone < 0 || zone >= d.Z) FAIL(SB_E_ARG, "zone out of range");
+    if (kind != SB_OP_GROW_ZONE && kind != SB_OP_SHRINK_ZONE && kind != SB_OP_SWAP_ZONE) FAIL(SB_E_ARG, "kind");
+    if (kind != SB_OP_SHRINK_ZONE && (site_new < 0 || site_new >= d.N)) FAIL(SB_E_ARG, "site_new out of range");
+    if (kind != SB_OP_GROW_ZONE && (site_removed < 0 || site_removed >= d.N)) FAIL(SB_E_ARG, "site_removed out of range");
+    r = ensure_step_scratch(ctx);
+    if (r != SB_OK) return r;
+    const size_t smem = step_smem_bytes(ctx->sp);
+    if (smem > 48 * 1024)
+        CK(cudaFuncSetAttribute(move_log_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    double* dout;
+    CK(cudaMalloc((void**)&dout, 2 * sizeof(double)));
+    move_log_q_kernel<<<1, STEP_THREADS, smem, ctx->stream>>>(d, ctx->st, ctx->sp, chain, kind, zone, site_new,
+                                                             site_removed, rho, dout);
+    ++ctx->launches;
+    double h[2] = {0, 0};
+    r = d2h(ctx, h, dout, 2);
+    cudaFree(dout);
+    if (r != SB_OK) return r;
+    *log_q = h[0]; *log_q_back = h[1];
+    return SB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,155 @@
+// sb_common.cuh -- device-side data model shared by all kernels of libsbayes_b200.so (sm_100a).
+//
+// HBM layout (DESIGN.md "Data layout"):
+//   immutable, one copy per GPU, shared by all chains (L2-resident at every shape we run):
+//     x    u8 [N][ldx]   state index per (site, feature), row = site; 255 = NA, 254 = row padding
+//     xT   u8 [F][ldn]   the same, row = feature (column operators: alter_*, gibbs_p_global)
+//     fam  i16[N]        family id or -1;  fam_ptr/fam_sites: CSR member lists of the families
+//     adj  CSR           Delaunay adjacency (neighbourhood of a zone)
+//     cost f64[N][N]     dense cost matrix of the geo prior (optional)
+//   per chain (struct-of-arrays over chains, chain-major):
+//     zone_id i8[N], zone_members i32[Z][N], zone_size i32[Z], weights f64[F][3], wnorm f64[F][4][3],
+//     p_global f64[F][S], p_zones f64[Z][F][S], p_fam f64[Fam][F][S], source u8[N][ldx],
+//     cnt_glob i32[F][S], cnt_zone i32[Z][F][S], cnt_fam i32[Fam][F][S], cnt_src i32[F][4][3]
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+
+#define SB_NA 255
+#define SB_PAD 254
+#define SB_MAX_S 32
+#define SB_MAX_Z 64
+#define SB_LN2 0.693147180559945309417232121458
+
+struct DevData {
+    int N, F, S, Z, Fam, C;
+    int ldx;   // padded row length of x / source (multiple of 16)
+    int ldn;   // padded row length of xT (multiple of 16)
+    int inheritance, sample_source, warmup;
+    const uint8_t* x;
+    const uint8_t* xT;
+    const int16_t* fam_id;
+    const int* fam_ptr;
+    const int* fam_sites;
+    const uint32_t* app_mask;   // [F] bit s set <=> state s applicable (data.states)
+    const int* n_app;           // [F]
+    const int* adj_ptr;
+    const int* adj_idx;
+    const double* cost;         // may be null
+    // priors
+    int size_type, geo_type, pg_type, pf_type;
+    double geo_scale;
+    const double* gibbs_g;      // [F][S]     prior_p_global.counts
+    const double* alpha_g;      // [F][S]     Dirichlet density alpha (counts prior)
+    const double* lnorm_g;      // [F]        lgamma(sum a) - sum lgamma(a)
+    const double* gibbs_f;      // [Fam][F][S]
+    const double* alpha_f;      // [Fam][F][S]
+    const double* lnorm_f;      // [Fam][F]
+};
+
+// Pointers to chain 0 of every per-chain array plus the per-chain strides (in elements).
+struct ChainArrays {
+    int8_t* zone_id;      size_t s_zone_id;
+    int* zone_members;    size_t s_zone_members;
+    int* zone_size;       size_t s_zone_size;
+    double* weights;      size_t s_weights;      // [F][3]
+    double* wnorm;        size_t s_wnorm;        // [F][4][3]   cfg = has_zone + 2*has_family
+    double* p_global;     size_t s_p_global;
+    double* p_zones;      size_t s_p_zones;
+    double* p_fam;        size_t s_p_fam;
+    uint8_t* source;      size_t s_source;
+    int* cnt_glob;        size_t s_cnt_glob;
+    int* cnt_zone;        size_t s_cnt_zone;
+    int* cnt_fam;         size_t s_cnt_fam;
+    int* cnt_src;         size_t s_cnt_src;      // [F][4][3]
+    double* ll;           // [chains] running log-likelihood
+    double* prior;        // [chains] running log-prior
+    double* geo;          // [chains] geo-prior term
+    double* prior_pg;     size_t s_prior_pg;     // [F]      per-feature Dirichlet prior terms (cache)
+    double* prior_pf;     size_t s_prior_pf;     // [Fam][F]
+    unsigned long long* acc;   // [chains][SB_N_OPS]
+    unsigned long long* rej;   // [chains][SB_N_OPS]
+    unsigned long long* step;  // [chains] steps done so far (RNG counter)
+    int* err;                  // [chains] sticky error flags
+};
+
+// ---------------------------------------------------------------------------------------------
+// Sum of logs as the log of a running product: one fp64 multiply per factor instead of one fp64 log.
+// The mantissa is renormalised (exponent moved into an integer) every SB_LP_PERIOD factors; factors
+// below 2^-120 (incl. 0 and subnormals) take the exact slow path through log().  Relative error of the
+// result is ~ n_factors * 2^-53 on the product, i.e. ~1e-16 absolute per factor on the log -- far inside
+// the 1e-9 relative parity bound (tests/test_gpu_parity.py).
+// ---------------------------------------------------------------------------------------------
+#define SB_LP_PERIOD 8
+struct LogProd {
+    double m;      // mantissa product, in [2^-960, 2)
+    double side;   // exact logs of tiny factors (may be -inf)
+    int e;         // accumulated binary exponent
+    int k;         // factors since the last renormalisation
+};
+__device__ __forceinline__ void lp_init(LogProd& a) { a.m = 1.0; a.side = 0.0; a.e = 0; a.k = 0; }
+__device__ __forceinline__ void lp_renorm(LogProd& a) {
+    int hi = __double2hiint(a.m);
+    a.e += ((hi >> 20) & 0x7ff) - 1023;
+    a.m = __hiloint2double((hi & 0x800fffff) | 0x3ff00000, __double2loint(a.m));
+    a.k = 0;
+}
+__device__ __forceinline__ void lp_mul(LogProd& a, double v) {
+    if (__double2hiint(v) < 0x38700000) {   // v < 2^-120, zero, subnormal (or negative/NaN): exact path
+        a.side += log(v);
+    } else {
+        a.m *= v;
+        if (++a.k == SB_LP_PERIOD) lp_renorm(a);
+    }
+}
+__device__ __forceinline__ double lp_value(LogProd& a) {
+    lp_renorm(a);
+    return log(a.m) + (double)a.e * SB_LN2 + a.side;
+}
+
+// ---------------------------------------------------------------------------------------------
+// deterministic block reductions (fixed shuffle tree + fixed warp order)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ int warp_sum_i(int v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+// Result valid in every thread. `red` = shared scratch of >= 33 doubles.
+__device__ __forceinline__ double block_sum(double v, double* red) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) red[w] = v;
+    __syncthreads();
+    if (w == 0) {
+        double t = lane < nw ? red[lane] : 0.0;
+        t = warp_sum(t);
+        if (lane == 0) red[32] = t;
+    }
+    __syncthreads();
+    return red[32];
+}
+__device__ __forceinline__ int block_sum_i(int v, int* red) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    v = warp_sum_i(v);
+    __syncthreads();
+    if (lane == 0) red[w] = v;
+    __syncthreads();
+    if (w == 0) {
+        int t = lane < nw ? red[lane] : 0;
+        t = warp_sum_i(t);
+        if (lane == 0) red[32] = t;
+    }
+    __syncthreads();
+    return red[32];
+}
+
+// xlogy semantics of scipy (dirichlet._logpdf): 0 * log(0) = 0
+__device__ __forceinline__ double xlogy_d(double a, double p) { return a == 0.0 ? 0.0 : a * log(p); }

@@ -1,0 +1,722 @@
+// sb_step.cuh -- K5/K7/K8: the persistent per-chain MCMC step kernel.
+//
+// One CTA owns one chain for the whole launch and runs `n_steps` Metropolis-Hastings / Gibbs steps
+// (MCMCGenerative.step, mcmc_generative.py:282-329) without any host round-trip.  All proposals are DELTAS
+// on the resident chain state (no Sample.copy(), zone_sampling.py:95-115):
+//   zone moves      O(F*C) marginal-likelihood ratio of the moved site(s)       (K5)
+//   alter_*         O(N) / O(|zone|) / O(|family|) column delta on feature f    (K5)
+//   gibbs_*         O(F*S) draws from the integer count tables                   (K4 tables)
+// and only an ACCEPTED zone move (or gibbs_sample_sources) pays the O(N*F) source-resampling pass that the
+// reference pays three times per zone proposal (zone_sampling.py:801-809,859-862).
+#pragma once
+#include "sb_common.cuh"
+#include "sb_rng.cuh"
+#include "sb_eval.cuh"
+#include "../../include/sbayes_b200.h"
+
+#define STEP_THREADS 512
+
+struct StepParams {
+    int n_ops;
+    int op_ids[SB_N_OPS];
+    double op_cdf[SB_N_OPS];
+    double prec_w, prec_g, prec_z, prec_f;
+    int min_size;
+    double frac;
+    uint32_t seed_lo, seed_hi;
+    int chain_offset;
+    const double* p_grow;     // [chains]
+    const int* max_size;      // [chains]
+    int nwords;               // words of one site bitmap
+    int prim_cap;             // member capacity of the Prim scratch
+    double* scratch;          // [chains][F*S]   Gamma draws of the Gibbs operators
+    size_t s_scratch;
+    int* tmp_members;         // [chains][N]     candidate member list for the geo prior
+    size_t s_tmp;
+};
+
+// ---- site bitmaps in shared memory -----------------------------------------------------------
+__device__ __forceinline__ void bits_clear(unsigned* bits, int nwords) {
+    for (int i = threadIdx.x; i < nwords; i += blockDim.x) bits[i] = 0u;
+}
+__device__ __forceinline__ bool bit_test(const unsigned* bits, int n) { return bits[n >> 5] >> (n & 31) & 1u; }
+
+// number of set bits (all threads get the result)
+__device__ __forceinline__ int bits_count(const unsigned* bits, int nwords, int* redi) {
+    int c = 0;
+    for (int i = threadIdx.x; i < nwords; i += blockDim.x) c += __popc(bits[i]);
+    return block_sum_i(c, redi);
+}
+
+// index of the k-th (0-based) set bit, ascending site order == order of `candidates.nonzero()[0]`
+// (zone_sampling.py:744,836).  Executed by warp 0; result broadcast through *out.  Caller syncs.
+__device__ void bits_select(const unsigned* bits, int nwords, int k, int* out) {
+    if (threadIdx.x >= 32) return;
+    const int lane = threadIdx.x;
+    const int per = (nwords + 31) / 32;
+    const int b = lane * per, e = min(nwords, b + per);
+    int c = 0;
+    for (int i = b; i < e; ++i) c += __popc(bits[i]);
+    int incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    const int excl = incl - c;
+    if (k >= excl && k < incl) {
+        int r = k - excl;
+        for (int i = b; i < e; ++i) {
+            const int pc = __popc(bits[i]);
+            if (r < pc) {
+                unsigned w = bits[i];
+                for (int j = 0; j < r; ++j) w &= w - 1;      // drop the r lowest set bits
+                *out = (i << 5) + (__ffs(w) - 1);
+                break;
+            }
+            r -= pc;
+        }
+    }
+}
+
+// free[n] = site n is in no zone  (== ~occupied, zone_sampling.py:714,799)
+__device__ void build_free_bits(const DevData& d, const int8_t* zone_id, unsigned* bits, int nwords) {
+    for (int w = threadIdx.x; w < nwords; w += blockDim.x) {
+        unsigned v = 0u;
+        const int n0 = w << 5;
+        for (int j = 0; j < 32; ++j) {
+            const int n = n0 + j;
+            if (n < d.N && zone_id[n] < 0) v |= 1u << j;
+        }
+        bits[w] = v;
+    }
+}
+
+// neighbours of zone z: (adj_mat @ zone) & ~occupied (util.py:139-155).  `skip` (-1 = none) is a member that is
+// treated as already removed (its adjacency does not count and it is itself free) -- the back step of shrink_zone
+// (zone_sampling.py:906-908).
+__device__ void build_nbr_bits(const DevData& d, const int8_t* zone_id, const int* members, int size, int skip,
+                               unsigned* bits, int nwords) {
+    bits_clear(bits, nwords);
+    __syncthreads();
+    // one warp per member, lanes over its adjacency row
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int i = w; i < size; i += nw) {
+        const int m = members[i];
+        if (m == skip) continue;
+        const int b = d.adj_ptr[m], e = d.adj_ptr[m + 1];
+        for (int j = b + lane; j < e; j += 32) {
+            const int n = d.adj_idx[j];
+            if (zone_id[n] < 0 || n == skip) atomicOr(&bits[n >> 5], 1u << (n & 31));
+        }
+    }
+    __syncthreads();
+}
+
+// ---- per-chain view ------------------------------------------------------------------------------
+struct Chain {
+    int8_t* zone_id; int* members; int* zsize;
+    double* w; double* wn; double* pg; double* pz; double* pf;
+    uint8_t* src;
+    int* cg; int* cz; int* cf; int* cs;
+    double* ppg; double* ppf;
+    double* scratch; int* tmp;
+};
+__device__ __forceinline__ Chain chain_view(const ChainArrays& st, const StepParams& sp, int c) {
+    Chain k;
+    k.zone_id = st.zone_id + c * st.s_zone_id; k.members = st.zone_members + c * st.s_zone_members;
+    k.zsize = st.zone_size + c * st.s_zone_size;
+    k.w = st.weights + c * st.s_weights; k.wn = st.wnorm + c * st.s_wnorm;
+    k.pg = st.p_global + c * st.s_p_global; k.pz = st.p_zones + c * st.s_p_zones; k.pf = st.p_fam + c * st.s_p_fam;
+    k.src = st.source + c * st.s_source;
+    k.cg = st.cnt_glob + c * st.s_cnt_glob; k.cz = st.cnt_zone + c * st.s_cnt_zone;
+    k.cf = st.cnt_fam + c * st.s_cnt_fam; k.cs = st.cnt_src + c * st.s_cnt_src;
+    k.ppg = st.prior_pg + c * st.s_prior_pg; k.ppf = st.prior_pf + c * st.s_prior_pf;
+    k.scratch = sp.scratch + c * sp.s_scratch; k.tmp = sp.tmp_members + c * sp.s_tmp;
+    return k;
+}
+
+// mixture value of one cell: sum_c w~[f][cfg][c] * p_c[f][x]   (model.py:174-175); x must not be NA
+__device__ __forceinline__ double cell_mix(const DevData& d, const Chain& k, int f, int xs, int zid, int fam,
+                                           const double* wrow /* wn[f] or a candidate row, [4][3] */) {
+    const int cfg = (zid >= 0 ? 1 : 0) + (fam >= 0 ? 2 : 0);
+    const double* w = wrow + cfg * 3;
+    const size_t o = (size_t)f * d.S + xs;
+    double mix = w[0] * k.pg[o];
+    if (zid >= 0) mix += w[1] * k.pz[(size_t)zid * d.F * d.S + o];
+    if (fam >= 0) mix += w[2] * k.pf[(size_t)fam * d.F * d.S + o];
+    return mix;
+}
+
+// K5a: log marginal-likelihood change of ONE site whose zone assignment changes zid_old -> zid_new
+// (either may be -1).  Sum over features of log mix_new - log mix_old; NA cells contribute 0 in both the
+// source-free likelihood (model.py:247) and the source-marginalised Hastings ratio.
+__device__ double site_zone_delta(const DevData& d, const Chain& k, int site, int zid_old, int zid_new, double* red) {
+    const int fam = d.inheritance ? d.fam_id[site] : -1;
+    double acc = 0.0;
+    for (int f = threadIdx.x; f < d.F; f += blockDim.x) {
+        const int xs = d.x[(size_t)site * d.ldx + f];
+        if (xs == SB_NA) continue;
+        const double* wrow = k.wn + (size_t)f * 12;
+        acc += log(cell_mix(d, k, f, xs, zid_new, fam, wrow)) - log(cell_mix(d, k, f, xs, zid_old, fam, wrow));
+    }
+    return block_sum(acc, red);
+}
+
+// ---- K7a: resample every source cell from its posterior, rebuild all count tables, return the new
+// complete-data log-likelihood sum log(w~ * lh)[source]  (gibbs_sample_sources, zone_sampling.py:180-220;
+// sample_categorical, preprocessing.py:321-348: first c with u < cumsum(post)[c], else 0).
+__device__ double resample_all_sources(const DevData& d, const Chain& k, RngKey key, uint64_t step, double* red) {
+    const int S = d.S, F = d.F, C = d.C;
+    const size_t FS = (size_t)F * S;
+    for (size_t i = threadIdx.x; i < FS; i += blockDim.x) k.cg[i] = 0;
+    for (size_t i = threadIdx.x; i < (size_t)d.Z * FS; i += blockDim.x) k.cz[i] = 0;
+    for (size_t i = threadIdx.x; i < (size_t)d.Fam * FS; i += blockDim.x) k.cf[i] = 0;
+    for (size_t i = threadIdx.x; i < (size_t)F * 12; i += blockDim.x) k.cs[i] = 0;
+    __syncthreads();
+    const int upr = d.ldx >> 4;
+    const int units = d.N * upr;
+    LogProd acc;
+    lp_init(acc);
+    for (int u = threadIdx.x; u < units; u += blockDim.x) {
+        const int n = u / upr;
+        const int f0 = (u - n * upr) << 4;
+        const uint4 xv = *reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + f0);
+        const int zid = k.zone_id[n];
+        const int fam = d.inheritance ? d.fam_id[n] : -1;
+        const int cfg = (zid >= 0 ? 1 : 0) + (fam >= 0 ? 2 : 0);
+        const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+        uint32_t sw[4] = {0u, 0u, 0u, 0u};
+        for (int j = 0; j < 16; j += 2) {
+            const Draw dr = rng_draw(key, step, RP_SOURCE, 0, (uint32_t)(u * 8 + (j >> 1)));
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int jj = j + h;
+                const int xs = (xw[jj >> 2] >> ((jj & 3) * 8)) & 0xff;
+                if (xs == SB_PAD) continue;
+                const int f = f0 + jj;
+                const double* w = k.wn + (size_t)f * 12 + cfg * 3;
+                double t0 = w[0], t1 = w[1], t2 = C == 3 ? w[2] : 0.0;
+                if (xs != SB_NA) {
+                    const size_t o = (size_t)f * S + xs;
+                    t0 *= k.pg[o];
+                    t1 = zid >= 0 ? t1 * k.pz[(size_t)zid * FS + o] : 0.0;
+                    t2 = fam >= 0 ? t2 * k.pf[(size_t)fam * FS + o] : 0.0;
+                }
+                const double tot = (t0 + t1) + t2;
+                const double p0 = t0 / tot, p1 = t1 / tot, p2 = t2 / tot;
+                const double uu = h == 0 ? dr.u0 : dr.u1;
+                int s = 0;
+                if (uu < p0) s = 0;
+                else if (uu < p0 + p1) s = 1;
+                else if (C == 3 && uu < (p0 + p1) + p2) s = 2;
+                const double ts = s == 0 ? t0 : (s == 1 ? t1 : t2);
+                lp_mul(acc, ts);
+                sw[jj >> 2] |= (uint32_t)s << ((jj & 3) * 8);
+                atomicAdd(k.cs + (size_t)f * 12 + cfg * 3 + s, 1);
+                if (xs != SB_NA) {
+                    if (s == 0) atomicAdd(k.cg + (size_t)f * S + xs, 1);
+                    else if (s == 1) atomicAdd(k.cz + (size_t)zid * FS + (size_t)f * S + xs, 1);
+                    else atomicAdd(k.cf + (size_t)fam * FS + (size_t)f * S + xs, 1);
+                }
+            }
+        }
+        *reinterpret_cast<uint4*>(k.src + (size_t)n * d.ldx + f0) = make_uint4(sw[0], sw[1], sw[2], sw[3]);
+    }
+    const double v = block_sum(lp_value(acc), red);
+    return v;
+}
+
+// ---- shared scratch of the step kernel -----------------------------------------------------------
+struct StepShared {
+    double red[33];
+    int redi[33];
+    int pick;           // bits_select result
+    double dshare[4];
+};
+
+// prior terms that depend on the zones: size prior (model.py:932-972) and geo prior (:1096-1139, last zone only)
+__device__ __forceinline__ double size_prior_of(const DevData& d, const int* zsize, int z_changed, int new_size) {
+    if (d.size_type == 0) return 0.0;
+    double p = 0.0;
+    for (int z = 0; z < d.Z; ++z) {
+        const double k = (double)(z == z_changed ? new_size : zsize[z]);
+        p -= d.size_type == 1 ? log_binom_d((double)d.N, k) : log(k * k);
+    }
+    return p;
+}
+
+__device__ double geo_prior_of(const DevData& d, const int* members, int M, double* key, unsigned char* intree,
+                               StepShared& sh) {
+    double sum; int cnt;
+    prim_mst(d.cost, d.N, members, M, key, intree, sh.red, sh.redi, &sum, &cnt);
+    return cnt > 0 ? (-(double)cnt * log(d.geo_scale) - sum / d.geo_scale) / (double)cnt : -log(d.geo_scale);
+}
+
+// q of adding `site` to a zone whose neighbour bitmap is `nbr`: (1-rho)/n_free + [site in nbr] rho/n_nbr
+// (zone_sampling.py:839-845, 757-770, 910-917)
+__device__ __forceinline__ double grow_q(bool in_nbr, int n_free, int n_nbr, double rho) {
+    double q = (1.0 - rho) / (double)n_free;
+    if (in_nbr) q += rho / (double)n_nbr;
+    return q;
+}
+
+// K7b: grow / shrink / swap (zone_sampling.py:704-933 and the warm-up variants :1328-1574).
+// Returns true if accepted.  ll / prior / geo are the chain's running values (updated on accept).
+__device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain& k, int kind, int chain,
+                             RngKey key, uint64_t step, double& ll, double& prior, double& geo,
+                             unsigned* nbr, unsigned* freeb, double* prim_key, unsigned char* prim_tree,
+                             StepShared& sh) {
+    const double rho = sp.p_grow[chain];
+    const int max_size = sp.max_size[chain];
+    const int z = rng_int(key, step, RP_ZONE, 0, d.Z);
+    const int size = k.zsize[z];
+    int* mem = k.members + (size_t)z * d.N;
+    if (kind == SB_OP_GROW_ZONE && size >= max_size) return false;        // :818-820
+    if (kind == SB_OP_SHRINK_ZONE && size <= sp.min_size) return false;   // :894-896
+
+    int n_occ = 0;
+    for (int i = 0; i < d.Z; ++i) n_occ += k.zsize[i];
+    const int n_free = d.N - n_occ;
+    int site_new = -1, site_removed = -1;
+    double q, q_back;
+
+    if (kind != SB_OP_SHRINK_ZONE) {
+        build_nbr_bits(d, k.zone_id, mem, size, -1, nbr, sp.nwords);
+        const int n_nbr = bits_count(nbr, sp.nwords, sh.redi);
+        const bool connected = rng_uniform(key, step, RP_CONNECTED, 0) < rho;     // :731,823
+        const int n_cand = connected ? n_nbr : n_free;
+        if (n_cand == 0) return false;                                            // :740-741, 832-833
+        const int pick = rng_int(key, step, RP_SITE_NEW, 0, n_cand);
+        if (connected) {
+            bits_select(nbr, sp.nwords, pick, &sh.pick);
+        } else {
+            build_free_bits(d, k.zone_id, freeb, sp.nwords);
+            __syncthreads();
+            bits_select(freeb, sp.nwords, pick, &sh.pick);
+        }
+        __syncthreads();
+        site_new = sh.pick;
+        q = grow_q(bit_test(nbr, site_new), n_free, n_nbr, rho);
+        if (kind == SB_OP_GROW_ZONE) {
+            q_back = 1.0 / (double)(size + 1);                                    // :848
+        } else {
+            site_removed = mem[rng_int(key, step, RP_SITE_REMOVED, 0, size)];     // :748-750
+            q_back = grow_q(false, n_free, n_nbr, rho);    // old zone's neighbourhood never holds a member (:753,768)
+        }
+    } else {
+        site_removed = mem[rng_int(key, step, RP_SITE_REMOVED, 0, size)];         // :899-901
+        q = 1.0 / (double)size;                                                   // :904
+        build_nbr_bits(d, k.zone_id, mem, size, site_removed, nbr, sp.nwords);    // :906-908
+        const int n_nbr_back = bits_count(nbr, sp.nwords, sh.redi);
+        q_back = grow_q(bit_test(nbr, site_removed), n_free + 1, n_nbr_back, rho);   // :911-917
+        if (d.warmup) q_back = 1.0 / (double)(size + 1);                          // :1552 (quirk Q3)
+    }
+    __syncthreads();
+
+    // likelihood ratio of the moved site(s)
+    double dll = 0.0;
+    if (site_new >= 0) dll += site_zone_delta(d, k, site_new, -1, z, sh.red);
+    if (site_removed >= 0) dll += site_zone_delta(d, k, site_removed, z, -1, sh.red);
+
+    // prior ratio: only the size and geo terms depend on the zones
+    const int new_size = size + (site_new >= 0 ? 1 : 0) - (site_removed >= 0 ? 1 : 0);
+    double dprior = 0.0;
+    if (d.size_type != 0) dprior += size_prior_of(d, k.zsize, z, new_size) - size_prior_of(d, k.zsize, -1, 0);
+    double geo_new = geo;
+    if (d.geo_type == 1 && z == d.Z - 1) {
+        int m = 0;
+        if (threadIdx.x == 0) {
+            for (int i = 0; i < size; ++i)
+                if (mem[i] != site_removed) k.tmp[m++] = mem[i];
+            if (site_new >= 0) k.tmp[m++] = site_new;
+        }
+        __syncthreads();
+        geo_new = geo_prior_of(d, k.tmp, min(new_size, sp.prim_cap), prim_key, prim_tree, sh);
+        dprior += geo_new - geo;
+    }
+
+    bool accept;
+    if (d.warmup && d.sample_source) {
+        accept = true;      // warm-up forces as_gibbs=True in gibbs_sample_sources => log_q = -inf => accept (:1293-1296)
+    } else {
+        const double mh = dll - (log(q) - log(q_back)) + dprior;                  // mcmc_generative.py:345-349
+        accept = log(rng_uniform(key, step, RP_ACCEPT, 0)) < mh;                  // :318
+    }
+    if (!accept) return false;
+
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (site_removed >= 0) {
+            int i = 0;
+            while (mem[i] != site_removed) ++i;
+            mem[i] = mem[size - 1];
+            k.zone_id[site_removed] = -1;
+        }
+        if (site_new >= 0) {
+            mem[new_size - 1] = site_new;
+            k.zone_id[site_new] = (int8_t)z;
+        }
+        k.zsize[z] = new_size;
+    }
+    __syncthreads();
+    prior += dprior;
+    geo = geo_new;
+    if (d.sample_source) ll = resample_all_sources(d, k, key, step, sh.red);      // :859-862 (on accept only)
+    else ll += dll;
+    return true;
+}
+
+// ---- K7c: Gibbs operators on the count tables ----------------------------------------------------
+// complete-data log-likelihood terms that depend on the weights of feature f:
+//   sum_{cfg,c} cnt_src[f][cfg][c] * log w~[f][cfg][c]        (cells with count 0 contribute nothing)
+__device__ __forceinline__ double weight_ll_row(const int* cs_row, const double* wn_row) {
+    double t = 0.0;
+#pragma unroll
+    for (int i = 0; i < 12; ++i)
+        if (cs_row[i] > 0) t += (double)cs_row[i] * log(wn_row[i]);
+    return t;
+}
+
+// gibbs_sample_weights (zone_sampling.py:222-331).  Always accepted (incl. quirk Q2: with inheritance the
+// per-feature MH decision is overwritten by `sample_new.weights = w_new`, :325-327).
+__device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, uint64_t step, double& ll,
+                                 StepShared& sh) {
+    // fixed = choice(['inheritance', 'contact'])  (:249)
+    const bool fixed_inheritance = rng_uniform(key, step, RP_FIXED, 0) < 0.5;
+    double dll = 0.0;
+    for (int f = threadIdx.x; f < d.F; f += blockDim.x) {
+        const int* cs = k.cs + (size_t)f * 12;
+        double* w = k.w + (size_t)f * 3;
+        double* wn = k.wn + (size_t)f * 12;
+        const double old_term = weight_ll_row(cs, wn);
+        if (d.C == 2) {
+            // counts over sites with a zone (:239-243): cfg = 1
+            const double g0 = rng_gamma(key, step, RP_BETA_A, f, 1.0 + (double)cs[3 + 0]);
+            const double g1 = rng_gamma(key, step, RP_BETA_B, f, 1.0 + (double)cs[3 + 1]);
+            const double s = g0 + g1;
+            w[0] = g0 / s; w[1] = g1 / s;
+        } else {
+            // counts over has_zone sites (cfg 1,3) or has_family sites (cfg 2,3)   (:256-259, 283-286)
+            const int a = fixed_inheritance ? 1 : 2;       // cfg of the "only this component" sites; also the column x
+            const int c_univ = cs[a * 3 + 0] + cs[9 + 0];
+            const int c_x = cs[a * 3 + a] + cs[9 + a];
+            const double gx = rng_gamma(key, step, RP_BETA_A, f, 1.0 + (double)c_x);
+            const double gu = rng_gamma(key, step, RP_BETA_B, f, 1.0 + (double)c_univ);
+            const double ax = gx / (gx + gu);              // ~ Beta(1 + c_x, 1 + c_univ)      (:262-265, 289-292)
+            const double w0 = w[0];
+            double v[3] = {w0, w[1], w[2]};
+            v[a] = ax * w0 / (1.0 - ax);                    // :270, 297
+            const double s = (v[0] + v[1]) + v[2];          // normalize(w_new) :271, 298
+            w[0] = v[0] / s; w[1] = v[1] / s; w[2] = v[2] / s;
+        }
+        wnorm_row(w, wn, d.C);
+        dll += weight_ll_row(cs, wn) - old_term;
+    }
+    ll += block_sum(dll, sh.red);
+}
+
+// Shared body of gibbs_sample_p_global / p_zones / p_families (zone_sampling.py:334-406):
+// p[f][applicable] ~ Dirichlet(prior_counts[f] + cnt[f]) for the selected features.
+//   p, cnt: tables of the row being resampled ([F][S]);  pc: prior pseudo-counts [F][S] or null (= 1)
+//   use_subset: features chosen with probability sp.frac (:335,385), else all (:370)
+//   alpha/lnorm/pcache: Dirichlet prior density tables for the prior delta (null if that prior is uniform)
+__device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Chain& k, RngKey key, uint64_t step,
+                                double* p, const int* cnt, const double* pc, bool use_subset,
+                                const double* alpha, const double* lnorm, double* pcache,
+                                double& ll, double& prior, StepShared& sh) {
+    const int S = d.S, FS = d.F * d.S;
+    // phase 1: Gamma draws (one thread per (feature, state))
+    for (int i = threadIdx.x; i < FS; i += blockDim.x) {
+        const int f = i / S, s = i - f * S;
+        double g = -1.0;      // -1 = feature not selected
+        if (!use_subset || rng_uniform(key, step, RP_SUBSET, f) < sp.frac) {
+            g = 0.0;
+            if (d.app_mask[f] >> s & 1u)
+                g = rng_gamma(key, step, RP_GAMMA, i, (pc ? pc[i] : 1.0) + (double)cnt[i]);
+        }
+        k.scratch[i] = g;
+    }
+    __syncthreads();
+    // phase 2: normalise, write, accumulate the likelihood / prior deltas (one thread per feature)
+    double dll = 0.0, dpr = 0.0;
+    for (int f = threadIdx.x; f < d.F; f += blockDim.x) {
+        const double* g = k.scratch + (size_t)f * S;
+        if (g[0] < 0.0) continue;
+        double tot = 0.0;
+        for (int s = 0; s < S; ++s) tot += g[s];
+        double t = 0.0;
+        for (int s = 0; s < S; ++s) {
+            if (!(d.app_mask[f] >> s & 1u)) continue;
+            const double pn = g[s] / tot;
+            const int c = cnt[(size_t)f * S + s];
+            if (c > 0) t += (double)c * (log(pn) - log(p[(size_t)f * S + s]));
+            p[(size_t)f * S + s] = pn;
+        }
+        dll += t;
+        if (alpha) {
+            const double v = dirichlet_row(p + (size_t)f * S, alpha + (size_t)f * S, lnorm[f], d.app_mask[f], S);
+            dpr += v - pcache[f];
+            pcache[f] = v;
+        }
+    }
+    ll += block_sum(dll, sh.red);
+    if (alpha) prior += block_sum(dpr, sh.red);
+}
+
+// ---- K7d: alter_* operators (source-free mode), zone_sampling.py:408-612 --------------------------
+// log pdf of a 2-component Dirichlet
+__device__ __forceinline__ double dir2_logpdf(double x0, double x1, double a0, double a1) {
+    return lgamma(a0 + a1) - lgamma(a0) - lgamma(a1) + xlogy_d(a0 - 1.0, x0) + xlogy_d(a1 - 1.0, x1);
+}
+
+// dirichlet_proposal on a renormalised pair (zone_sampling.py:538-569): v' ~ Dir(1 + kappa v);
+// returns new pair (scaled back by the pair's mass) and log_q - log_q_back.
+__device__ __forceinline__ void pair_proposal(RngKey key, uint64_t step, double c0, double c1, double kappa,
+                                              double& n0, double& n1, double& log_q_ratio) {
+    const double mass = c0 + c1;
+    const double t0 = c0 / mass, t1 = c1 / mass;
+    const double a0 = 1.0 + kappa * t0, a1 = 1.0 + kappa * t1;
+    const double g0 = rng_gamma(key, step, RP_PROPOSAL, 0, a0);
+    const double g1 = rng_gamma(key, step, RP_PROPOSAL, 1, a1);
+    const double v0 = g0 / (g0 + g1), v1 = g1 / (g0 + g1);
+    const double log_q = dir2_logpdf(v0, v1, a0, a1);
+    const double log_q_back = dir2_logpdf(t0, t1, 1.0 + kappa * v0, 1.0 + kappa * v1);
+    n0 = v0 * mass; n1 = v1 * mass;
+    log_q_ratio = log_q - log_q_back;
+}
+
+// ordered pair of distinct indices out of n (== random.sample(list, 2))
+__device__ __forceinline__ void pick_pair(RngKey key, uint64_t step, int n, int& a, int& b) {
+    a = rng_int(key, step, RP_PAIR, 0, n);
+    b = rng_int(key, step, RP_PAIR, 1, n - 1);
+    if (b >= a) ++b;
+}
+// index of the j-th applicable state of a feature
+__device__ __forceinline__ int nth_state(uint32_t mask, int j) {
+    for (int i = 0; i < j; ++i) mask &= mask - 1;
+    return __ffs(mask) - 1;
+}
+
+// Column delta of feature f: sum over the given sites of log mix_new - log mix_old, where "new" replaces either the
+// weight row (wrow_new) or one probability row (which = 0 global / 1 zone z / 2 family fam; states s0,s1 -> v0,v1).
+__device__ double column_delta(const DevData& d, const Chain& k, int f, const int* sites, int n_sites,
+                               const double* wrow_new, int which, int tab, int s0, int s1, double v0, double v1,
+                               double* red) {
+    const double* wrow = k.wn + (size_t)f * 12;
+    const size_t FS = (size_t)d.F * d.S;
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < n_sites; i += blockDim.x) {
+        const int n = sites ? sites[i] : i;
+        const int xs = sites ? d.x[(size_t)n * d.ldx + f] : d.xT[(size_t)f * d.ldn + n];
+        if (xs == SB_NA) continue;
+        if (which >= 0 && xs != s0 && xs != s1) continue;      // cell does not see the changed entries
+        const int zid = k.zone_id[n];
+        const int fam = d.inheritance ? d.fam_id[n] : -1;
+        const double old = cell_mix(d, k, f, xs, zid, fam, wrow);
+        double nw;
+        if (which < 0) {
+            nw = cell_mix(d, k, f, xs, zid, fam, wrow_new);
+        } else {
+            const int cfg = (zid >= 0 ? 1 : 0) + (fam >= 0 ? 2 : 0);
+            const double* w = wrow + cfg * 3;
+            const size_t o = (size_t)f * d.S + xs;
+            const double pv = xs == s0 ? v0 : v1;
+            double g = k.pg[o], zt = zid >= 0 ? k.pz[(size_t)zid * FS + o] : 0.0, ft = fam >= 0 ? k.pf[(size_t)fam * FS + o] : 0.0;
+            if (which == 0) g = pv;
+            else if (which == 1) { if (zid == tab) zt = pv; }
+            else if (fam == tab) ft = pv;
+            nw = w[0] * g;
+            if (zid >= 0) nw += w[1] * zt;
+            if (fam >= 0) nw += w[2] * ft;
+        }
+        acc += log(nw) - log(old);
+    }
+    return block_sum(acc, red);
+}
+
+// alter_weights / alter_p_global / alter_p_zones / alter_p_families (zone_sampling.py:408-612). Returns accepted.
+__device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k, int op, RngKey key, uint64_t step,
+                         double& ll, double& prior, StepShared& sh) {
+    const int f = rng_int(key, step, RP_FEATURE, 0, d.F);            // np.random.choice(range(n_features))
+    double lqr, n0, n1, dll, dprior = 0.0;
+    if (op == SB_OP_ALTER_WEIGHTS) {
+        int a = 0, b = 1;
+        if (d.C == 3) pick_pair(key, step, 3, a, b);                  // _random.sample([0,1,2], 2)  :423
+        double* w = k.w + (size_t)f * 3;
+        pair_proposal(key, step, w[a], w[b], sp.prec_w, n0, n1, lqr);
+        __shared__ double wrow_new[12];
+        if (threadIdx.x == 0) {
+            double v[3] = {w[0], w[1], w[2]};
+            v[a] = n0; v[b] = n1;
+            wnorm_row(v, wrow_new, d.C);
+        }
+        __syncthreads();
+        dll = column_delta(d, k, f, nullptr, d.N, wrow_new, -1, 0, 0, 0, 0.0, 0.0, sh.red);
+        const bool accept = log(rng_uniform(key, step, RP_ACCEPT, 0)) < dll - lqr;
+        if (accept) {
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                w[a] = n0; w[b] = n1;
+                for (int i = 0; i < 12; ++i) k.wn[(size_t)f * 12 + i] = wrow_new[i];
+            }
+            __syncthreads();
+            ll += dll;
+        }
+        return accept;
+    }
+    const uint32_t mask = d.app_mask[f];
+    const int napp = d.n_app[f];
+    if (napp < 2) return false;       // the reference's random.sample(list, 2) raises here; we reject the step
+    int ia, ib;
+    pick_pair(key, step, napp, ia, ib);                               // _random.sample(list(f_states), 2)
+    const int s0 = nth_state(mask, ia), s1 = nth_state(mask, ib);
+    double* row;
+    int which, tab = 0;
+    const int* sites = nullptr;
+    int n_sites = d.N;
+    double kappa;
+    const double* alpha = nullptr; const double* lnorm = nullptr; double* pcache = nullptr;
+    if (op == SB_OP_ALTER_P_GLOBAL) {
+        which = 0; row = k.pg + (size_t)f * d.S; kappa = sp.prec_g;
+        if (d.pg_type == 1) { alpha = d.alpha_g + (size_t)f * d.S; lnorm = d.lnorm_g + f; pcache = k.ppg + f; }
+    } else if (op == SB_OP_ALTER_P_ZONES) {
+        which = 1; tab = rng_int(key, step, RP_ZONE, 0, d.Z); kappa = sp.prec_z;
+        row = k.pz + ((size_t)tab * d.F + f) * d.S;
+        sites = k.members + (size_t)tab * d.N; n_sites = k.zsize[tab];
+    } else {
+        which = 2; tab = rng_int(key, step, RP_FAMILY, 0, d.Fam); kappa = sp.prec_f;
+        row = k.pf + ((size_t)tab * d.F + f) * d.S;
+        sites = d.fam_sites + d.fam_ptr[tab]; n_sites = d.fam_ptr[tab + 1] - d.fam_ptr[tab];
+        if (d.pf_type == 1) {
+            alpha = d.alpha_f + ((size_t)tab * d.F + f) * d.S; lnorm = d.lnorm_f + (size_t)tab * d.F + f;
+            pcache = k.ppf + (size_t)tab * d.F + f;
+        }
+    }
+    pair_proposal(key, step, row[s0], row[s1], kappa, n0, n1, lqr);
+    dll = column_delta(d, k, f, sites, n_sites, nullptr, which, tab, s0, s1, n0, n1, sh.red);
+    double new_prior_term = 0.0;
+    if (alpha) {
+        // Dirichlet prior of the changed row with the two entries replaced
+        double t = *lnorm;
+        for (int s = 0; s < d.S; ++s)
+            if (mask >> s & 1u) t += xlogy_d(alpha[s] - 1.0, s == s0 ? n0 : (s == s1 ? n1 : row[s]));
+        new_prior_term = t;
+        dprior = t - *pcache;
+    }
+    const bool accept = log(rng_uniform(key, step, RP_ACCEPT, 0)) < dll - lqr + dprior;
+    if (accept) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            row[s0] = n0; row[s1] = n1;
+            if (alpha) *pcache = new_prior_term;
+        }
+        __syncthreads();
+        ll += dll;
+        prior += dprior;
+    }
+    return accept;
+}
+
+// ---- K8: the persistent kernel ---------------------------------------------------------------------
+__global__ void __launch_bounds__(STEP_THREADS)
+mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
+    extern __shared__ unsigned char step_smem[];
+    __shared__ StepShared sh;
+    const int chain = blockIdx.x;
+    unsigned* nbr = reinterpret_cast<unsigned*>(step_smem);
+    unsigned* freeb = nbr + sp.nwords;
+    double* prim_key = reinterpret_cast<double*>(freeb + sp.nwords + (sp.nwords & 1));
+    unsigned char* prim_tree = reinterpret_cast<unsigned char*>(prim_key + sp.prim_cap);
+
+    const Chain k = chain_view(st, sp, chain);
+    const unsigned gchain = (unsigned)(sp.chain_offset + chain);
+    const RngKey key = {sp.seed_lo ^ (gchain * 0x9E3779B9u), sp.seed_hi ^ gchain};
+    double ll = st.ll[chain], prior = st.prior[chain], geo = st.geo[chain];
+    const uint64_t step0 = st.step[chain];
+    unsigned long long acc[SB_N_OPS], rej[SB_N_OPS];
+#pragma unroll
+    for (int i = 0; i < SB_N_OPS; ++i) { acc[i] = 0ull; rej[i] = 0ull; }
+
+    for (long long it = 0; it < n_steps; ++it) {
+        const uint64_t step = step0 + (uint64_t)it;
+        // operator choice: np.random.choice(fn_operators, p=p_operators)  (mcmc_generative.py:294)
+        const double uo = rng_uniform(key, step, RP_OP, 0);
+        int oi = 0;
+        while (oi < sp.n_ops - 1 && uo >= sp.op_cdf[oi]) ++oi;
+        const int op = sp.op_ids[oi];
+        bool accepted = true;
+        switch (op) {
+            case SB_OP_SHRINK_ZONE: case SB_OP_GROW_ZONE: case SB_OP_SWAP_ZONE:
+                accepted = op_zone_move(d, sp, k, op, chain, key, step, ll, prior, geo, nbr, freeb, prim_key,
+                                        prim_tree, sh);
+                break;
+            case SB_OP_GIBBS_SOURCES:
+                ll = resample_all_sources(d, k, key, step, sh.red);
+                break;
+            case SB_OP_GIBBS_WEIGHTS:
+                op_gibbs_weights(d, k, key, step, ll, sh);
+                break;
+            case SB_OP_GIBBS_P_GLOBAL:
+                gibbs_table_row(d, sp, k, key, step, k.pg, k.cg, d.gibbs_g, true,
+                                d.pg_type == 1 ? d.alpha_g : nullptr, d.lnorm_g, k.ppg, ll, prior, sh);
+                break;
+            case SB_OP_GIBBS_P_ZONES: {
+                const size_t o = (size_t)rng_int(key, step, RP_ZONE, 0, d.Z) * d.F * d.S;
+                gibbs_table_row(d, sp, k, key, step, k.pz + o, k.cz + o, nullptr, false, nullptr, nullptr, nullptr,
+                                ll, prior, sh);
+                break;
+            }
+            case SB_OP_GIBBS_P_FAMILIES: {
+                const int fam = rng_int(key, step, RP_FAMILY, 0, d.Fam);
+                const size_t o = (size_t)fam * d.F * d.S;
+                gibbs_table_row(d, sp, k, key, step, k.pf + o, k.cf + o, d.gibbs_f + o, true,
+                                d.pf_type == 1 ? d.alpha_f + o : nullptr, d.lnorm_f + (size_t)fam * d.F,
+                                k.ppf + (size_t)fam * d.F, ll, prior, sh);
+                break;
+            }
+            default:
+                accepted = op_alter(d, sp, k, op, key, step, ll, prior, sh);
+                break;
+        }
+        if (accepted) ++acc[op]; else ++rej[op];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        st.ll[chain] = ll; st.prior[chain] = prior; st.geo[chain] = geo;
+        st.step[chain] = step0 + (uint64_t)n_steps;
+        for (int i = 0; i < SB_N_OPS; ++i) {
+            st.acc[(size_t)chain * SB_N_OPS + i] += acc[i];
+            st.rej[(size_t)chain * SB_N_OPS + i] += rej[i];
+        }
+    }
+}
+
+// ---- forced zone move: (log_q, log_q_back) without touching the state (parity of :704-933) --------
+__global__ void __launch_bounds__(STEP_THREADS)
+move_log_q_kernel(DevData d, ChainArrays st, StepParams sp, int chain, int kind, int z, int site_new,
+                  int site_removed, double rho, double* out) {
+    extern __shared__ unsigned char step_smem[];
+    __shared__ StepShared sh;
+    unsigned* nbr = reinterpret_cast<unsigned*>(step_smem);
+    const Chain k = chain_view(st, sp, chain);
+    const int size = k.zsize[z];
+    const int* mem = k.members + (size_t)z * d.N;
+    int n_occ = 0;
+    for (int i = 0; i < d.Z; ++i) n_occ += k.zsize[i];
+    const int n_free = d.N - n_occ;
+    double q, q_back;
+    if (kind != SB_OP_SHRINK_ZONE) {
+        build_nbr_bits(d, k.zone_id, mem, size, -1, nbr, sp.nwords);
+        const int n_nbr = bits_count(nbr, sp.nwords, sh.redi);
+        q = grow_q(bit_test(nbr, site_new), n_free, n_nbr, rho);
+        q_back = kind == SB_OP_GROW_ZONE ? 1.0 / (double)(size + 1) : grow_q(false, n_free, n_nbr, rho);
+    } else {
+        q = 1.0 / (double)size;
+        build_nbr_bits(d, k.zone_id, mem, size, site_removed, nbr, sp.nwords);
+        const int n_nbr = bits_count(nbr, sp.nwords, sh.redi);
+        q_back = grow_q(bit_test(nbr, site_removed), n_free + 1, n_nbr, rho);
+        if (d.warmup) q_back = 1.0 / (double)(size + 1);
+    }
+    if (threadIdx.x == 0) { out[0] = log(q); out[1] = log(q_back); }
+}

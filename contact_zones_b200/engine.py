@@ -1,0 +1,240 @@
+"""`Engine`: one C-ABI context (one GPU, a shard of chains) with numpy-friendly methods.
+
+This is the only module that talks to libsbayes_b200.so; the reference-shaped objects in `model.py` and
+`sampling/` are thin layers over it.  Array conventions at this level are the reference's `Sample` ones
+(`zone_sampling.py:49-75`): zones bool (Z,N), weights (F,C), p_global (1,F,S), p_zones (Z,F,S),
+p_families (Fam,F,S), source bool (N,F,C) one-hot (or the packed uint8 (N,F) form used on the device).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import SbDims, SbOperatorCfg, SbPriorCfg, SbError, as_c, ptr
+
+
+def state_index(features):
+    """One-hot bool (N,F,S) -> uint8 (N,F) state index, 255 = NA (all-zero one-hot, `model.py:112`)."""
+    features = np.asarray(features)
+    if features.ndim == 2:
+        return np.ascontiguousarray(features, dtype=np.uint8)
+    idx = np.argmax(features, axis=-1).astype(np.uint8)
+    idx[features.sum(axis=-1) == 0] = 255
+    return idx
+
+
+def family_index(families, n_sites):
+    """bool (Fam,N) -> int16 (N) family id, -1 = none.  A site in two families is rejected (the reference lets
+    the later family overwrite, `model.py:427-431`)."""
+    fid = np.full(n_sites, -1, dtype=np.int16)
+    if families is None:
+        return fid
+    fam = np.asarray(families, dtype=bool)
+    if fam.size and fam.sum(axis=0).max() > 1:
+        raise ValueError('a site belongs to more than one family')
+    for k in range(fam.shape[0]):
+        fid[fam[k]] = k
+    return fid
+
+
+def pack_source(source, n_components):
+    if source is None:
+        return None
+    source = np.asarray(source)
+    if source.ndim == 3:
+        return np.argmax(source, axis=-1).astype(np.uint8)
+    return np.ascontiguousarray(source, dtype=np.uint8)
+
+
+class Engine:
+    def __init__(self, features, states, families=None, adj_mat=None, cost_matrix=None, *, n_zones, n_chains=1,
+                 inheritance=False, sample_source=False, warmup=False, device=0, chain_offset=0):
+        self.lib = _lib.load()
+        self._ctx = C.c_void_p()
+        x = state_index(features)
+        self.N, self.F = x.shape
+        states = np.asarray(states, dtype=bool)
+        self.S = states.shape[1]
+        self.Z = int(n_zones)
+        self.inheritance = bool(inheritance)
+        self.sample_source = bool(sample_source)
+        self.warmup = bool(warmup)
+        self.Fam = int(np.asarray(families).shape[0]) if (inheritance and families is not None) else 0
+        self.C = 3 if inheritance else 2
+        self.n_chains = int(n_chains)
+        self.chain_offset = int(chain_offset)
+        flags = ((_lib.SB_F_INHERITANCE if inheritance else 0) | (_lib.SB_F_SAMPLE_SOURCE if sample_source else 0) |
+                 (_lib.SB_F_WARMUP if warmup else 0))
+        dims = SbDims(self.N, self.F, self.S, self.Z, self.Fam, self.n_chains, self.chain_offset, flags)
+        rc = self.lib.sb_create(C.byref(self._ctx), int(device), C.byref(dims))
+        if rc != 0:
+            msg = self.lib.sb_last_error(self._ctx).decode() if self._ctx else 'sb_create failed (no CUDA device?)'
+            if self._ctx:
+                self.lib.sb_destroy(self._ctx)
+                self._ctx = C.c_void_p()
+            raise SbError(rc, msg)
+        fid = family_index(families, self.N) if inheritance else None
+        indptr = indices = None
+        if adj_mat is not None:
+            if isinstance(adj_mat, tuple):
+                indptr, indices = adj_mat
+            else:
+                csr = adj_mat.tocsr()
+                csr.sort_indices()
+                indptr, indices = csr.indptr, csr.indices
+            indptr, indices = as_c(indptr, np.int32), as_c(indices, np.int32)
+        cost = as_c(cost_matrix, np.float64)
+        xs, st = as_c(x, np.uint8), as_c(states, np.uint8)
+        self._check(self.lib.sb_upload_data(self._ctx, ptr(xs), ptr(st), ptr(fid), ptr(indptr), ptr(indices), ptr(cost)))
+        self.has_cost = cost is not None
+        self.set_priors()
+
+    # -- plumbing ---------------------------------------------------------------------------------
+    def _check(self, rc):
+        if rc != 0:
+            raise SbError(rc, self.lib.sb_last_error(self._ctx).decode())
+
+    def close(self):
+        if getattr(self, '_ctx', None):
+            self.lib.sb_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_stream(self, cuda_stream):
+        self._check(self.lib.sb_set_stream(self._ctx, C.c_void_p(cuda_stream or 0)))
+
+    def sync(self):
+        self._check(self.lib.sb_sync(self._ctx))
+
+    @property
+    def kernel_launches(self):
+        v = C.c_int64()
+        self._check(self.lib.sb_kernel_launches(self._ctx, C.byref(v)))
+        return v.value
+
+    # -- priors -----------------------------------------------------------------------------------
+    def set_priors(self, size_type='none', geo_type='uniform', geo_scale=1.0, p_global_type='uniform',
+                   p_families_type='uniform', gibbs_counts_global=None, alpha_global=None,
+                   gibbs_counts_fam=None, alpha_fam=None):
+        cfg = SbPriorCfg(_lib.SIZE_TYPES[size_type], _lib.GEO_TYPES[geo_type], float(geo_scale),
+                         _lib.DIR_TYPES[p_global_type], _lib.DIR_TYPES[p_families_type])
+        a = [as_c(v, np.float64) for v in (gibbs_counts_global, alpha_global, gibbs_counts_fam, alpha_fam)]
+        self._check(self.lib.sb_set_priors(self._ctx, C.byref(cfg), *[ptr(v) for v in a]))
+
+    # -- state ------------------------------------------------------------------------------------
+    def set_state(self, chain, zones, weights, p_global, p_zones, p_families=None, source=None):
+        zones = as_c(np.asarray(zones).reshape(self.Z, self.N), np.uint8)
+        w = as_c(np.asarray(weights).reshape(self.F, self.C), np.float64)
+        pg = as_c(np.asarray(p_global).reshape(self.F, self.S), np.float64)
+        pz = as_c(np.asarray(p_zones).reshape(self.Z, self.F, self.S), np.float64)
+        pf = as_c(np.asarray(p_families).reshape(self.Fam, self.F, self.S), np.float64) if self.inheritance else None
+        src = pack_source(source, self.C) if self.sample_source else None
+        if self.sample_source and src is None:
+            raise ValueError('a SAMPLE_SOURCE engine needs a source array')
+        self._check(self.lib.sb_set_state(self._ctx, int(chain), ptr(zones), ptr(w), ptr(pg), ptr(pz), ptr(pf), ptr(src)))
+
+    def get_state(self, chain, one_hot_source=True):
+        zones = np.zeros((self.Z, self.N), np.uint8)
+        w = np.zeros((self.F, self.C))
+        pg = np.zeros((1, self.F, self.S))
+        pz = np.zeros((self.Z, self.F, self.S))
+        pf = np.zeros((self.Fam, self.F, self.S)) if self.inheritance else None
+        src = np.zeros((self.N, self.F), np.uint8) if self.sample_source else None
+        self._check(self.lib.sb_get_state(self._ctx, int(chain), ptr(zones), ptr(w), ptr(pg), ptr(pz), ptr(pf), ptr(src)))
+        if src is not None and one_hot_source:
+            src = np.eye(self.C, dtype=bool)[src]
+        return {'zones': zones.astype(bool), 'weights': w, 'p_global': pg, 'p_zones': pz, 'p_families': pf,
+                'source': src}
+
+    def copy_state(self, dst, src):
+        self._check(self.lib.sb_copy_state(self._ctx, int(dst), int(src)))
+
+    # -- evaluation -------------------------------------------------------------------------------
+    def eval(self, chain_begin=0, n_chains=None, use_source=None):
+        n = self.n_chains - chain_begin if n_chains is None else int(n_chains)
+        use_source = self.sample_source if use_source is None else bool(use_source)
+        ll, pr, geo = np.zeros(n), np.zeros(n), np.zeros(n)
+        self._check(self.lib.sb_eval(self._ctx, int(chain_begin), n, int(use_source), ptr(ll), ptr(pr), ptr(geo)))
+        return ll, pr, geo
+
+    def eval_likelihood_async(self, chain_begin=0, n_chains=None, use_source=False):
+        n = self.n_chains - chain_begin if n_chains is None else int(n_chains)
+        self._check(self.lib.sb_eval_likelihood_async(self._ctx, int(chain_begin), n, int(bool(use_source))))
+
+    def read_ll(self, chain_begin=0, n_chains=None):
+        n = self.n_chains - chain_begin if n_chains is None else int(n_chains)
+        ll = np.zeros(n)
+        self._check(self.lib.sb_read_ll(self._ctx, int(chain_begin), n, ptr(ll)))
+        return ll
+
+    def components(self, chain):
+        lh = np.zeros((self.N, self.F, self.C))
+        wn = np.zeros((self.N, self.F, self.C))
+        self._check(self.lib.sb_eval_components(self._ctx, int(chain), ptr(lh), ptr(wn)))
+        return lh, wn
+
+    def source_posterior(self, chain):
+        post = np.zeros((self.N, self.F, self.C))
+        self._check(self.lib.sb_source_posterior(self._ctx, int(chain), ptr(post)))
+        return post
+
+    def counts(self, chain, recount=False):
+        cg = np.zeros((self.F, self.S), np.int32)
+        cz = np.zeros((self.Z, self.F, self.S), np.int32)
+        cf = np.zeros((self.Fam, self.F, self.S), np.int32) if self.inheritance else None
+        csz = np.zeros((self.F, self.C), np.int32)
+        csf = np.zeros((self.F, self.C), np.int32)
+        self._check(self.lib.sb_counts(self._ctx, int(chain), int(recount), ptr(cg), ptr(cz), ptr(cf), ptr(csz), ptr(csf)))
+        return {'cnt_glob': cg, 'cnt_zone': cz, 'cnt_fam': cf, 'cnt_src_zone': csz, 'cnt_src_fam': csf}
+
+    def move_log_q(self, chain, kind, zone, site_new=-1, site_removed=-1, p_grow_connected=0.85):
+        lq, lqb = C.c_double(), C.c_double()
+        self._check(self.lib.sb_move_log_q(self._ctx, int(chain), _lib.OP_IDS[kind + '_zone'], int(zone), int(site_new),
+                                           int(site_removed), float(p_grow_connected), C.byref(lq), C.byref(lqb)))
+        return lq.value, lqb.value
+
+    # -- sampler ----------------------------------------------------------------------------------
+    def set_operators(self, operators, precision, min_size, max_size, p_grow_connected, seed=0,
+                      gibbs_feature_fraction=0.4):
+        """operators: {name: weight} as built by `MCMC.steps_per_operator` (`mcmc_setup.py:70-95`);
+        precision: {'weights','universal','contact','inheritance'} (`PROPOSAL_PRECISION`);
+        max_size / p_grow_connected: scalar or per-chain sequence."""
+        cfg = SbOperatorCfg()
+        items = [(k, float(v)) for k, v in operators.items() if k in _lib.OP_IDS]
+        unknown = [k for k, v in operators.items() if k not in _lib.OP_IDS and float(v) > 0]
+        if unknown:
+            raise ValueError(f'operators not implemented on the device: {unknown}')
+        cfg.n_ops = len(items)
+        for i, (k, v) in enumerate(items):
+            cfg.op_ids[i] = _lib.OP_IDS[k]
+            cfg.op_prob[i] = v
+        cfg.precision_weights = float(precision.get('weights', 15))
+        cfg.precision_p_global = float(precision.get('universal', 40))
+        cfg.precision_p_zones = float(precision.get('contact', 20))
+        cfg.precision_p_families = float(precision.get('inheritance') or 20)
+        cfg.min_size = int(min_size)
+        cfg.gibbs_feature_fraction = float(gibbs_feature_fraction)
+        cfg.seed = int(seed) & (2 ** 64 - 1)
+        pg = np.ascontiguousarray(np.broadcast_to(np.asarray(p_grow_connected, dtype=np.float64), (self.n_chains,)))
+        ms = np.ascontiguousarray(np.broadcast_to(np.asarray(max_size, dtype=np.int32), (self.n_chains,)))
+        self._check(self.lib.sb_set_operators(self._ctx, C.byref(cfg), ptr(pg), ptr(ms)))
+        self.op_names = [k for k, _ in items]
+
+    def run(self, n_steps):
+        self._check(self.lib.sb_run(self._ctx, int(n_steps)))
+
+    def chain_scalars(self):
+        ll, pr = np.zeros(self.n_chains), np.zeros(self.n_chains)
+        self._check(self.lib.sb_read_chain_scalars(self._ctx, ptr(ll), ptr(pr)))
+        return ll, pr
+
+    def op_stats(self):
+        acc = np.zeros((self.n_chains, _lib.SB_N_OPS), np.int64)
+        rej = np.zeros((self.n_chains, _lib.SB_N_OPS), np.int64)
+        self._check(self.lib.sb_read_op_stats(self._ctx, ptr(acc), ptr(rej)))
+        return acc, rej

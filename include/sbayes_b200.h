@@ -1,0 +1,170 @@
+/*
+ * sbayes_b200.h -- C ABI of the B200-native sBayes MCMC inner loop (libsbayes_b200.so).
+ *
+ * The reference (derpetermann/contact_zones) is pure Python and has no FFI of its own; the boundary it
+ * offers for this path is its Python object API.  Each entry point below names the reference interface
+ * whose arithmetic it replaces (paths relative to the reference root).  The Python mirror of that object
+ * API (contact_zones_b200/{model,sampling,...}.py) binds these symbols through ctypes -- see
+ * INTEGRATION.md for the stub a reference maintainer would add.
+ *
+ * Conventions
+ *  - every function returns 0 on success, a negative SB_E_* code on failure, never throws;
+ *    sb_last_error(ctx) returns a message owned by the context (valid until the next call on it);
+ *  - all pointer arguments are HOST pointers borrowed for the duration of the call; device memory is
+ *    owned by the context and released by sb_destroy;
+ *  - one context per (process, GPU); calls on one context are serialised by the caller and are
+ *    stream-ordered on the context's CUDA stream (sb_set_stream); contexts are independent;
+ *  - arrays are C-contiguous, layouts as in the reference: zones (Z,N) u8 0/1, weights (F,C) f64,
+ *    p_global (F,S), p_zones (Z,F,S), p_families (Fam,F,S) f64, x / source (N,F) u8.
+ *    x[n,f] = state index, 255 = NA (all-zero one-hot, model.py:112); source[n,f] in {0,1,2} =
+ *    [universal, contact, inheritance] (model.py:243-245).
+ */
+#ifndef SBAYES_B200_H
+#define SBAYES_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sb_ctx sb_ctx;
+
+enum {
+    SB_OK = 0,
+    SB_E_ARG = -1,        /* invalid argument / shape                      */
+    SB_E_CUDA = -2,       /* CUDA runtime error (message in sb_last_error) */
+    SB_E_STATE = -3,      /* call order (data / state / operators not set) */
+    SB_E_OVERLAP = -4,    /* sb_set_state: overlapping zones (quirk Q7)    */
+    SB_E_NOGPU = -5       /* no CUDA device                                */
+};
+
+/* sb_create flags */
+enum {
+    SB_F_INHERITANCE = 1u << 0,    /* model.py:45  config['INHERITANCE']   -> C = 3 */
+    SB_F_SAMPLE_SOURCE = 1u << 1,  /* model.py:46  config['SAMPLE_SOURCE'] -> per-cell source state */
+    SB_F_WARMUP = 1u << 2          /* ZoneMCMCWarmup semantics (zone_sampling.py:1272-1577) */
+};
+
+/* prior types (model.py:567-1056) */
+enum { SB_SIZE_NONE = 0, SB_SIZE_UNIFORM = 1, SB_SIZE_QUADRATIC = 2 };      /* ZoneSizePrior :893-976 */
+enum { SB_GEO_UNIFORM = 0, SB_GEO_COST_BASED = 1 };                          /* GeoPrior      :979-1056 */
+enum { SB_DIR_UNIFORM = 0, SB_DIR_COUNTS = 1 };                              /* PGlobalPrior :567, PFamiliesPrior :633 */
+
+/* operator ids (zone_sampling.py; table built by mcmc_setup.py:70-95) */
+enum {
+    SB_OP_SHRINK_ZONE = 0, SB_OP_GROW_ZONE = 1, SB_OP_SWAP_ZONE = 2,
+    SB_OP_GIBBS_SOURCES = 3, SB_OP_GIBBS_WEIGHTS = 4, SB_OP_GIBBS_P_GLOBAL = 5,
+    SB_OP_GIBBS_P_ZONES = 6, SB_OP_GIBBS_P_FAMILIES = 7,
+    SB_OP_ALTER_WEIGHTS = 8, SB_OP_ALTER_P_GLOBAL = 9, SB_OP_ALTER_P_ZONES = 10, SB_OP_ALTER_P_FAMILIES = 11,
+    SB_N_OPS = 12
+};
+
+typedef struct {
+    int32_t n_sites;       /* N   */
+    int32_t n_features;    /* F   */
+    int32_t n_states;      /* S   (max states per feature, <= 32) */
+    int32_t n_zones;       /* Z   */
+    int32_t n_families;    /* Fam (0 without inheritance) */
+    int32_t n_chains;      /* chains resident in this context (this rank's shard) */
+    int32_t chain_offset;  /* global id of local chain 0: RNG streams are keyed by the GLOBAL chain id, so
+                              trajectories do not depend on how chains are sharded over GPUs */
+    uint32_t flags;        /* SB_F_* */
+} sb_dims;
+
+typedef struct {
+    int32_t size_type;       /* SB_SIZE_*  */
+    int32_t geo_type;        /* SB_GEO_*   */
+    double geo_scale;        /* GeoPrior.scale, model.py:1010 */
+    int32_t p_global_type;   /* SB_DIR_*   */
+    int32_t p_families_type; /* SB_DIR_*   */
+} sb_prior_cfg;
+
+typedef struct {
+    int32_t n_ops;                   /* <= SB_N_OPS */
+    int32_t op_ids[SB_N_OPS];        /* SB_OP_*                                              */
+    double op_prob[SB_N_OPS];        /* selection probabilities (mcmc_generative.py:294)     */
+    double precision_weights;        /* PROPOSAL_PRECISION (zone_sampling.py:165-169)        */
+    double precision_p_global;
+    double precision_p_zones;
+    double precision_p_families;
+    int32_t min_size;                /* MIN_M  (model.py:43)                                 */
+    double gibbs_feature_fraction;   /* 0.4: zone_sampling.py:334,381                        */
+    uint64_t seed;
+} sb_operator_cfg;
+
+/* ---- lifetime -------------------------------------------------------------------------------- */
+int sb_version(void);
+int sb_device_count(void);
+int sb_create(sb_ctx** out, int device, const sb_dims* dims);
+int sb_destroy(sb_ctx* ctx);
+const char* sb_last_error(const sb_ctx* ctx);
+int sb_set_stream(sb_ctx* ctx, void* cuda_stream);   /* NULL = the context's own stream */
+int sb_sync(sb_ctx* ctx);
+
+/* ---- immutable data: replaces Likelihood.__init__ (model.py:105-131), ZoneMCMC.__init__
+ *      (zone_sampling.py:127-151) and the Prior constructors (model.py:470-482) ------------------- */
+int sb_upload_data(sb_ctx* ctx,
+                   const uint8_t* x,            /* (N,F)  state index, 255 = NA                       */
+                   const uint8_t* applicable,   /* (F,S)  data.states                                  */
+                   const int16_t* family_id,    /* (N)    -1 = none; NULL without inheritance          */
+                   const int32_t* adj_indptr,   /* (N+1)  network['adj_mat'] CSR (util.py:139-155)     */
+                   const int32_t* adj_indices,  /* (nnz)                                               */
+                   const double* cost);         /* (N,N)  geo_prior['cost_matrix'] or NULL             */
+int sb_set_priors(sb_ctx* ctx, const sb_prior_cfg* cfg,
+                  const double* gibbs_counts_global,  /* (F,S)     prior_p_global.counts   (model.py:577,585)  or NULL = 1 */
+                  const double* alpha_global,         /* (F,S)     Dirichlet density alpha (util.py:589-623)   or NULL     */
+                  const double* gibbs_counts_fam,     /* (Fam,F,S) prior_p_families.counts (model.py:647,664)  or NULL = 1 */
+                  const double* alpha_fam);           /* (Fam,F,S)                                              or NULL     */
+
+/* ---- per-chain state: the device image of a `Sample` (zone_sampling.py:49-115) ------------------ */
+int sb_set_state(sb_ctx* ctx, int chain, const uint8_t* zones, const double* weights, const double* p_global,
+                 const double* p_zones, const double* p_families, const uint8_t* source /* or NULL */);
+int sb_get_state(sb_ctx* ctx, int chain, uint8_t* zones, double* weights, double* p_global,
+                 double* p_zones, double* p_families, uint8_t* source /* any may be NULL */);
+int sb_copy_state(sb_ctx* ctx, int dst_chain, int src_chain);
+
+/* ---- stateless full evaluation of resident states (kernels K1, K2, K3) --------------------------
+ * ll    : Likelihood.__call__  model.py:145-184   (use_source: 0 -> :174-176, 1 -> :177-184)
+ * prior : Prior.__call__       model.py:484-505
+ * geo   : GeoPrior.__call__    model.py:1018-1043 / geo_prior_distance :1096-1139 (quirk Q1: last zone)
+ * Outputs are host arrays of n_chains doubles (any may be NULL).  Also refreshes the running ll/prior of
+ * the sampler for those chains. */
+int sb_eval(sb_ctx* ctx, int chain_begin, int n_chains, int use_source, double* ll, double* prior, double* geo);
+/* launch-only variant for timing the likelihood kernel with device-resident inputs (no D2H, no sync) */
+int sb_eval_likelihood_async(sb_ctx* ctx, int chain_begin, int n_chains, int use_source);
+int sb_read_ll(sb_ctx* ctx, int chain_begin, int n_chains, double* ll);
+
+/* debug / parity: per-cell arrays of update_component_likelihoods (:230-249) and update_weights (:257-294) */
+int sb_eval_components(sb_ctx* ctx, int chain, double* all_lh /* (N,F,C) */, double* wnorm /* (N,F,C) */);
+/* source posterior of gibbs_sample_sources (zone_sampling.py:196-202) */
+int sb_source_posterior(sb_ctx* ctx, int chain, double* post /* (N,F,C) */);
+
+/* ---- integer count tables of the Gibbs operators (kernel K4), bit-exact parity surface ----------
+ * cnt_glob (F,S)      zone_sampling.py:339-350     cnt_zone (Z,F,S)   :366-372
+ * cnt_fam  (Fam,F,S)  :389-400                     cnt_src_zone (F,C) :239-240,256-257
+ * cnt_src_fam (F,C)   :283-284
+ * recount != 0 recomputes from the resident source state; 0 returns the incrementally maintained tables. */
+int sb_counts(sb_ctx* ctx, int chain, int recount, int32_t* cnt_glob, int32_t* cnt_zone, int32_t* cnt_fam,
+              int32_t* cnt_src_zone, int32_t* cnt_src_fam);
+
+/* ---- zone-move proposal probabilities for a forced move (parity of zone_sampling.py:704-933) ----
+ * kind: SB_OP_GROW_ZONE / SB_OP_SHRINK_ZONE / SB_OP_SWAP_ZONE; unused site = -1.  Does not modify state. */
+int sb_move_log_q(sb_ctx* ctx, int chain, int kind, int zone, int site_new, int site_removed,
+                  double p_grow_connected, double* log_q, double* log_q_back);
+
+/* ---- sampler: MCMCGenerative.step / generate_samples (mcmc_generative.py:149-351) ---------------- */
+int sb_set_operators(sb_ctx* ctx, const sb_operator_cfg* cfg,
+                     const double* p_grow_connected,  /* (n_chains) zone_sampling.py:138,1288-1291 */
+                     const int32_t* max_size);        /* (n_chains) MAX_M / warm-up list :1280-1285 */
+/* Run n_steps MH steps on every resident chain in one persistent launch (kernel K8). Asynchronous. */
+int sb_run(sb_ctx* ctx, int64_t n_steps);
+int sb_read_chain_scalars(sb_ctx* ctx, double* ll, double* prior);              /* (n_chains) each */
+int sb_read_op_stats(sb_ctx* ctx, int64_t* accepted, int64_t* rejected);        /* (n_chains, SB_N_OPS) each */
+int sb_step_counter(sb_ctx* ctx, int64_t* steps_done);                          /* per context      */
+int sb_kernel_launches(sb_ctx* ctx, int64_t* launches);                         /* launches issued so far */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SBAYES_B200_H */

@@ -1,0 +1,60 @@
+"""Shared helpers of the test-suite: load a golden case and rebuild the reference-shaped arrays."""
+import os
+
+import numpy as np
+from scipy.sparse import csr_matrix
+
+import sbayes_oracle as orc
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
+
+
+def load_case(name):
+    g = dict(np.load(os.path.join(GOLDEN, name + '.npz'), allow_pickle=False))
+    n, f = g['features_idx'].shape
+    s = int(g['n_states'])
+    c = {'name': name, 'g': g, 'N': n, 'F': f, 'S': s, 'inheritance': bool(g['inheritance'])}
+    c['features'] = orc.one_hot(g['features_idx'], s)
+    c['families'] = g['families'].astype(bool)
+    c['adj'] = csr_matrix((np.ones(len(g['adj_indices']), dtype=np.int64), g['adj_indices'], g['adj_indptr']), shape=(n, n))
+    c['cost'] = g['cost'] if g['cost'].size else None
+    C = 3 if c['inheritance'] else 2
+    c['C'] = C
+    c['source'] = np.eye(C, dtype=bool)[g['source_idx']]
+    c['p_families'] = g['p_families'] if c['inheritance'] else None
+    c['Z'] = g['zones'].shape[0]
+    c['geo_type'] = str(g['geo_type'])
+    c['size_type'] = str(g['size_type'])
+    c['geo_scale'] = float(g['geo_scale'])
+    c['counts_prior'] = bool(g['counts_prior'])
+    c['prior_cfg'] = {
+        'geo': {'type': c['geo_type'], 'scale': c['geo_scale']}, 'area_size': {'type': c['size_type']},
+        'weights': {'type': 'uniform'}, 'contact': {'type': 'uniform'},
+        'universal': {'type': 'counts' if c['counts_prior'] else 'uniform'},
+        'inheritance': {'type': 'counts' if c['counts_prior'] else 'uniform'}}
+    return c
+
+
+def rel_err(a, b):
+    a, b = np.asarray(a, float), np.asarray(b, float)
+    return float(np.max(np.abs(a - b) / np.maximum(1e-300, np.maximum(np.abs(a), np.abs(b)))))
+
+
+def make_engine(c, n_chains=1, sample_source=True, warmup=False, **kw):
+    from contact_zones_b200.engine import Engine
+    g = c['g']
+    eng = Engine(g['features_idx'], g['states'], c['families'] if c['inheritance'] else None, c['adj'], c['cost'],
+                 n_zones=c['Z'], n_chains=n_chains, inheritance=c['inheritance'], sample_source=sample_source,
+                 warmup=warmup, **kw)
+    eng.set_priors(size_type=c['size_type'], geo_type=c['geo_type'], geo_scale=c['geo_scale'],
+                   p_global_type='counts' if c['counts_prior'] else 'uniform',
+                   p_families_type='counts' if (c['counts_prior'] and c['inheritance']) else 'uniform',
+                   gibbs_counts_global=g.get('gibbs_counts_global'), alpha_global=g.get('alpha_global'),
+                   gibbs_counts_fam=g.get('gibbs_counts_fam'), alpha_fam=g.get('alpha_fam'))
+    return eng
+
+
+def set_golden_state(eng, c, chain=0, with_source=True):
+    g = c['g']
+    eng.set_state(chain, g['zones'], g['weights'], g['p_global'], g['p_zones'], c['p_families'],
+                  g['source_idx'] if with_source else None)

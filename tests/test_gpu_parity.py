@@ -1,0 +1,171 @@
+"""GPU: the CUDA path (through the C ABI) against the golden vectors from the reference and against the
+oracle on the same seeded inputs.
+
+Bars (BASELINE.json north_star): log-likelihood / log-prior / geo-prior within 1e-9 relative (fp64), the
+integer count tables bit-exact, per-cell arrays 1e-12 absolute."""
+import numpy as np
+import pytest
+
+import sbayes_oracle as orc
+from conftest import golden_cases
+from helpers import load_case, make_engine, rel_err, set_golden_state
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-9
+
+
+@pytest.mark.parametrize('name', golden_cases())
+def test_eval_matches_reference(name, built_lib):
+    c = load_case(name)
+    g = c['g']
+    eng = make_engine(c, n_chains=2, sample_source=True)
+    for ch in range(2):
+        set_golden_state(eng, c, ch)
+    ll, prior, geo = eng.eval(use_source=True)
+    assert rel_err(ll, g['ref_ll_src']) < RTOL
+    assert abs(prior[0] - g['ref_prior']) <= RTOL * max(1.0, abs(g['ref_prior']))
+    assert abs(geo[1] - g['ref_geo']) <= RTOL * max(1.0, abs(g['ref_geo']))
+    ll0, _, _ = eng.eval(use_source=False)
+    assert rel_err(ll0, g['ref_ll_nosrc']) < RTOL
+    eng.close()
+    # a context without source state evaluates the source-free likelihood
+    eng = make_engine(c, n_chains=1, sample_source=False)
+    set_golden_state(eng, c, 0, with_source=False)
+    ll1, prior1, _ = eng.eval()
+    assert rel_err(ll1, g['ref_ll_nosrc']) < RTOL
+    assert abs(prior1[0] - g['ref_prior']) <= RTOL * max(1.0, abs(g['ref_prior']))
+    eng.close()
+
+
+@pytest.mark.parametrize('name', golden_cases())
+def test_components_and_posterior(name, built_lib):
+    c = load_case(name)
+    g = c['g']
+    eng = make_engine(c)
+    set_golden_state(eng, c)
+    lh, wn = eng.components(0)
+    assert np.max(np.abs(wn - g['ref_wnorm'])) < 1e-15
+    ref_lh = orc.component_likelihoods(c['features'], g['zones'], c['families'], g['p_global'], g['p_zones'],
+                                       c['p_families'], c['inheritance'])
+    assert np.max(np.abs(lh - ref_lh)) == 0.0      # pure table look-ups
+    assert np.max(np.abs(eng.source_posterior(0) - g['ref_post'])) < 1e-14
+    eng.close()
+
+
+@pytest.mark.parametrize('name', golden_cases())
+def test_counts_bit_exact(name, built_lib):
+    c = load_case(name)
+    g = c['g']
+    eng = make_engine(c)
+    set_golden_state(eng, c)
+    for recount in (False, True):
+        cnt = eng.counts(0, recount=recount)
+        assert np.array_equal(cnt['cnt_glob'], g['ref_cnt_glob'])
+        assert np.array_equal(cnt['cnt_zone'], g['ref_cnt_zone'])
+        assert np.array_equal(cnt['cnt_src_zone'], g['ref_cnt_src_zone'])
+        if c['inheritance']:
+            assert np.array_equal(cnt['cnt_fam'], g['ref_cnt_fam'])
+            assert np.array_equal(cnt['cnt_src_fam'], g['ref_cnt_src_fam'])
+    eng.close()
+
+
+@pytest.mark.parametrize('name', golden_cases())
+def test_move_probabilities(name, built_lib):
+    c = load_case(name)
+    g = c['g']
+    eng = make_engine(c)
+    set_golden_state(eng, c)
+    for kind, z, sn, sr, lq, lqb in g['ref_moves']:
+        k = ['grow', 'shrink', 'swap'][int(kind)]
+        q, qb = eng.move_log_q(0, k, int(z), int(sn), int(sr), 0.85)
+        assert abs(q - lq) < 1e-12 and abs(qb - lqb) < 1e-12, (k, q, lq, qb, lqb)
+    eng.close()
+
+
+def test_state_roundtrip_and_overlap(built_lib):
+    from contact_zones_b200._lib import SbError
+    c = load_case('D_small')
+    g = c['g']
+    eng = make_engine(c, n_chains=2)
+    set_golden_state(eng, c, 1)
+    s = eng.get_state(1)
+    assert np.array_equal(s['zones'], g['zones'])
+    assert np.array_equal(s['weights'], g['weights']) and np.array_equal(s['p_zones'], g['p_zones'])
+    assert np.array_equal(s['p_global'][0], g['p_global'][0]) and np.array_equal(s['p_families'], g['p_families'])
+    assert np.array_equal(np.argmax(s['source'], -1), g['source_idx'])
+    eng.copy_state(0, 1)
+    assert np.array_equal(eng.get_state(0)['zones'], g['zones'])
+    bad = g['zones'].copy()
+    bad[1] |= bad[0]
+    with pytest.raises(SbError):
+        eng.set_state(0, bad, g['weights'], g['p_global'], g['p_zones'], c['p_families'], g['source_idx'])
+    eng.close()
+
+
+def test_edge_cases(built_lib):
+    """-inf for a source pointing at a zero-weight component (model.py:181-182); zero probability -> -inf;
+    NA-only rows; a zone-free state; tiny probabilities (slow path of the product accumulator)."""
+    from contact_zones_b200 import synthetic
+    from contact_zones_b200.engine import Engine
+    data = synthetic.make_data(64, 9, 3, n_families=0, na_frac=0.3, seed=5)
+    data.features[3] = False                      # a site with only NA cells
+    st = synthetic.random_state(data, 2, 4, False, True, seed=6)
+    eng = Engine(data.features, data.states, None, data.network['adj_mat'], None, n_zones=2, n_chains=1,
+                 inheritance=False, sample_source=True)
+    args = (data.features, data.families, False, st['zones'], st['weights'], st['p_global'], st['p_zones'], None)
+
+    def both(src, **over):
+        a = list(args)
+        for k, v in over.items():
+            a[{'zones': 3, 'weights': 4, 'p_global': 5, 'p_zones': 6}[k]] = v
+        eng.set_state(0, a[3], a[4], a[5], a[6], None, src)
+        return (eng.eval(use_source=True)[0][0], eng.eval(use_source=False)[0][0],
+                orc.log_likelihood(*a, source=src), orc.log_likelihood(*a, source=None))
+
+    g1, g0, o1, o0 = both(st['source'])
+    assert rel_err(g1, o1) < RTOL and rel_err(g0, o0) < RTOL
+    # source -> contact at a site that is in no zone: chosen weight is 0 -> -inf
+    src = st['source'].copy()
+    free = np.flatnonzero(~st['zones'].any(0))[0]
+    src[free, 0] = [False, True]
+    g1, g0, o1, o0 = both(src)
+    assert g1 == -np.inf and o1 == -np.inf and rel_err(g0, o0) < RTOL
+    # zero and tiny probabilities
+    pg = st['p_global'].copy()
+    pg[0, 0, :] = [1e-250, 1.0 - 1e-250, 0.0][:pg.shape[2]] if pg.shape[2] == 3 else pg[0, 0, :]
+    g1, g0, o1, o0 = both(st['source'], p_global=pg)
+    assert (g0 == o0) or rel_err(g0, o0) < RTOL
+    assert (g1 == o1) or rel_err(g1, o1) < RTOL
+    # no site in any zone
+    z0 = np.zeros_like(st['zones'])
+    src0 = np.zeros_like(st['source'])
+    src0[..., 0] = True
+    g1, g0, o1, o0 = both(src0, zones=z0)
+    assert rel_err(g1, o1) < RTOL and rel_err(g0, o0) < RTOL
+    eng.close()
+
+
+def test_large_shape_properties(built_lib):
+    """BASELINE.json shape D (2000 x 200 x 8, 7 zones, 20 families): oracle parity plus size-independent
+    properties: chains holding the same state give the same bits; family == zone overlap identity
+    (test/test_model.py:52-92) at full size."""
+    from contact_zones_b200 import synthetic
+    from contact_zones_b200.engine import Engine
+    data = synthetic.make_data(2000, 200, 8, n_families=20, seed=0, with_dist=False)
+    st = synthetic.random_state(data, 7, 20, True, True, seed=1)
+    eng = Engine(data.features, data.states, data.families, data.network['adj_mat'], None, n_zones=7, n_chains=3,
+                 inheritance=True, sample_source=True)
+    for ch in range(3):
+        eng.set_state(ch, st['zones'], st['weights'], st['p_global'], st['p_zones'], st['p_families'], st['source'])
+    fam = np.asarray(data.families, bool)
+    args = (data.features, fam, True, st['zones'], st['weights'], st['p_global'], st['p_zones'], st['p_families'])
+    ll1 = eng.eval(use_source=True)[0]
+    ll0 = eng.eval(use_source=False)[0]
+    assert ll1[0] == ll1[1] == ll1[2] and ll0[0] == ll0[1] == ll0[2]
+    assert rel_err(ll1[0], orc.log_likelihood(*args, source=st['source'])) < RTOL
+    assert rel_err(ll0[0], orc.log_likelihood(*args, source=None)) < RTOL
+    cnt = eng.counts(0, recount=True)
+    assert np.array_equal(cnt['cnt_glob'], orc.state_counts_global(data.features, st['source']))
+    assert np.array_equal(cnt['cnt_fam'][7], orc.state_counts_family(data.features, st['source'], fam[7]))
+    assert np.array_equal(cnt['cnt_src_fam'], orc.source_counts(st['source'], fam.any(0)))
+    eng.close()
