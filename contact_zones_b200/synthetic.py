@@ -22,12 +22,12 @@ def delaunay_csr(locations):
 
 
 def make_data(n_sites, n_features, n_states, n_families=0, na_frac=0.02, seed=0, ragged_states=False,
-              with_dist=True, counts_prior=False, planted_zones=0, planted_size=20):
+              with_dist=True, counts_prior=False, planted_zones=0, planted_size=20, planted_conc=0.5):
     """Synthetic data set of SURVEY.md §8(d): uniform random states, `na_frac` NA cells, random family
     assignment (-1 = none), uniform locations on [0,1000]^2 with Delaunay adjacency.
 
     planted_zones > 0 draws the members of that many random connected groups from their own
-    Dirichlet(0.5) state distribution so that area moves are accepted at realistic rates."""
+    Dirichlet(planted_conc) state distribution so that area moves are accepted at realistic rates."""
     rng = np.random.default_rng(seed)
     n_states_f = np.full(n_features, n_states)
     if ragged_states and n_states > 2:
@@ -52,7 +52,7 @@ def make_data(n_sites, n_features, n_states, n_families=0, na_frac=0.02, seed=0,
             taken[s] = True
         planted[z, members] = True
         for f in range(n_features):
-            p = rng.dirichlet(np.full(n_states_f[f], 0.5))
+            p = rng.dirichlet(np.full(n_states_f[f], planted_conc))
             x[members, f] = rng.choice(n_states_f[f], size=len(members), p=p)
 
     features = np.zeros((n_sites, n_features, n_states), dtype=bool)
@@ -122,7 +122,7 @@ def random_zones(data, n_zones, size, rng):
     return zones
 
 
-def random_state(data, n_zones, zone_size, inheritance, with_source, seed=0):
+def random_state(data, n_zones, zone_size, inheritance, with_source, seed=0, zones=None):
     """A random sampler state (dict of the `Sample` arrays, `zone_sampling.py:68-75`)."""
     rng = np.random.default_rng(seed)
     n, f, s = data.features.shape
@@ -137,7 +137,7 @@ def random_state(data, n_zones, zone_size, inheritance, with_source, seed=0):
         return out
 
     st = {
-        'zones': random_zones(data, n_zones, zone_size, rng),
+        'zones': random_zones(data, n_zones, zone_size, rng) if zones is None else np.asarray(zones, dtype=bool),
         'weights': rng.dirichlet(np.ones(c), size=f),
         'p_global': dirichlet_rows((1,)),
         'p_zones': dirichlet_rows((n_zones,)),
