@@ -358,7 +358,7 @@ def run_gpu_arm(args, rank, world, local_rank):
         sweep = likelihood_leg(torch, local_rank)
         top = sweep[-1]
         peak, how = measured_peak()
-        roof = {'bound': 'hbm', 'kernel': 'lh_full_kernel<0> (K1) on 256 chains x 20000 x 100 x 4',
+        roof = {'bound': 'hbm', 'kernel': 'lh_table_kernel<2> (K1, source-free) on 256 chains x 20000 x 100 x 4',
                 'achieved': top['gbs_mean'], 'peak': peak, 'peak_source': how, 'unit': 'GB/s',
                 'frac': top['gbs_mean'] / peak, 'traffic': None,
                 'bytes_per_launch': top['bytes_per_launch'], 'us_per_launch': top['us_mean']}

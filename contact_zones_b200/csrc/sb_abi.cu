@@ -4,8 +4,10 @@
 #include "../../include/sbayes_b200.h"
 #include "sb_common.cuh"
 #include "sb_eval.cuh"
+#include "sb_lhtab.cuh"
 #include "sb_step.cuh"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -23,6 +25,9 @@ struct sb_ctx {
     std::vector<void*> allocs;
     double* partial = nullptr;       // [n_chains][n_tiles]
     int n_tiles = 0, sites_per_tile = 0;
+    LhTab lt{};                      // static layout of the table-driven K1 (sb_lhtab.cuh)
+    double* lt_partial = nullptr;    // [n_chains][lt.n_tiles * lt.n_chunks]
+    unsigned* lt_ticket = nullptr;   // [n_chains]
     int geo_cap = 0;                 // capacity (members) of the Prim scratch
     int64_t launches = 0;
     int64_t steps_done = 0;
@@ -254,6 +259,70 @@ int sb_upload_data(sb_ctx* ctx, const uint8_t* x, const uint8_t* applicable, con
         H2D(dcost, cost, (size_t)N * N);
     }
     d.cost = dcost;
+
+    // ---- static layout of the table-driven K1 (sb_lhtab.cuh): class-ordered groups + packed state codes ----
+    {
+        LhTab& t = ctx->lt;
+        t.radix = S + 1;
+        t.cpb = 1;
+        while (t.cpb < 3 && std::pow((double)t.radix, t.cpb + 1) <= (double)LT_ROW) ++t.cpb;
+        t.row_entries = 1;
+        for (int i = 0; i < t.cpb; ++i) t.row_entries *= t.radix;
+        t.G = 16 * t.cpb;
+        const int ncls_all = d.Fam + 1;                      // class = family id, "no family" last
+        std::vector<std::vector<int>> by_class(ncls_all);
+        for (int n = 0; n < N; ++n) by_class[fid[n] >= 0 ? fid[n] : d.Fam].push_back(n);
+        std::vector<int> perm, gclass, cfam;
+        for (int c = 0; c < ncls_all; ++c) {
+            if (by_class[c].empty()) continue;
+            const int ci = (int)cfam.size();
+            cfam.push_back(c < d.Fam ? c : -1);
+            for (size_t i = 0; i < by_class[c].size(); ++i) {
+                if (i % t.G == 0) gclass.push_back(ci);
+                perm.push_back(by_class[c][i]);
+            }
+            while (perm.size() % t.G) perm.push_back(-1);
+        }
+        t.n_groups = (int)gclass.size();
+        t.n_classes = (int)cfam.size();
+        t.n_tiles = (t.n_groups + LT_THREADS - 1) / LT_THREADS;
+        t.max_cls_tile = 1;
+        for (int tile = 0; tile < t.n_tiles; ++tile) {
+            const int g0 = tile * LT_THREADS, g1 = std::min(t.n_groups, g0 + LT_THREADS);
+            t.max_cls_tile = std::max(t.max_cls_tile, gclass[g1 - 1] - gclass[g0] + 1);
+        }
+        t.fc_max = std::max(1, std::min(F, (40 * 1024) / (t.max_cls_tile * 2 * LT_ROW * 4)));
+        std::vector<uint8_t> code((size_t)F * t.n_groups * 16);
+        for (int f = 0; f < F; ++f)
+            for (int g = 0; g < t.n_groups; ++g)
+                for (int b = 0; b < 16; ++b) {
+                    int c = 0, mul = 1;
+                    for (int i = 0; i < t.cpb; ++i) {
+                        const int n = perm[(size_t)g * t.G + b * t.cpb + i];
+                        int digit = S;
+                        if (n >= 0 && x[(size_t)n * F + f] != SB_NA) digit = x[(size_t)n * F + f];
+                        c += digit * mul;
+                        mul *= t.radix;
+                    }
+                    code[((size_t)f * t.n_groups + g) * 16 + b] = (uint8_t)(4 * c);   // byte offset of the table entry
+                }
+        // states that occur in the data count as applicable for the zero / tiny check of the table rows
+        for (int n = 0; n < N; ++n)
+            for (int f = 0; f < F; ++f)
+                if (x[(size_t)n * F + f] != SB_NA) mask[f] |= 1u << x[(size_t)n * F + f];
+        uint32_t* dchk;
+        DA(dchk, F);
+        H2D(dchk, mask.data(), F);
+        t.chk_mask = dchk;
+        uint8_t* dcode; int *dgc, *dcf, *dperm;
+        DA(dcode, code.size()); DA(dgc, gclass.size()); DA(dcf, cfam.size()); DA(dperm, perm.size());
+        H2D(dcode, code.data(), code.size()); H2D(dgc, gclass.data(), gclass.size());
+        H2D(dcf, cfam.data(), cfam.size()); H2D(dperm, perm.data(), perm.size());
+        t.xcode = dcode; t.group_class = dgc; t.class_fam = dcf; t.perm = dperm;
+        DA(ctx->lt_partial, (size_t)ctx->dims.n_chains * t.n_tiles * F);
+        DA(ctx->lt_ticket, ctx->dims.n_chains);
+        CK(cudaStreamSynchronize(ctx->stream));
+    }
     ctx->has_data = true;
     return SB_OK;
 }
@@ -444,6 +513,29 @@ int sb_copy_state(sb_ctx* ctx, int dst, int src) {
 // ---------------------------------------------------------------------------------------------
 static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source) {
     const DevData& d = ctx->d;
+    if (!use_source) {      // table-driven K1: one launch (weights normalisation and the per-chain reduction are fused)
+        LhTab t = ctx->lt;
+        // feature chunk: small enough for >= ~4 waves of CTAs (148 SMs x 8 resident) when the shape allows, and for
+        // the tables of one CTA to fit in 40 KB of shared memory
+        const long want = 4L * 148 * 8;
+        int chunks = (int)std::min<long>(d.F, std::max<long>(1, (want + (long)t.n_tiles * n - 1) / ((long)t.n_tiles * n)));
+        t.fc = std::min(t.fc_max, std::max(std::min(d.F, 8), (d.F + chunks - 1) / chunks));
+        t.n_chunks = (d.F + t.fc - 1) / t.fc;
+        t.smem = (((size_t)t.fc * 12 * sizeof(double) + 255) & ~(size_t)255) +
+                 (size_t)t.max_cls_tile * t.fc * 2 * LT_ROW * 4 + (((size_t)t.max_cls_tile * t.fc + 15) & ~(size_t)15);
+        dim3 grid(t.n_tiles, t.n_chunks, n);
+        double* part = ctx->lt_partial + (size_t)chain_begin * t.n_tiles * d.F;
+        unsigned* tick = ctx->lt_ticket + chain_begin;
+        if (t.cpb == 1)
+            lh_table_kernel<1><<<grid, LT_THREADS, t.smem, ctx->stream>>>(d, ctx->st, t, chain_begin, part, tick);
+        else if (t.cpb == 2)
+            lh_table_kernel<2><<<grid, LT_THREADS, t.smem, ctx->stream>>>(d, ctx->st, t, chain_begin, part, tick);
+        else
+            lh_table_kernel<3><<<grid, LT_THREADS, t.smem, ctx->stream>>>(d, ctx->st, t, chain_begin, part, tick);
+        ++ctx->launches;
+        CK(cudaGetLastError());
+        return SB_OK;
+    }
     dim3 gw((d.F + 127) / 128, n);
     wnorm_kernel<<<gw, 128, 0, ctx->stream>>>(d, ctx->st, chain_begin);
     dim3 grid(ctx->n_tiles, n);
