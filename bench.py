@@ -215,10 +215,20 @@ def likelihood_leg(torch, device, n_launch=60):
             b.record()
         torch.cuda.synchronize()
         ms = np.array([a.elapsed_time(b) for a, b in evs])
+        # the same launches back to back inside ONE event pair: the stream never runs dry, so this is pure device time
+        # per launch (a per-launch event pair also sees the host's enqueue gap when the kernel is shorter than it)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(n_launch):
+            eng.eval_likelihood_async()
+        b.record()
+        torch.cuda.synchronize()
+        us_b2b = a.elapsed_time(b) * 1e3 / n_launch
         nbytes = e['chains'] * b_lh(N, e['F'], e['S'], e['Z'], 0, 2, 0, 0)
         ll = eng.read_ll()
         out.append({'N': N, 'chains': e['chains'], 'bytes_per_launch': nbytes, 'us_mean': float(ms.mean() * 1e3),
-                    'us_min': float(ms.min() * 1e3), 'gbs_mean': float(nbytes / ms.mean() / 1e6),
+                    'us_min': float(ms.min() * 1e3), 'us_back_to_back': float(us_b2b),
+                    'gbs_mean': float(nbytes / ms.mean() / 1e6),
                     'll_chain0': float(ll[0])})
         eng.close()
     return out

@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -28,6 +29,8 @@ struct sb_ctx {
     LhTab lt{};                      // static layout of the table-driven K1 (sb_lhtab.cuh)
     double* lt_partial = nullptr;    // [n_chains][lt.n_tiles * lt.n_chunks]
     unsigned* lt_ticket = nullptr;   // [n_chains]
+    long lt_want = 148L * 14;        // CTA target of one K1 launch (SB_K1_CTAS overrides, for tuning)
+    std::vector<int> h_gclass;       // host copy of lt.group_class (class span of a group range)
     int geo_cap = 0;                 // capacity (members) of the Prim scratch
     int64_t launches = 0;
     int64_t steps_done = 0;
@@ -118,6 +121,7 @@ int sb_create(sb_ctx** out, int device, const sb_dims* dims) {
     sb_ctx* ctx = new sb_ctx();
     ctx->device = device;
     ctx->dims = *dims;
+    if (const char* e = getenv("SB_K1_CTAS")) ctx->lt_want = std::max(1L, atol(e));
     *out = ctx;   // returned even on failure so that the caller can read sb_last_error, then sb_destroy
     CK(cudaSetDevice(device));
     CK(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
@@ -285,13 +289,7 @@ int sb_upload_data(sb_ctx* ctx, const uint8_t* x, const uint8_t* applicable, con
         }
         t.n_groups = (int)gclass.size();
         t.n_classes = (int)cfam.size();
-        t.n_tiles = (t.n_groups + LT_THREADS - 1) / LT_THREADS;
-        t.max_cls_tile = 1;
-        for (int tile = 0; tile < t.n_tiles; ++tile) {
-            const int g0 = tile * LT_THREADS, g1 = std::min(t.n_groups, g0 + LT_THREADS);
-            t.max_cls_tile = std::max(t.max_cls_tile, gclass[g1 - 1] - gclass[g0] + 1);
-        }
-        t.fc_max = std::max(1, std::min(F, (40 * 1024) / (t.max_cls_tile * 2 * LT_ROW * 4)));
+        ctx->h_gclass = gclass;
         std::vector<uint8_t> code((size_t)F * t.n_groups * 16);
         for (int f = 0; f < F; ++f)
             for (int g = 0; g < t.n_groups; ++g)
@@ -319,7 +317,7 @@ int sb_upload_data(sb_ctx* ctx, const uint8_t* x, const uint8_t* applicable, con
         H2D(dcode, code.data(), code.size()); H2D(dgc, gclass.data(), gclass.size());
         H2D(dcf, cfam.data(), cfam.size()); H2D(dperm, perm.data(), perm.size());
         t.xcode = dcode; t.group_class = dgc; t.class_fam = dcf; t.perm = dperm;
-        DA(ctx->lt_partial, (size_t)ctx->dims.n_chains * t.n_tiles * F);
+        DA(ctx->lt_partial, (size_t)ctx->dims.n_chains * ((t.n_groups + LT_THREADS - 1) / LT_THREADS) * (F + LT_CORR_CTAS));
         DA(ctx->lt_ticket, ctx->dims.n_chains);
         CK(cudaStreamSynchronize(ctx->stream));
     }
@@ -515,16 +513,30 @@ static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source
     const DevData& d = ctx->d;
     if (!use_source) {      // table-driven K1: one launch (weights normalisation and the per-chain reduction are fused)
         LhTab t = ctx->lt;
-        // feature chunk: small enough for >= ~4 waves of CTAs (148 SMs x 8 resident) when the shape allows, and for
-        // the tables of one CTA to fit in 40 KB of shared memory
-        const long want = 4L * 148 * 8;
-        int chunks = (int)std::min<long>(d.F, std::max<long>(1, (want + (long)t.n_tiles * n - 1) / ((long)t.n_tiles * n)));
-        t.fc = std::min(t.fc_max, std::max(std::min(d.F, 8), (d.F + chunks - 1) / chunks));
+        // grid = (group splits, feature chunks, chains).  Every CTA pays a fixed latency chain (tables, zone-member
+        // correction, reduction); measured best on B200 (scripts/gpu_k1_sweep.sh) at about two waves of
+        // 148 SMs x 7 resident CTAs, each walking all groups of its split for its feature chunk
+        const int n_tiles = (t.n_groups + LT_THREADS - 1) / LT_THREADS;
+        const long want = ctx->lt_want;
+        const int fc_min = std::min(d.F, 4);
+        int chunks = (int)std::min<long>((d.F + fc_min - 1) / fc_min, std::max<long>(1, (want + n - 1) / n));
+        t.n_splits = (int)std::min<long>(n_tiles, std::max<long>(1, (want + (long)chunks * n - 1) / ((long)chunks * n)));
+        t.gsplit = (n_tiles + t.n_splits - 1) / t.n_splits * LT_THREADS;
+        t.n_splits = (t.n_groups + t.gsplit - 1) / t.gsplit;
+        t.max_cls = 1;
+        for (int sp = 0; sp < t.n_splits; ++sp) {
+            const int g0 = sp * t.gsplit, g1 = std::min(t.n_groups, g0 + t.gsplit);
+            t.max_cls = std::max(t.max_cls, ctx->h_gclass[g1 - 1] - ctx->h_gclass[g0] + 1);
+        }
+        t.fc = std::max(1, (d.F + chunks - 1) / chunks);
+        while (t.fc > 1 && lt_smem_bytes(t.fc, t.max_cls, d.S) > 46 * 1024) --t.fc;
+        if (lt_smem_bytes(t.fc, t.max_cls, d.S) > 46 * 1024) FAIL(SB_E_ARG, "K1 tables exceed shared memory (too many families)");
         t.n_chunks = (d.F + t.fc - 1) / t.fc;
-        t.smem = (((size_t)t.fc * 12 * sizeof(double) + 255) & ~(size_t)255) +
-                 (size_t)t.max_cls_tile * t.fc * 2 * LT_ROW * 4 + (((size_t)t.max_cls_tile * t.fc + 15) & ~(size_t)15);
-        dim3 grid(t.n_tiles, t.n_chunks, n);
-        double* part = ctx->lt_partial + (size_t)chain_begin * t.n_tiles * d.F;
+        t.smem = std::max(lt_smem_bytes(t.fc, t.max_cls, d.S), (size_t)std::min(d.F, LT_CORR_FB) * 12 * sizeof(double));
+        // blockIdx.y >= n_chunks: correction CTAs (zone members), concurrent with the streaming CTAs
+        const int n_corr = d.Z > 0 ? std::max(1, LT_CORR_CTAS / t.n_splits) : 0;
+        dim3 grid(t.n_splits, t.n_chunks + n_corr, n);
+        double* part = ctx->lt_partial + (size_t)chain_begin * n_tiles * (d.F + LT_CORR_CTAS);
         unsigned* tick = ctx->lt_ticket + chain_begin;
         if (t.cpb == 1)
             lh_table_kernel<1><<<grid, LT_THREADS, t.smem, ctx->stream>>>(d, ctx->st, t, chain_begin, part, tick);

@@ -21,11 +21,15 @@
 
 #define LT_THREADS 128
 #define LT_ROW 32                      // padded entries per table row (hi words, then lo words: 256 B per row)
+#define LT_CORR_FB 256                 // features per pass of a correction CTA (its w~ rows live in shared memory)
+#define LT_CORR_CTAS 4                 // correction CTAs per (chain, split)
 #define LT_TINY_HI 0x3C300000          // hi word of 2^-60: smaller factors (and 0) take the exact log path
 
 struct LhTab {
     int cpb, radix, row_entries, G;    // sites per code byte, S+1, radix^cpb, sites per group (16*cpb)
-    int n_groups, n_classes, n_tiles, fc, n_chunks, max_cls_tile, fc_max;   // fc / n_chunks are chosen per launch
+    int n_groups, n_classes;
+    // chosen per launch: features per CTA, groups per CTA (multiple of LT_THREADS), class capacity of the tables
+    int fc, n_chunks, gsplit, n_splits, max_cls;
     const uint8_t* xcode;              // [F][n_groups][16]
     const int* group_class;            // [n_groups] ascending
     const int* class_fam;              // [n_classes] family id or -1
@@ -33,6 +37,18 @@ struct LhTab {
     const uint32_t* chk_mask;          // [F] applicable states | states that occur in the data
     size_t smem;
 };
+
+// shared-memory footprint of one CTA (host + device agree through these helpers)
+__host__ __device__ __forceinline__ size_t lt_off_val(int fc) { return ((size_t)fc * 12 * 8 + 255) & ~(size_t)255; }
+__host__ __device__ __forceinline__ size_t lt_off_tab(int fc, int max_cls, int S) {
+    return (lt_off_val(fc) + (size_t)max_cls * fc * (S + 1) * 8 + 255) & ~(size_t)255;
+}
+__host__ __device__ __forceinline__ size_t lt_off_slow(int fc, int max_cls, int S) {
+    return lt_off_tab(fc, max_cls, S) + (size_t)max_cls * fc * 2 * LT_ROW * 4;
+}
+__host__ __device__ __forceinline__ size_t lt_smem_bytes(int fc, int max_cls, int S) {
+    return lt_off_slow(fc, max_cls, S) + (((size_t)max_cls * fc + 15) & ~(size_t)15);
+}
 
 __device__ __forceinline__ double lt_free_value(const DevData& d, const double* __restrict__ wn12,
                                                 const double* __restrict__ pg, const double* __restrict__ pf,
@@ -43,6 +59,117 @@ __device__ __forceinline__ double lt_free_value(const DevData& d, const double* 
     return wn12[0] * pg[o];
 }
 
+// 16 look-ups of one (group, feature) unit folded into the running product (m, e)
+template <int CPB>
+__device__ __forceinline__ void lt_unit(const uint4 xv, uint32_t row, double& m, int& e) {
+    constexpr int PERIOD = CPB == 1 ? 16 : (CPB == 2 ? 8 : 5);      // look-ups per partial product
+    const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+    double m0 = m, m1 = 1.0;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        // rows are 256-byte aligned and the code bytes hold 4*code, so one PRMT forms the LDS address
+        const uint32_t a = __byte_perm(row, xw[j >> 2], 0x3214 + (j & 3));
+        uint32_t hi, lo;
+        asm("ld.shared.u32 %0, [%1];" : "=r"(hi) : "r"(a));
+        asm("ld.shared.u32 %0, [%1+128];" : "=r"(lo) : "r"(a));
+        const double tv = __hiloint2double((int)hi, (int)lo);
+        if (j & 1) m1 *= tv; else m0 *= tv;
+        if ((j + 1) % (2 * PERIOD) == 0 || j == 15) {
+            // each partial product holds <= PERIOD factors >= 2^-60*CPB: no underflow before the merge
+            const int h0 = __double2hiint(m0), h1 = __double2hiint(m1);
+            e += ((h0 >> 20) & 0x7ff) + ((h1 >> 20) & 0x7ff) - 2046;
+            m0 = __hiloint2double((h0 & 0x800fffff) | 0x3ff00000, __double2loint(m0));
+            m1 = __hiloint2double((h1 & 0x800fffff) | 0x3ff00000, __double2loint(m1));
+            m0 *= m1;                       // in [1, 4)
+            m1 = 1.0;
+        }
+    }
+    m = m0;
+}
+
+// Correction CTA: zone members, + log prod mix_zone - log prod v_free over the member's non-NA cells.  CTA `idx` of
+// `nidx` takes members idx, idx + nidx, ... of every zone; one warp per member, lanes over the features (coalesced row
+// of x); the member ids of a warp are fetched by its lanes up front so that only one dependent load remains per cell.
+__device__ double lt_correction(const DevData& d, const ChainArrays& st, int chain, int idx, int nidx, double* wn /* smem */) {
+    LogProd num, den;
+    lp_init(num);
+    lp_init(den);
+    const int S = d.S;
+    const size_t FS = (size_t)d.F * S;
+    const double* __restrict__ w = st.weights + chain * st.s_weights;
+    const double* __restrict__ pg = st.p_global + chain * st.s_p_global;
+    const double* __restrict__ pz = st.p_zones + chain * st.s_p_zones;
+    const double* __restrict__ pf = st.p_fam + chain * st.s_p_fam;
+    const int* zsize = st.zone_size + chain * st.s_zone_size;
+    const int* members = st.zone_members + chain * st.s_zone_members;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = LT_THREADS >> 5;
+    for (int fb = 0; fb < d.F; fb += LT_CORR_FB) {
+        const int nfb = min(LT_CORR_FB, d.F - fb);
+        __syncthreads();
+        for (int i = threadIdx.x; i < nfb; i += LT_THREADS) wnorm_row(w + (size_t)(fb + i) * 3, wn + (size_t)i * 12, d.C);
+        __syncthreads();
+        int fill = 0;
+        double nm = num.m, dm = den.m;
+        for (int z = 0; z < d.Z; ++z) {
+            const int zs = zsize[z];
+            // this warp's members of zone z: mi = idx + (wid + j*nw) * nidx, j = 0, 1, ...
+            for (int j0 = 0; idx + (wid + j0 * nw) * nidx < zs; j0 += 32) {
+                const int mi_l = idx + (wid + (j0 + lane) * nw) * nidx;
+                int n_l = -1, fam_l = -1;
+                if (mi_l < zs) {
+                    n_l = members[(size_t)z * d.N + mi_l];
+                    if (d.inheritance) fam_l = d.fam_id[n_l];
+                }
+                const int cnt = __popc(__ballot_sync(0xffffffffu, n_l >= 0));
+                for (int j = 0; j < cnt; ++j) {
+                    const int n = __shfl_sync(0xffffffffu, n_l, j), fam = __shfl_sync(0xffffffffu, fam_l, j);
+                    const uint8_t* __restrict__ xr = d.x + (size_t)n * d.ldx + fb;
+                    const double* __restrict__ pzz = pz + (size_t)z * FS + (size_t)fb * S;
+                    const double* __restrict__ pff = pf + (size_t)max(fam, 0) * FS + (size_t)fb * S;
+                    const double* __restrict__ pgg = pg + (size_t)fb * S;
+                    for (int fi = lane; fi < nfb; fi += 32) {
+                        const int xs = xr[fi];
+                        if (xs == SB_NA) continue;
+                        const double* wr = wn + (size_t)fi * 12;
+                        const int o = fi * S + xs;
+                        const double pgv = pgg[o], pzv = pzz[o];
+                        double mix, vf;
+                        if (fam >= 0) {
+                            const double pfv = pff[o];
+                            mix = wr[9] * pgv + wr[10] * pzv + wr[11] * pfv;       // cfg = 3
+                            vf = wr[6] * pgv + wr[8] * pfv;                          // cfg = 2
+                        } else {
+                            mix = wr[3] * pgv + wr[4] * pzv;                         // cfg = 1
+                            vf = wr[0] * pgv;                                        // cfg = 0
+                        }
+                        const bool vf_ok = __double2hiint(vf) >= LT_TINY_HI;   // else: the main pass skipped the cell
+                        if (__double2hiint(mix) < LT_TINY_HI) {
+                            num.side += log(mix);                                    // exact path (may be -inf)
+                            if (!vf_ok) continue;
+                        } else {
+                            nm *= mix;
+                        }
+                        if (vf_ok) dm *= vf;
+                        if (++fill == 8) {                 // factors in [2^-60, 1]: renormalise every 8
+                            fill = 0;
+                            const int h0 = __double2hiint(nm), h1 = __double2hiint(dm);
+                            num.e += ((h0 >> 20) & 0x7ff) - 1023;
+                            den.e += ((h1 >> 20) & 0x7ff) - 1023;
+                            nm = __hiloint2double((h0 & 0x800fffff) | 0x3ff00000, __double2loint(nm));
+                            dm = __hiloint2double((h1 & 0x800fffff) | 0x3ff00000, __double2loint(dm));
+                        }
+                    }
+                }
+            }
+        }
+        num.m = nm;
+        den.m = dm;
+        lp_renorm(num);
+        lp_renorm(den);
+    }
+    return lp_value(num) - lp_value(den);
+}
+
 template <int CPB>
 __global__ void __launch_bounds__(LT_THREADS)
 lh_table_kernel(DevData d, ChainArrays st, LhTab t, int chain_begin, double* __restrict__ partial,
@@ -51,150 +178,119 @@ lh_table_kernel(DevData d, ChainArrays st, LhTab t, int chain_begin, double* __r
     __shared__ double red[33];
     __shared__ int is_last;
     const int chain = chain_begin + blockIdx.z;
-    const int tile = blockIdx.x, chunk = blockIdx.y;
+    const int split = blockIdx.x, chunk = blockIdx.y;
+    double v;
+    if (chunk >= t.n_chunks) {      // correction CTAs: blockIdx.y = n_chunks .. gridDim.y-1
+        v = lt_correction(d, st, chain, (chunk - t.n_chunks) * gridDim.x + split, (gridDim.y - t.n_chunks) * gridDim.x,
+                          reinterpret_cast<double*>(lt_smem));
+    } else {
     const int f0 = chunk * t.fc, nf = min(d.F, f0 + t.fc) - f0;
-    const int g0 = tile * LT_THREADS, g1 = min(t.n_groups, g0 + LT_THREADS);
+    const int g0 = split * t.gsplit, g1 = min(t.n_groups, g0 + t.gsplit);
     const int c_lo = t.group_class[g0], ncls = t.group_class[g1 - 1] - c_lo + 1;
+    const int S = d.S, S1 = S + 1;
 
-    // shared layout: wn [fc][12] f64 | tab [max_cls_tile][fc][2][LT_ROW] u32 (256-byte aligned rows) | slow [..] u8
+    // shared layout: wn [fc][12] f64 | val [max_cls*fc][S+1] f64 | tab [max_cls*fc][2][LT_ROW] u32 | slow [..] u8
     double* wn = reinterpret_cast<double*>(lt_smem);
-    uint32_t* tab = reinterpret_cast<uint32_t*>(lt_smem + (((size_t)t.fc * 12 * sizeof(double) + 255) & ~(size_t)255));
-    unsigned char* slow = reinterpret_cast<unsigned char*>(tab + (size_t)t.max_cls_tile * t.fc * 2 * LT_ROW);
+    double* val = reinterpret_cast<double*>(lt_smem + lt_off_val(t.fc));
+    uint32_t* tab = reinterpret_cast<uint32_t*>(lt_smem + lt_off_tab(t.fc, t.max_cls, S));
+    unsigned char* slow = lt_smem + lt_off_slow(t.fc, t.max_cls, S);
     const uint32_t tab_s = (uint32_t)__cvta_generic_to_shared(tab);
 
     const double* __restrict__ w = st.weights + chain * st.s_weights;
     const double* __restrict__ pg = st.p_global + chain * st.s_p_global;
-    const double* __restrict__ pz = st.p_zones + chain * st.s_p_zones;
     const double* __restrict__ pf = st.p_fam + chain * st.s_p_fam;
     const int8_t* __restrict__ zone_id = st.zone_id + chain * st.s_zone_id;
-    const int S = d.S;
 
+    // ---- tables of this CTA: rows (class, feature) -------------------------------------------------
     for (int i = threadIdx.x; i < nf; i += LT_THREADS) wnorm_row(w + (size_t)(f0 + i) * 3, wn + (size_t)i * 12, d.C);
+    for (int i = threadIdx.x; i < ncls * nf; i += LT_THREADS) slow[i] = 0;
     __syncthreads();
-    // one thread builds one table row (class, feature): the S+1 cell values, then their CPB-fold products
-    for (int r = threadIdx.x; r < ncls * nf; r += LT_THREADS) {
-        const int ci = r / nf, fi = r - ci * nf;
-        const int fam = t.class_fam[c_lo + ci];
-        const uint32_t chk = t.chk_mask[f0 + fi];
-        double val[SB_MAX_S + 1];
-        bool tiny = false;
-        for (int s = 0; s < S; ++s) {
-            val[s] = lt_free_value(d, wn + (size_t)fi * 12, pg, pf, fam, f0 + fi, s);
+    int tiny = 0;
+    for (int i = threadIdx.x; i < ncls * nf * S1; i += LT_THREADS) {
+        const int r = i / S1, s = i - r * S1, ci = r / nf, fi = r - ci * nf;
+        double v = 1.0;                                                      // NA / padding digit
+        if (s < S) {
+            v = lt_free_value(d, wn + (size_t)fi * 12, pg, pf, t.class_fam[c_lo + ci], f0 + fi, s);
             // a tiny / zero value at a state that can occur sends the row to the exact cell-by-cell path
-            if ((chk >> s & 1u) && __double2hiint(val[s]) < LT_TINY_HI) tiny = true;
+            if ((t.chk_mask[f0 + fi] >> s & 1u) && __double2hiint(v) < LT_TINY_HI) { slow[r] = 1; tiny = 1; }
         }
-        val[S] = 1.0;
-        slow[ci * nf + fi] = tiny ? 1 : 0;
+        val[i] = v;
+    }
+    const int any_slow = __syncthreads_or(tiny);
+    for (int i = threadIdx.x; i < ncls * nf * LT_ROW; i += LT_THREADS) {
+        const int r = i / LT_ROW, code = i - r * LT_ROW, ci = r / nf, fi = r - ci * nf;
+        if (code >= t.row_entries) continue;
+        const double* vr = val + (size_t)r * S1;
+        double v = 1.0;
+        int c = code;
+#pragma unroll
+        for (int k = 0; k < CPB; ++k) {
+            const int q = c / t.radix;
+            v *= vr[c - q * t.radix];
+            c = q;
+        }
         uint32_t* row = tab + (size_t)(ci * t.fc + fi) * 2 * LT_ROW;
-        int code = 0;
-        const int R = t.radix;
-        for (int a2 = 0; a2 < (CPB >= 3 ? R : 1); ++a2)
-            for (int a1 = 0; a1 < (CPB >= 2 ? R : 1); ++a1)
-                for (int a0 = 0; a0 < R; ++a0, ++code) {
-                    double v = val[a0];
-                    if (CPB >= 2) v *= val[a1];
-                    if (CPB >= 3) v *= val[a2];
-                    row[code] = (uint32_t)__double2hiint(v);
-                    row[LT_ROW + code] = (uint32_t)__double2loint(v);
-                }
+        row[code] = (uint32_t)__double2hiint(v);
+        row[LT_ROW + code] = (uint32_t)__double2loint(v);
     }
     __syncthreads();
 
     // ---- main pass: every site as if it were in no zone -----------------------------------------
     LogProd acc;
     lp_init(acc);
-    const int g = g0 + threadIdx.x;
-    if (g < g1) {
+    const size_t xstride = (size_t)t.n_groups * 16;
+    constexpr int PF = 4;                                                // code vectors in flight per thread
+    for (int g = g0 + threadIdx.x; g < g1; g += LT_THREADS) {
         const int ci = t.group_class[g] - c_lo;
-        const size_t xstride = (size_t)t.n_groups * 16;
         const uint8_t* __restrict__ xp = t.xcode + (size_t)g * 16 + (size_t)f0 * xstride;
-        constexpr int PERIOD = CPB == 1 ? 16 : (CPB == 2 ? 8 : 5);      // look-ups between renormalisations
-        constexpr int PF = 4;                                            // code vectors in flight per thread
-        uint4 buf[PF];
-#pragma unroll
-        for (int k = 0; k < PF; ++k)
-            if (k < nf) buf[k] = __ldg(reinterpret_cast<const uint4*>(xp + (size_t)k * xstride));
-        for (int fb = 0; fb < nf; fb += PF) {
+        uint32_t row = tab_s + (uint32_t)(ci * t.fc) * (2 * LT_ROW * 4);
+        if (!any_slow) {
+            uint4 buf[PF];
 #pragma unroll
             for (int k = 0; k < PF; ++k) {
-                const int fi = fb + k;
-                if (fi >= nf) break;
-                const uint4 xv = buf[k];
-                if (fi + PF < nf) buf[k] = __ldg(reinterpret_cast<const uint4*>(xp + (size_t)(fi + PF) * xstride));
-                if (slow[ci * nf + fi]) {
-                    const int fam = t.class_fam[c_lo + ci];
-                    for (int q = 0; q < t.G; ++q) {
-                        const int n = t.perm[(size_t)g * t.G + q];
-                        if (n < 0) continue;
-                        const int xs = d.x[(size_t)n * d.ldx + f0 + fi];
-                        if (xs == SB_NA) continue;
-                        const double v = lt_free_value(d, wn + (size_t)fi * 12, pg, pf, fam, f0 + fi, xs);
-                        // a zone member with a tiny free value is left to the correction pass (no -inf - -inf)
-                        if (zone_id[n] >= 0 && __double2hiint(v) < LT_TINY_HI) continue;
-                        lp_mul(acc, v);
-                    }
-                    continue;
-                }
-                // rows are 256-byte aligned and the code bytes hold 4*code, so one PRMT forms the LDS address
-                const uint32_t row = tab_s + (uint32_t)(ci * t.fc + fi) * (2 * LT_ROW * 4);
-                const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
-                double m0 = acc.m, m1 = 1.0;
+                if (k < nf) buf[k] = __ldg(reinterpret_cast<const uint4*>(xp));
+                xp += xstride;
+            }
+            double m = acc.m;
+            int e = acc.e;
+            for (int fb = 0; fb < nf; fb += PF) {
 #pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    const uint32_t a = __byte_perm(row, xw[j >> 2], 0x3214 + (j & 3));
-                    uint32_t hi, lo;
-                    asm volatile("ld.shared.u32 %0, [%2];\n\tld.shared.u32 %1, [%2+128];" : "=r"(hi), "=r"(lo) : "r"(a));
-                    const double tv = __hiloint2double((int)hi, (int)lo);
-                    if (j & 1) m1 *= tv; else m0 *= tv;
-                    if ((j + 1) % (2 * PERIOD) == 0 || j == 15) {
-                        // each partial product holds <= PERIOD factors >= 2^-60*CPB: no underflow before the merge
-                        const int h0 = __double2hiint(m0), h1 = __double2hiint(m1);
-                        acc.e += ((h0 >> 20) & 0x7ff) + ((h1 >> 20) & 0x7ff) - 2046;
-                        m0 = __hiloint2double((h0 & 0x800fffff) | 0x3ff00000, __double2loint(m0));
-                        m1 = __hiloint2double((h1 & 0x800fffff) | 0x3ff00000, __double2loint(m1));
-                        m0 *= m1;                       // in [1, 4)
-                        m1 = 1.0;
+                for (int k = 0; k < PF; ++k) {
+                    if (fb + k < nf) {
+                        const uint4 xv = buf[k];
+                        if (fb + k + PF < nf) buf[k] = __ldg(reinterpret_cast<const uint4*>(xp));
+                        xp += xstride;
+                        lt_unit<CPB>(xv, row, m, e);
+                        row += 2 * LT_ROW * 4;
                     }
                 }
-                acc.m = m0;
-                acc.k = 0;
             }
+            acc.m = m;
+            acc.e = e;
+            continue;
+        }
+        // general path (some row of this CTA holds a tiny / zero value)
+        for (int fi = 0; fi < nf; ++fi, row += 2 * LT_ROW * 4) {
+            if (!slow[ci * nf + fi]) {
+                lt_unit<CPB>(__ldg(reinterpret_cast<const uint4*>(xp + (size_t)fi * xstride)), row, acc.m, acc.e);
+                continue;
+            }
+            for (int q = 0; q < t.G; ++q) {
+                const int n = t.perm[(size_t)g * t.G + q];
+                if (n < 0) continue;
+                const int xs = d.x[(size_t)n * d.ldx + f0 + fi];
+                if (xs == SB_NA) continue;
+                const double v = val[(size_t)(ci * nf + fi) * S1 + xs];
+                // a zone member with a tiny free value is left to the correction pass (no -inf - -inf)
+                if (zone_id[n] >= 0 && __double2hiint(v) < LT_TINY_HI) continue;
+                lp_mul(acc, v);
+            }
+            lp_renorm(acc);
         }
     }
-    double v = lp_value(acc);
+    v = lp_value(acc);
+    }
 
-    // ---- correction pass: zone members, + log mix_zone - log v_free.  Member i of a zone goes to tile i % n_tiles;
-    //      one warp per member, lanes over the features of the chunk (coalesced x row) ------------------------
-    if (d.Z > 0) {
-        LogProd num, den;
-        lp_init(num);
-        lp_init(den);
-        const int* zsize = st.zone_size + chain * st.s_zone_size;
-        const int* members = st.zone_members + chain * st.s_zone_members;
-        const size_t FS = (size_t)d.F * S;
-        const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = LT_THREADS >> 5;
-        const int n_tiles = gridDim.x;
-        for (int z = 0; z < d.Z; ++z) {
-            const int zs = zsize[z];
-            for (int mi = tile + wid * n_tiles; mi < zs; mi += nw * n_tiles) {
-                const int n = members[(size_t)z * d.N + mi];
-                const int fam = d.inheritance ? d.fam_id[n] : -1;
-                for (int fi = lane; fi < nf; fi += 32) {
-                    const int f = f0 + fi;
-                    const int xs = d.x[(size_t)n * d.ldx + f];
-                    if (xs == SB_NA) continue;
-                    const double* wr = wn + (size_t)fi * 12 + (fam >= 0 ? 9 : 3);      // cfg = 1 + 2*has_family
-                    const size_t o = (size_t)f * S + xs;
-                    double mix = wr[0] * pg[o] + wr[1] * pz[(size_t)z * FS + o];
-                    if (fam >= 0) mix += wr[2] * pf[(size_t)fam * FS + o];
-                    lp_mul(num, mix);
-                    const double vf = lt_free_value(d, wn + (size_t)fi * 12, pg, pf, fam, f, xs);
-                    if (__double2hiint(vf) >= LT_TINY_HI) lp_mul(den, vf);          // else: the main pass skipped it
-                }
-            }
-        }
-        v += lp_value(num) - lp_value(den);
-    }
     v = block_sum(v, red);
 
     // ---- deterministic per-chain reduction: the last CTA of the chain sums the partials in fixed order ---
