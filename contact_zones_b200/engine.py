@@ -138,18 +138,20 @@ class Engine:
             raise ValueError('a SAMPLE_SOURCE engine needs a source array')
         self._check(self.lib.sb_set_state(self._ctx, int(chain), ptr(zones), ptr(w), ptr(pg), ptr(pz), ptr(pf), ptr(src)))
 
-    def get_state(self, chain, one_hot_source=True):
-        zones = np.zeros((self.Z, self.N), np.uint8)
-        w = np.zeros((self.F, self.C))
-        pg = np.zeros((1, self.F, self.S))
-        pz = np.zeros((self.Z, self.F, self.S))
-        pf = np.zeros((self.Fam, self.F, self.S)) if self.inheritance else None
-        src = np.zeros((self.N, self.F), np.uint8) if self.sample_source else None
+    def get_state(self, chain, one_hot_source=True, fields=None):
+        """Device image of chain -> the `Sample` arrays.  `fields` limits the read-back (e.g. ('zones', 'weights'))."""
+        want = (lambda k: fields is None or k in fields)
+        zones = np.zeros((self.Z, self.N), np.uint8) if want('zones') else None
+        w = np.zeros((self.F, self.C)) if want('weights') else None
+        pg = np.zeros((1, self.F, self.S)) if want('p_global') else None
+        pz = np.zeros((self.Z, self.F, self.S)) if want('p_zones') else None
+        pf = np.zeros((self.Fam, self.F, self.S)) if (self.inheritance and want('p_families')) else None
+        src = np.zeros((self.N, self.F), np.uint8) if (self.sample_source and want('source')) else None
         self._check(self.lib.sb_get_state(self._ctx, int(chain), ptr(zones), ptr(w), ptr(pg), ptr(pz), ptr(pf), ptr(src)))
         if src is not None and one_hot_source:
             src = np.eye(self.C, dtype=bool)[src]
-        return {'zones': zones.astype(bool), 'weights': w, 'p_global': pg, 'p_zones': pz, 'p_families': pf,
-                'source': src}
+        return {'zones': None if zones is None else zones.astype(bool), 'weights': w, 'p_global': pg, 'p_zones': pz,
+                'p_families': pf, 'source': src}
 
     def copy_state(self, dst, src):
         self._check(self.lib.sb_copy_state(self._ctx, int(dst), int(src)))

@@ -58,3 +58,61 @@ def set_golden_state(eng, c, chain=0, with_source=True):
     g = c['g']
     eng.set_state(chain, g['zones'], g['weights'], g['p_global'], g['p_zones'], c['p_families'],
                   g['source_idx'] if with_source else None)
+
+
+# ---- posterior-summary fixtures of the reference sampler (oracle/make_golden_runs.py) -------------------------
+PRECISION = {'weights': 15, 'universal': 40, 'contact': 20, 'inheritance': 20}
+RUN_KEYS = ['zone_size', 'planted_occ', 'w_comp', 'll_mean', 'prior_mean', 'acc']
+
+
+def run_cases():
+    return sorted(f[:-4] for f in os.listdir(GOLDEN) if f.startswith('run_') and f.endswith('.npz'))
+
+
+def load_run(name):
+    g = dict(np.load(os.path.join(GOLDEN, name + '.npz'), allow_pickle=False))
+    n, f = g['features_idx'].shape
+    s = int(g['n_states'])
+    c = {'name': name, 'g': g, 'N': n, 'F': f, 'S': s, 'inheritance': bool(g['inheritance']),
+         'sample_source': bool(g['sample_source']), 'counts_prior': bool(g['counts_prior']),
+         'geo_type': str(g['geo_type']), 'size_type': str(g['size_type']), 'geo_scale': float(g['geo_scale'])}
+    c['features'] = orc.one_hot(g['features_idx'], s)
+    c['families'] = g['families'].astype(bool)
+    c['adj'] = csr_matrix((np.ones(len(g['adj_indices']), dtype=np.int64), g['adj_indices'], g['adj_indptr']), shape=(n, n))
+    c['cost'] = g['cost'] if g['cost'].size else None
+    c['Z'] = g['zones'].shape[0]
+    c['C'] = 3 if c['inheritance'] else 2
+    c['p_families'] = g['p_families'] if c['inheritance'] else None
+    c['operators'] = {str(k): float(v) for k, v in zip(g['op_names'], g['op_weights'])}
+    c['prior_cfg'] = {
+        'geo': {'type': c['geo_type'], 'scale': c['geo_scale']}, 'area_size': {'type': c['size_type']},
+        'weights': {'type': 'uniform'}, 'contact': {'type': 'uniform'},
+        'universal': {'type': 'counts' if c['counts_prior'] else 'uniform'},
+        'inheritance': {'type': 'counts' if c['counts_prior'] else 'uniform'}}
+    return c
+
+
+def summarise_run(zones, weights, ll, prior, acc, planted, burn):
+    """The label-switching-invariant scalars of oracle/make_golden_runs.py:summarise for one chain."""
+    zones, weights = np.asarray(zones)[burn:], np.asarray(weights)[burn:]
+    occ = zones.any(axis=1)
+    return {'zone_size': occ.sum(axis=1).mean(), 'planted_occ': occ[:, planted].mean(),
+            'w_comp': weights.mean(axis=(0, 1)), 'll_mean': np.mean(np.asarray(ll)[burn:]),
+            'prior_mean': np.mean(np.asarray(prior)[burn:]), 'acc': np.asarray(acc, dtype=float)}
+
+
+def run_z_scores(c, chains):
+    """z-score of the mean over `chains` (list of summarise_run dicts) against the reference runs' mean, using the
+    run-to-run spread of both sides; the spread is floored (1e-3 + 0.5 % of the mean) so that a statistic on which all
+    six reference runs happen to agree does not blow the score up."""
+    g = c['g']
+    out = {}
+    for k in RUN_KEYS:
+        ref = np.asarray(g['ref_' + k], dtype=float)
+        ours = np.stack([np.asarray(s[k], dtype=float) for s in chains])
+        rm, om = ref.mean(0), ours.mean(0)
+        floor = 1e-3 + 5e-3 * np.abs(rm)
+        rs = np.maximum(ref.std(0, ddof=1), floor)
+        os_ = np.maximum(ours.std(0, ddof=1), floor) if len(chains) > 1 else rs
+        out[k] = np.abs(om - rm) / np.sqrt(rs ** 2 / len(ref) + os_ ** 2 / len(chains))
+    return out

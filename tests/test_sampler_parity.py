@@ -1,0 +1,63 @@
+"""GPU: distributional parity of the CUDA sampler (persistent kernel K8 + operators K7, through the C ABI) with the
+reference's CPU sampler.  BASELINE.json north_star: "because the RNG differs, posterior summaries ... must agree with
+the reference's CPU run within Monte-Carlo error".  The fixtures hold six independent runs of the UNMODIFIED reference
+(oracle/make_golden_runs.py); we run 16 chains of the same length from the same initial state and compare the
+label-switching-invariant summaries.  Bar: |z| < 4.5 on every statistic (z against the run-to-run spread of both
+sides)."""
+import numpy as np
+import pytest
+
+from helpers import PRECISION, load_run, run_cases, run_z_scores, summarise_run
+
+pytestmark = pytest.mark.gpu
+N_CHAINS = 16
+Z_MAX = 4.5
+
+
+@pytest.mark.parametrize('name', run_cases())
+def test_posterior_summaries_match_reference(name, built_lib):
+    from contact_zones_b200 import _lib
+    from contact_zones_b200.engine import Engine
+    c = load_run(name)
+    g = c['g']
+    eng = Engine(g['features_idx'], g['states'], c['families'] if c['inheritance'] else None, c['adj'], c['cost'],
+                 n_zones=c['Z'], n_chains=N_CHAINS, inheritance=c['inheritance'], sample_source=c['sample_source'])
+    eng.set_priors(size_type=c['size_type'], geo_type=c['geo_type'], geo_scale=c['geo_scale'],
+                   p_global_type='counts' if c['counts_prior'] else 'uniform',
+                   p_families_type='counts' if (c['counts_prior'] and c['inheritance']) else 'uniform',
+                   gibbs_counts_global=g.get('gibbs_counts_global'), alpha_global=g.get('alpha_global'),
+                   gibbs_counts_fam=g.get('gibbs_counts_fam'), alpha_fam=g.get('alpha_fam'))
+    for ch in range(N_CHAINS):
+        eng.set_state(ch, g['zones'], g['weights'], g['p_global'], g['p_zones'], c['p_families'],
+                      g['source_idx'] if c['sample_source'] else None)
+    eng.eval()
+    eng.set_operators(c['operators'], PRECISION, min_size=3, max_size=30, p_grow_connected=0.85, seed=2024)
+    n_steps, n_samples = int(g['n_steps']), int(g['n_samples'])
+    every = n_steps // n_samples
+    zs = [[] for _ in range(N_CHAINS)]
+    ws = [[] for _ in range(N_CHAINS)]
+    lls, prs = [], []
+    for _ in range(n_samples):
+        eng.run(every)
+        ll, pr = eng.chain_scalars()
+        lls.append(ll)
+        prs.append(pr)
+        for ch in range(N_CHAINS):
+            s = eng.get_state(ch, fields=('zones', 'weights'))
+            zs[ch].append(s['zones'])
+            ws[ch].append(s['weights'])
+    acc, rej = eng.op_stats()
+    names = [str(k) for k in g['op_names']]
+    lls, prs = np.array(lls), np.array(prs)
+    chains = []
+    for ch in range(N_CHAINS):
+        a = [acc[ch, _lib.OP_IDS[k]] / max(1, acc[ch, _lib.OP_IDS[k]] + rej[ch, _lib.OP_IDS[k]]) for k in names]
+        chains.append(summarise_run(zs[ch], ws[ch], lls[:, ch], prs[:, ch], a, g['planted'], burn=n_samples // 5))
+    # the running ll / prior of the sampler equal a from-scratch evaluation of the final states
+    ll_new, pr_new, _ = eng.eval()
+    assert np.allclose(lls[-1], ll_new, rtol=1e-9) and np.allclose(prs[-1], pr_new, rtol=1e-9, atol=1e-9)
+    eng.close()
+    z = run_z_scores(c, chains)
+    worst = {k: float(np.max(v)) for k, v in z.items()}
+    assert max(worst.values()) < Z_MAX, (name, worst, {k: np.mean([s[k] for s in chains], axis=0) for k in z},
+                                         {k: g['ref_' + k].mean(0) for k in z})
