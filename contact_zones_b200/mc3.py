@@ -1,0 +1,111 @@
+"""K9 -- MC3 over several GPUs: chain sharding, the per-swap exchange of (log-likelihood, log-prior) and the snapshot
+hand-off of the logged chain.
+
+Reference semantics (`mcmc_generative.py:242-280`, quirk Q4): all chains run at temperature 1; a swap only exchanges
+which chain is LABEL 0 (the logged one): `chain_swaps` times pick j in [1, n) and swap labels 0 <-> j with probability
+min(1, exp((ll_j + prior_j) - (ll_0 + prior_0))).  No state moves between chains, so across GPUs the swap needs two
+doubles per chain (one all-gather) and every rank then takes the same decisions from a shared counter-based stream.
+
+One process per GPU (`torch.distributed`, backend nccl on the GPU box, gloo in the CPU tests); without an initialised
+process group everything degenerates to the single-process case.
+"""
+import numpy as np
+
+
+def _dist():
+    try:
+        import torch.distributed as dist
+    except Exception:           # torch is plumbing only; single-process use does not need it
+        return None
+    return dist if (dist.is_available() and dist.is_initialized()) else None
+
+
+class ChainShard:
+    """Block partition of `n_chains` global chains over the ranks of the default process group."""
+
+    def __init__(self, n_chains, rank=None, world=None):
+        dist = _dist()
+        self.world = int(world if world is not None else (dist.get_world_size() if dist else 1))
+        self.rank = int(rank if rank is not None else (dist.get_rank() if dist else 0))
+        self.n_chains = int(n_chains)
+        base, extra = divmod(self.n_chains, self.world)
+        self.counts = [base + (1 if r < extra else 0) for r in range(self.world)]
+        self.offsets = np.concatenate([[0], np.cumsum(self.counts)]).astype(int)
+        self.offset = int(self.offsets[self.rank])
+        self.n_local = int(self.counts[self.rank])
+
+    def owner(self, chain):
+        """(rank, local index) of a global chain id."""
+        r = int(np.searchsorted(self.offsets, chain, side='right') - 1)
+        return r, int(chain - self.offsets[r])
+
+    def is_local(self, chain):
+        return self.owner(chain)[0] == self.rank
+
+    # -- collectives ------------------------------------------------------------------------------------------
+    def all_gather_scalars(self, ll_local, prior_local, device=None):
+        """(ll, prior) of every global chain on every rank: 16 B per chain per swap period."""
+        ll_local, prior_local = np.asarray(ll_local, float), np.asarray(prior_local, float)
+        dist = _dist()
+        if dist is None or self.world == 1:
+            return ll_local.copy(), prior_local.copy()
+        import torch
+        m = max(self.counts)
+        buf = torch.zeros(2 * m, dtype=torch.float64)
+        buf[:self.n_local] = torch.from_numpy(ll_local)
+        buf[m:m + self.n_local] = torch.from_numpy(prior_local)
+        if device is not None:
+            buf = buf.to(device)
+        out = torch.empty(self.world * 2 * m, dtype=torch.float64, device=buf.device)
+        dist.all_gather_into_tensor(out, buf)
+        out = out.cpu().numpy().reshape(self.world, 2, m)
+        ll = np.concatenate([out[r, 0, :self.counts[r]] for r in range(self.world)])
+        pr = np.concatenate([out[r, 1, :self.counts[r]] for r in range(self.world)])
+        return ll, pr
+
+    def broadcast_state(self, chain, arrays_local, template, device=None):
+        """Every rank gets the state arrays of global `chain` from its owner (one broadcast of the packed arrays:
+        ~0.4 MB at shape D, only at the N_SAMPLES logging points).  `arrays_local`: callable evaluated on the owner
+        only, returns {name: array}; `template`: {name: (shape, dtype)}, identical on all ranks."""
+        owner, _ = self.owner(chain)
+        dist = _dist()
+        if dist is None or self.world == 1:
+            return arrays_local()
+        import torch
+        keys = sorted(template)
+        n = int(sum(int(np.prod(template[k][0])) for k in keys))
+        if self.rank == owner:
+            arrs = arrays_local()
+            flat = np.concatenate([np.asarray(arrs[k], dtype=np.float64).ravel() for k in keys])
+            t = torch.from_numpy(np.ascontiguousarray(flat))
+        else:
+            t = torch.empty(n, dtype=torch.float64)
+        if device is not None:
+            t = t.to(device)
+        dist.broadcast(t, src=owner)
+        flat = t.cpu().numpy()
+        out, o = {}, 0
+        for k in keys:
+            shape, dt = template[k]
+            sz = int(np.prod(shape))
+            out[k] = flat[o:o + sz].reshape(shape).astype(dt)
+            o += sz
+        return out
+
+
+def swap_chains(chain_idx, ll, prior, chain_swaps, rng, statistics=None):
+    """`MCMCGenerative.swap_chains` (mcmc_generative.py:242-280) on gathered scalars.  `chain_idx` (list, label ->
+    chain) is permuted in place; `rng` is a numpy Generator every rank seeds identically, so all ranks agree."""
+    n = len(chain_idx)
+    for _ in range(int(chain_swaps)):
+        if statistics is not None:
+            statistics['n_swaps'] += 1
+        swap_from = chain_idx[0]
+        swap_to_idx = int(rng.integers(1, n))                 # np.random.choice(range(1, n_chains))   :252
+        swap_to = chain_idx[swap_to_idx]
+        mh = (ll[swap_to] - ll[swap_from]) + (prior[swap_to] - prior[swap_from])     # :263-265 with q_to = q_from = 0
+        if np.log(rng.random()) < mh:                         # :268
+            chain_idx[0], chain_idx[swap_to_idx] = swap_to, swap_from
+            if statistics is not None:
+                statistics['accepted_swaps'] += 1
+    return chain_idx

@@ -116,3 +116,34 @@ def run_z_scores(c, chains):
         os_ = np.maximum(ours.std(0, ddof=1), floor) if len(chains) > 1 else rs
         out[k] = np.abs(om - rm) / np.sqrt(rs ** 2 / len(ref) + os_ ** 2 / len(chains))
     return out
+
+
+# ---- reference-shaped `data` / config objects for the API mirror (contact_zones_b200.model / .sampling) ----------
+def case_data(c):
+    """types.SimpleNamespace with the attributes the hot path reads."""
+    from types import SimpleNamespace
+    g = c['g']
+    f, s = c['F'], c['S']
+    data = SimpleNamespace(
+        features=c['features'], families=c['families'], states=g['states'].astype(bool),
+        network={'adj_mat': c['adj'], 'locations': None, 'dist_mat': c['cost']},
+        prior_universal={}, prior_inheritance={}, geo_prior={'cost_matrix': c['cost']},
+        state_names={'internal': [list(range(int(k))) for k in g['states'].sum(1)],
+                     'external': [[f's{j}' for j in range(int(k))] for k in g['states'].sum(1)]},
+        feature_names={'external': [f'f{i}' for i in range(f)]},
+        family_names={'external': [f'fam{i}' for i in range(c['families'].shape[0])]},
+        is_simulated=False)
+    if c['counts_prior']:
+        data.prior_universal = {'counts': g['gibbs_counts_global'] - 1.}
+        if c['inheritance']:
+            data.prior_inheritance = {'counts': g['gibbs_counts_fam'] - 1.}
+    return data
+
+
+def case_model_config(c, sample_source=True, min_m=3, max_m=30):
+    pc = {k: dict(v) for k, v in c['prior_cfg'].items()}
+    for k in ('universal', 'inheritance'):
+        if pc[k]['type'] == 'counts':
+            pc[k].update(scale_counts=10., file='golden', files={})
+    return {'N_AREAS': c['Z'], 'MIN_M': min_m, 'MAX_M': max_m, 'INHERITANCE': c['inheritance'],
+            'SAMPLE_SOURCE': sample_source, 'PRIOR': pc}

@@ -1,0 +1,102 @@
+"""GPU: `ZoneMCMC` / `ZoneMCMCWarmup` / `MCMC` with the reference's call sequence (mcmc_setup.py:96-118, 174-185):
+warm-up -> best sample -> sampling -> statistics -> contribution_per_area -> match / rank -> result files."""
+import logging
+import pathlib
+from types import SimpleNamespace
+
+import numpy as np
+import pytest
+
+from helpers import PRECISION, case_data, case_model_config, load_case, load_run
+
+pytestmark = pytest.mark.gpu
+
+STAT_KEYS = ['sample_id', 'sample_likelihood', 'sample_prior', 'sample_zones', 'sample_weights', 'sample_p_global',
+             'sample_p_zones', 'sample_p_families', 'last_sample', 'acceptance_ratio', 'accepted_steps', 'n_swaps',
+             'accepted_swaps', 'swap_ratio', 'accept_operator', 'reject_operator', 'sampling_time', 'time_per_sample']
+
+
+def _mcmc_config(n_steps, n_samples, n_chains=1, mc3=None):
+    c = {'N_STEPS': n_steps, 'N_SAMPLES': n_samples, 'N_RUNS': 1, 'P_GROW_CONNECTED': 0.85,
+         'PROPOSAL_PRECISION': dict(PRECISION), 'M_INITIAL': 5, 'N_CHAINS': n_chains, 'SEED': 123,
+         'STEPS': {'area': 0.05, 'weights': 0.4, 'universal': 0.05, 'contact': 0.4, 'inheritance': 0.1, 'source': 0.0},
+         'WARM_UP': {'N_WARM_UP_STEPS': 300, 'N_WARM_UP_CHAINS': 6}}
+    if mc3:
+        c['MC3'] = mc3
+    return c
+
+
+@pytest.mark.parametrize('sample_source', [True, False])
+def test_zone_mcmc_generate_samples(sample_source, built_lib):
+    from contact_zones_b200.model import Model
+    from contact_zones_b200.sampling import Sample, ZoneMCMC, ZoneMCMCWarmup
+    c = load_case('C_samerica_like')
+    data = case_data(c)
+    model = Model(data, case_model_config(c, sample_source=sample_source))
+    kind = 'gibbs_sample' if sample_source else 'alter'
+    ops = {'shrink_zone': 0.02, 'grow_zone': 0.02, 'swap_zone': 0.01, 'gibbsish_sample_zones': 0.0,
+           f'{kind}_weights': 0.4, f'{kind}_p_global': 0.05, f'{kind}_p_zones': 0.4, f'{kind}_p_families': 0.1}
+    kw = dict(data=data, model=model, operators=ops, var_proposal=PRECISION, p_grow_connected=0.85, initial_size=5,
+              seed=7)
+    warm = ZoneMCMCWarmup(n_chains=6, **kw)
+    assert len(warm.max_size) == 6 and warm.max_size[0] <= warm.max_size[-1] <= model.max_size
+    assert set(warm.p_grow_connected) <= {0.95, 0.85}
+    best = warm.generate_samples(n_steps=0, n_samples=0, warm_up=True, warm_up_steps=300)
+    warm.close()
+    assert isinstance(best, Sample) and best.zones.shape == (c['Z'], c['N'])
+    assert (best.zones.sum(axis=0) <= 1).all() and (best.zones.sum(axis=1) >= model.min_size).all()
+    assert (best.source is not None) == sample_source
+
+    n_steps, n_samples = 2000, 20
+    smp = ZoneMCMC(n_chains=4, initial_sample=best, mc3=True, swap_period=100, chain_swaps=2, **kw)
+    assert smp.generate_samples(n_steps, n_samples) is None
+    st = smp.statistics
+    for k in STAT_KEYS:
+        assert k in st, k
+    assert st['sample_id'] == list(range(n_samples))
+    assert len(st['sample_zones']) == n_samples and st['sample_zones'][0].shape == (c['Z'], c['N'])
+    assert st['sample_weights'][0].shape == (c['F'], c['C']) and st['sample_p_global'][0].shape == (1, c['F'], c['S'])
+    assert st['n_swaps'] == (n_steps // 100) * 2 and 0 <= st['accepted_swaps'] <= st['n_swaps']
+    total = sum(st['accept_operator'].values()) + sum(st['reject_operator'].values())
+    assert total == n_steps * 4                                       # every chain, every step (quirk Q4)
+    assert st['accepted_steps'] == sum(st['accept_operator'].values())
+    assert isinstance(st['last_sample'], Sample)
+    # the logged ll / prior are the model's values of the logged states (1e-9)
+    for i in (0, n_samples - 1):
+        s = Sample(st['sample_zones'][i], st['sample_weights'][i], st['sample_p_global'][i], st['sample_p_zones'][i],
+                   st['sample_p_families'][i])
+        assert abs(model.prior(s) - st['sample_prior'][i]) <= 1e-9 * max(1., abs(st['sample_prior'][i]))
+        if not sample_source:
+            assert abs(model.likelihood(s) - st['sample_likelihood'][i]) <= 1e-9 * abs(st['sample_likelihood'][i])
+    last = st['last_sample']
+    c0 = smp.chain_idx[0]
+    assert abs(model.likelihood(last) - smp._ll[c0]) <= 1e-9 * abs(smp._ll[c0])
+    smp.close()
+
+
+def test_mcmc_facade_writes_reference_files(built_lib, tmp_path):
+    from contact_zones_b200.mcmc_setup import MCMC
+    from contact_zones_b200.results import parse_area_columns
+    c = load_case('B_balkan_like')
+    data = case_data(c)
+    cfg = {'model': case_model_config(c), 'mcmc': _mcmc_config(1000, 10), 'results': {'FILE_INFO': 'n'}}
+    exp = SimpleNamespace(config=cfg, path_results=pathlib.Path(tmp_path), logger=logging.getLogger('t'))
+    mc = MCMC(data, exp)
+    assert abs(sum(mc.ops.values()) - 1.0) < 1e-12 and mc.ops['gibbsish_sample_zones'] == 0.0
+    mc.warm_up()
+    mc.sample()
+    assert len(mc.samples['sample_lh_single_zones']) == 10 and len(mc.samples['sample_lh_single_zones'][0]) == c['Z']
+    mc.save_samples(run=1)
+    mc.log_statistics()
+    fi = f"n{c['Z']}"
+    stats = (tmp_path / fi / f'stats_{fi}_1.txt').read_text().splitlines()
+    areas = (tmp_path / fi / f'areas_{fi}_1.txt').read_text().splitlines()
+    hdr = stats[0].split('\t')
+    assert hdr[:4] == ['Sample', 'posterior', 'likelihood', 'prior'] and hdr[4] == 'size_a0'
+    assert 'w_universal_f0' in hdr and 'alpha_f0_s0' in hdr and 'gamma_a1_f0_s0' in hdr and 'beta_fam0_f0_s0' in hdr
+    assert hdr[-3:] == [f"lh_a{c['Z']}", f"prior_a{c['Z']}", f"post_a{c['Z']}"]
+    assert len(stats) == 11 and len(areas) == 10
+    row = dict(zip(hdr, stats[1].split('\t')))
+    assert abs(float(row['posterior']) - float(row['likelihood']) - float(row['prior'])) < 1e-6
+    z = parse_area_columns(areas[0])
+    assert z.shape == (c['Z'], c['N']) and int(row['size_a0']) == z[0].sum()
