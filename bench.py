@@ -187,14 +187,14 @@ def measured_peak():
         return 6650.0, 'fallback'
 
 
-def likelihood_leg(torch, device, n_launch=60):
+def likelihood_leg(torch, device, n_launch=60, sizes=(500, 2000, 20000)):
     """K1 on configs[4] (256 chains x N x 100 x 4, Z=4 zones of 25, C=2, no source): GB/s per SURVEY.md 8(d)."""
     from contact_zones_b200 import synthetic
     from contact_zones_b200.engine import Engine
     out = []
     stream = torch.cuda.current_stream().cuda_stream
     assert stream != 0, 'the legacy default stream cannot be handed to the C ABI (0 selects the context\'s own stream)'
-    for N in (500, 2000, 20000):
+    for N in sizes:
         e = E_SHAPE
         data = synthetic.make_data(N, e['F'], e['S'], n_families=0, seed=2, with_dist=False)
         eng = Engine(state_idx(data), data.states, None, data.network['adj_mat'], None, n_zones=e['Z'],

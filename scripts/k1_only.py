@@ -10,5 +10,6 @@ import bench  # noqa: E402
 torch.cuda.set_device(0)
 torch.cuda.set_stream(torch.cuda.Stream())
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 20
-for r in bench.likelihood_leg(torch, 0, n_launch=n):
+sizes = tuple(int(v) for v in sys.argv[2].split(',')) if len(sys.argv) > 2 else (500, 2000, 20000)
+for r in bench.likelihood_leg(torch, 0, n_launch=n, sizes=sizes):
     print(r)
