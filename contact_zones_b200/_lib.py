@@ -30,7 +30,7 @@ SYMBOLS = [
     'sb_upload_data', 'sb_set_priors', 'sb_set_state', 'sb_get_state', 'sb_copy_state',
     'sb_eval', 'sb_eval_likelihood_async', 'sb_read_ll', 'sb_eval_components', 'sb_source_posterior',
     'sb_counts', 'sb_move_log_q', 'sb_set_operators', 'sb_run', 'sb_read_chain_scalars', 'sb_read_op_stats',
-    'sb_step_counter', 'sb_kernel_launches',
+    'sb_step_counter', 'sb_kernel_launches', 'sb_rng_sample',
 ]
 
 
@@ -94,6 +94,7 @@ def load():
         'sb_read_op_stats': ([vp, vp, vp], i32),
         'sb_step_counter': ([vp, C.POINTER(i64)], i32),
         'sb_kernel_launches': ([vp, C.POINTER(i64)], i32),
+        'sb_rng_sample': ([vp, i32, dbl, C.c_uint64, i32, vp], i32),
     }
     for name, (argtypes, restype) in sig.items():
         fn = getattr(lib, name)

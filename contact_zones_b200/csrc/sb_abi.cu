@@ -695,7 +695,7 @@ static int ensure_step_scratch(sb_ctx* ctx) {
     StepParams& sp = ctx->sp;
     const DevData& d = ctx->d;
     if (!sp.scratch) {
-        sp.s_scratch = (size_t)d.F * d.S;
+        sp.s_scratch = (size_t)d.F * (d.S > 12 ? d.S : 12);     // Gamma draws [F][S] or staged w~ rows [F][12]
         DA(sp.scratch, (size_t)ctx->dims.n_chains * sp.s_scratch);
         sp.s_tmp = (size_t)d.N;
         DA(sp.tmp_members, (size_t)ctx->dims.n_chains * sp.s_tmp);
@@ -845,6 +845,18 @@ int sb_move_log_q(sb_ctx* ctx, int chain, int kind, int zone, int site_new, int 
     if (r != SB_OK) return r;
     *log_q = h[0]; *log_q_back = h[1];
     return SB_OK;
+}
+
+int sb_rng_sample(sb_ctx* ctx, int kind, double alpha, uint64_t seed, int n, double* out) {
+    if (!ctx || !out || n < 1 || (kind != 0 && kind != 1) || (kind == 1 && !(alpha > 0.0))) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    double* dout;
+    CK(cudaMalloc((void**)&dout, (size_t)n * sizeof(double)));
+    rng_sample_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(kind, alpha, (uint32_t)seed, (uint32_t)(seed >> 32), n, dout);
+    ++ctx->launches;
+    const int r = d2h(ctx, out, dout, (size_t)n);
+    cudaFree(dout);
+    return r;
 }
 
 }  // extern "C"

@@ -66,36 +66,47 @@ __device__ __forceinline__ int rng_int(RngKey key, uint64_t step, uint32_t purpo
 }
 
 // Gamma(alpha, 1), Marsaglia & Tsang (2000).  alpha < 1 uses Gamma(alpha+1) * U^(1/alpha).
-// Each attempt consumes one Philox block (normal by Box-Muller from u0,u1 of block 2a; accept test from
-// block 2a+1).
+// One Philox block per attempt: words 0-1 -> 53-bit radius uniform, word 2 -> Box-Muller angle, word 3 -> accept
+// uniform.  The candidate normal x is evaluated with fp32 transcendentals (logf / sqrtf / cospif: relative error
+// ~1e-7 on x, i.e. a 1e-7 perturbation of the proposal density -- five orders below the Monte-Carlo error of any run)
+// and then treated as an exact fp64 number, so everything downstream (v, the accept test, the variate) is fp64.
+// The log-form accept test is decided in fp32 when its margin is clear and in fp64 otherwise.
 __device__ double rng_gamma(RngKey key, uint64_t step, uint32_t purpose, uint32_t index, double alpha) {
     double boost = 1.0;
-    uint32_t sub = 0;
     if (alpha < 1.0) {
         const Draw b = rng_draw(key, step, purpose, 0xfffffeu, index);
         boost = pow(b.u0, 1.0 / alpha);
         alpha += 1.0;
     }
     const double d = alpha - 1.0 / 3.0;
-    const double c = 1.0 / sqrt(9.0 * d);
-    for (int attempt = 0; attempt < 64; ++attempt) {
-        const Draw n = rng_draw(key, step, purpose, sub++, index);
-        const Draw a = rng_draw(key, step, purpose, sub++, index);
-        double sn, cs;
-        sincospi(2.0 * n.u1, &sn, &cs);
-        const double r = sqrt(-2.0 * log(n.u0));
-        // both Box-Muller normals are tried before a new block is drawn
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const double x = r * (h == 0 ? cs : sn);
-            const double u = h == 0 ? a.u0 : a.u1;
-            double v = 1.0 + c * x;
-            if (v <= 0.0) continue;
-            v = v * v * v;
-            const double x2 = x * x;
-            if (u < 1.0 - 0.0331 * x2 * x2) return boost * d * v;
-            if (log(u) < 0.5 * x2 + d * (1.0 - v + log(v))) return boost * d * v;
-        }
+    const double c = rsqrt(9.0 * d);
+    for (uint32_t attempt = 0; attempt < 128u; ++attempt) {
+        uint32_t o[4];
+        philox4x32((uint32_t)step, (uint32_t)(step >> 32), (purpose << 24) | attempt, index, key.k0, key.k1, o);
+        const float u0 = (float)u53(o[0], o[1]);                               // in (0, 1]
+        const float r = sqrtf(-2.0f * logf(u0));
+        const double x = (double)(r * cospif(((float)(o[2] >> 8) + 0.5f) * (2.0f / 16777216.0f)));
+        const double u = ((double)o[3] + 0.5) * (1.0 / 4294967296.0);
+        double v = 1.0 + c * x;
+        if (v <= 0.0) continue;
+        v = v * v * v;
+        const double x2 = x * x;
+        if (u < 1.0 - 0.0331 * x2 * x2) return boost * d * v;                   // squeeze
+        const float lu = logf((float)u), lv = logf((float)v);
+        const float rhs = (float)(0.5 * x2) + (float)d * ((float)(1.0 - v) + lv);
+        const float margin = 2e-6f * (fabsf(lu) + (float)(0.5 * x2) + (float)d * (fabsf((float)(1.0 - v)) + fabsf(lv))) + 1e-6f;
+        bool acc;
+        if (fabsf(lu - rhs) > margin) acc = lu < rhs;
+        else acc = log(u) < 0.5 * x2 + d * (1.0 - v + log(v));
+        if (acc) return boost * d * v;
     }
     return boost * d;   // unreachable in practice (acceptance > 95 % per attempt)
+}
+
+// debug / parity surface of K6 (sb_rng_sample): n independent draws, kind 0 = uniform(0,1), 1 = Gamma(alpha, 1)
+__global__ void rng_sample_kernel(int kind, double alpha, uint32_t seed_lo, uint32_t seed_hi, int n, double* out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const RngKey key = {seed_lo, seed_hi};
+    out[i] = kind == 0 ? rng_uniform(key, 0, RP_GAMMA, (uint32_t)i) : rng_gamma(key, 0, RP_GAMMA, (uint32_t)i, alpha);
 }

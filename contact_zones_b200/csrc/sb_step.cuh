@@ -384,12 +384,10 @@ __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, u
                                  StepShared& sh) {
     // fixed = choice(['inheritance', 'contact'])  (:249)
     const bool fixed_inheritance = rng_uniform(key, step, RP_FIXED, 0) < 0.5;
-    double dll = 0.0;
+    // phase A (one thread per feature): draw the new weights, stage their normalisations in the scratch
     for (int f = threadIdx.x; f < d.F; f += blockDim.x) {
         const int* cs = k.cs + (size_t)f * 12;
         double* w = k.w + (size_t)f * 3;
-        double* wn = k.wn + (size_t)f * 12;
-        const double old_term = weight_ll_row(cs, wn);
         if (d.C == 2) {
             // counts over sites with a zone (:239-243): cfg = 1
             const double g0 = rng_gamma(key, step, RP_BETA_A, f, 1.0 + (double)cs[3 + 0]);
@@ -410,8 +408,16 @@ __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, u
             const double s = (v[0] + v[1]) + v[2];          // normalize(w_new) :271, 298
             w[0] = v[0] / s; w[1] = v[1] / s; w[2] = v[2] / s;
         }
-        wnorm_row(w, wn, d.C);
-        dll += weight_ll_row(cs, wn) - old_term;
+        wnorm_row(w, k.scratch + (size_t)f * 12, d.C);
+    }
+    __syncthreads();
+    // phase B (one thread per table entry): complete-data likelihood change  sum cnt_src * log(w~_new / w~_old)
+    double dll = 0.0;
+    for (int i = threadIdx.x; i < d.F * 12; i += blockDim.x) {
+        const double nw = k.scratch[i], old = k.wn[i];
+        const int c = k.cs[i];
+        if (c > 0 && nw != old) dll += (double)c * log(nw / old);
+        k.wn[i] = nw;
     }
     ll += block_sum(dll, sh.red);
 }
@@ -438,23 +444,24 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
         k.scratch[i] = g;
     }
     __syncthreads();
-    // phase 2: normalise, write, accumulate the likelihood / prior deltas (one thread per feature)
+    // phase 2: normalise, write, accumulate the likelihood delta -- one thread per (feature, state); the S threads of a
+    // row each form the row total in the same order, so they agree bit for bit
     double dll = 0.0, dpr = 0.0;
-    for (int f = threadIdx.x; f < d.F; f += blockDim.x) {
+    for (int i = threadIdx.x; i < FS; i += blockDim.x) {
+        const int f = i / S, s = i - f * S;
         const double* g = k.scratch + (size_t)f * S;
-        if (g[0] < 0.0) continue;
+        if (g[0] < 0.0 || !(d.app_mask[f] >> s & 1u)) continue;
         double tot = 0.0;
-        for (int s = 0; s < S; ++s) tot += g[s];
-        double t = 0.0;
-        for (int s = 0; s < S; ++s) {
-            if (!(d.app_mask[f] >> s & 1u)) continue;
-            const double pn = g[s] / tot;
-            const int c = cnt[(size_t)f * S + s];
-            if (c > 0) t += (double)c * (log(pn) - log(p[(size_t)f * S + s]));
-            p[(size_t)f * S + s] = pn;
-        }
-        dll += t;
-        if (alpha) {
+        for (int t = 0; t < S; ++t) tot += g[t];
+        const double pn = g[s] / tot;
+        const int c = cnt[i];
+        if (c > 0) dll += (double)c * log(pn / p[i]);
+        p[i] = pn;
+    }
+    if (alpha) {
+        __syncthreads();
+        for (int f = threadIdx.x; f < d.F; f += blockDim.x) {
+            if (k.scratch[(size_t)f * S] < 0.0) continue;
             const double v = dirichlet_row(p + (size_t)f * S, alpha + (size_t)f * S, lnorm[f], d.app_mask[f], S);
             dpr += v - pcache[f];
             pcache[f] = v;

@@ -200,6 +200,13 @@ class Engine:
                                            int(site_removed), float(p_grow_connected), C.byref(lq), C.byref(lqb)))
         return lq.value, lqb.value
 
+    def rng_sample(self, kind, n, alpha=1.0, seed=0):
+        """n draws of the device generator: kind 'uniform' or 'gamma' (K6 parity surface)."""
+        out = np.zeros(int(n))
+        self._check(self.lib.sb_rng_sample(self._ctx, {'uniform': 0, 'gamma': 1}[kind], float(alpha), int(seed), int(n),
+                                           ptr(out)))
+        return out
+
     # -- sampler ----------------------------------------------------------------------------------
     def set_operators(self, operators, precision, min_size, max_size, p_grow_connected, seed=0,
                       gibbs_feature_fraction=0.4):

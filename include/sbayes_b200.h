@@ -164,6 +164,11 @@ int sb_read_op_stats(sb_ctx* ctx, int64_t* accepted, int64_t* rejected);        
 int sb_step_counter(sb_ctx* ctx, int64_t* steps_done);                          /* per context      */
 int sb_kernel_launches(sb_ctx* ctx, int64_t* launches);                         /* launches issued so far */
 
+/* ---- K6 parity surface: n independent draws of the device generator (Philox4x32-10 + Marsaglia-Tsang), which
+ *      replaces np.random.dirichlet / scipy.stats.beta.rvs (zone_sampling.py:243,262-265,351,373,401,560).
+ *      kind 0 = uniform(0,1), 1 = Gamma(alpha, 1). */
+int sb_rng_sample(sb_ctx* ctx, int kind, double alpha, uint64_t seed, int n, double* out);
+
 #ifdef __cplusplus
 }
 #endif
