@@ -686,9 +686,24 @@ int sb_counts(sb_ctx* ctx, int chain, int recount, int32_t* cnt_glob, int32_t* c
 // ---------------------------------------------------------------------------------------------
 // sampler
 // ---------------------------------------------------------------------------------------------
-static size_t step_smem_bytes(const StepParams& sp) {
+static size_t step_smem_base(const StepParams& sp) {
     const size_t words = 2 * (size_t)sp.nwords + (sp.nwords & 1);
-    return words * sizeof(unsigned) + (size_t)sp.prim_cap * 9 + 16;
+    return (words * sizeof(unsigned) + (size_t)sp.prim_cap * 9 + 16 + 15) & ~(size_t)15;
+}
+// Shared work area of the step kernel (one CTA per SM, so up to ~200 KB): the Gibbs scratch and the count tables of
+// the source sweep are used at different times and overlay each other; whatever does not fit stays in global memory.
+static size_t step_smem_bytes(const DevData& d, StepParams& sp) {
+    const size_t base = step_smem_base(sp);
+    const size_t scratch = (size_t)d.F * (d.S > 12 ? d.S : 12) * sizeof(double);
+    const size_t counts = ((size_t)16 * d.S * (1 + d.Z + d.Fam) + 192) * sizeof(int);
+    const size_t room = 160 * 1024 > base ? 160 * 1024 - base : 0;
+    sp.work_off = (int)base;
+    sp.work_scratch = scratch <= room;
+    sp.work_counts = d.sample_source && counts <= room;
+    size_t work = 0;
+    if (sp.work_scratch) work = scratch;
+    if (sp.work_counts && counts > work) work = counts;
+    return base + work;
 }
 
 static int ensure_step_scratch(sb_ctx* ctx) {
@@ -763,7 +778,7 @@ int sb_set_operators(sb_ctx* ctx, const sb_operator_cfg* cfg, const double* p_gr
     H2D(ctx->d_maxsize, max_size, nc);
     sp.p_grow = ctx->d_pgrow; sp.max_size = ctx->d_maxsize;
     sp.prim_cap = d.geo_type == SB_GEO_COST_BASED ? cap : 0;
-    ctx->step_smem = step_smem_bytes(sp);
+    ctx->step_smem = step_smem_bytes(d, sp);
     if (ctx->step_smem > 200 * 1024) FAIL(SB_E_ARG, "step kernel scratch exceeds shared memory (N or MAX_M too large)");
     if (ctx->step_smem > 48 * 1024) {
         CK(cudaFuncSetAttribute(mcmc_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->step_smem));
@@ -831,7 +846,7 @@ int sb_move_log_q(sb_ctx* ctx, int chain, int kind, int zone, int site_new, int 
     if (kind != SB_OP_GROW_ZONE && (site_removed < 0 || site_removed >= d.N)) FAIL(SB_E_ARG, "site_removed out of range");
     r = ensure_step_scratch(ctx);
     if (r != SB_OK) return r;
-    const size_t smem = step_smem_bytes(ctx->sp);
+    const size_t smem = step_smem_base(ctx->sp);
     if (smem > 48 * 1024)
         CK(cudaFuncSetAttribute(move_log_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     double* dout;

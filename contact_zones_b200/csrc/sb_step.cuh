@@ -29,6 +29,9 @@ struct StepParams {
     const int* max_size;      // [chains]
     int nwords;               // words of one site bitmap
     int prim_cap;             // member capacity of the Prim scratch
+    int work_off;             // byte offset of the shared work area in the dynamic smem (16 B aligned)
+    int work_scratch;         // != 0: the Gibbs scratch ([F][max(S,12)] doubles) lives in the work area
+    int work_counts;          // != 0: resample_all_sources keeps per-feature-block count tables in the work area
     double* scratch;          // [chains][F*S]   Gamma draws of the Gibbs operators
     size_t s_scratch;
     int* tmp_members;         // [chains][N]     candidate member list for the geo prior
@@ -121,6 +124,7 @@ struct Chain {
     int* cg; int* cz; int* cf; int* cs;
     double* ppg; double* ppf;
     double* scratch; int* tmp;
+    int* cnt_tab;       // shared-memory count tables of resample_all_sources_blocked, or null
 };
 __device__ __forceinline__ Chain chain_view(const ChainArrays& st, const StepParams& sp, int c) {
     Chain k;
@@ -133,6 +137,7 @@ __device__ __forceinline__ Chain chain_view(const ChainArrays& st, const StepPar
     k.cf = st.cnt_fam + c * st.s_cnt_fam; k.cs = st.cnt_src + c * st.s_cnt_src;
     k.ppg = st.prior_pg + c * st.s_prior_pg; k.ppf = st.prior_pf + c * st.s_prior_pf;
     k.scratch = sp.scratch + c * sp.s_scratch; k.tmp = sp.tmp_members + c * sp.s_tmp;
+    k.cnt_tab = nullptr;
     return k;
 }
 
@@ -225,6 +230,103 @@ __device__ double resample_all_sources(const DevData& d, const Chain& k, RngKey 
     }
     const double v = block_sum(lp_value(acc), red);
     return v;
+}
+
+// Same operator with shared-memory count tables: features are processed in blocks of 16 (one 16-byte vector of x per
+// site); the counters of the block's features ([16][S] global, [16][12] source, [Z][16][S] zone, [Fam][16][S] family)
+// live in shared memory, are filled with shared atomics and flushed with plain coalesced stores -- no global atomics,
+// no zeroing pass.  One Philox block serves four cells (32-bit uniforms).
+__device__ double resample_all_sources_blocked(const DevData& d, const Chain& k, RngKey key, uint64_t step, double* red,
+                                               int* tab) {
+    const int S = d.S, F = d.F, C = d.C, N = d.N;
+    const size_t FS = (size_t)F * S;
+    const int bS = 16 * S;
+    int* tcg = tab;                     // [16][S]
+    int* tcs = tcg + bS;                // [16][12]
+    int* tcz = tcs + 192;               // [Z][16][S]
+    int* tcf = tcz + d.Z * bS;          // [Fam][16][S]
+    const int T = bS * (1 + d.Z + d.Fam) + 192;
+    const int nb = d.ldx >> 4;
+    for (int i = threadIdx.x; i < T; i += blockDim.x) tab[i] = 0;
+    __syncthreads();
+    LogProd acc;
+    lp_init(acc);
+    for (int fb = 0; fb < nb; ++fb) {
+        const int f0 = fb << 4;
+        for (int n = threadIdx.x; n < N; n += blockDim.x) {
+            const uint4 xv = *reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + f0);
+            const int zid = k.zone_id[n];
+            const int fam = d.inheritance ? d.fam_id[n] : -1;
+            const int cfg = (zid >= 0 ? 1 : 0) + (fam >= 0 ? 2 : 0);
+            const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+            uint32_t sw[4] = {0u, 0u, 0u, 0u};
+            const double* pzr = k.pz + (size_t)(zid >= 0 ? zid : 0) * FS;
+            const double* pfr = k.pf + (size_t)(fam >= 0 ? fam : 0) * FS;
+            int* czr = tcz + (zid >= 0 ? zid : 0) * bS;
+            int* cfr = tcf + (fam >= 0 ? fam : 0) * bS;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                uint32_t o[4];
+                philox4x32((uint32_t)step, (uint32_t)(step >> 32), ((uint32_t)RP_SOURCE << 24) | (uint32_t)q,
+                           (uint32_t)(n * nb + fb), key.k0, key.k1, o);
+#pragma unroll
+                for (int h = 0; h < 4; ++h) {
+                    const int xs = (xw[q] >> (h * 8)) & 0xff;
+                    if (xs == SB_PAD) continue;
+                    const int j = q * 4 + h;
+                    const int f = f0 + j;
+                    const double* w = k.wn + (size_t)f * 12 + cfg * 3;
+                    double t0 = w[0], t1 = zid >= 0 ? w[1] : 0.0, t2 = (C == 3 && fam >= 0) ? w[2] : 0.0;
+                    if (xs != SB_NA) {
+                        const size_t oo = (size_t)f * S + xs;
+                        t0 *= k.pg[oo];
+                        if (zid >= 0) t1 *= pzr[oo];
+                        if (C == 3 && fam >= 0) t2 *= pfr[oo];
+                    }
+                    const double tot = (t0 + t1) + t2;
+                    const double ut = (((double)o[h] + 0.5) * (1.0 / 4294967296.0)) * tot;
+                    // sample_categorical (preprocessing.py:338-341): first component whose cumulative mass exceeds u
+                    int sc = 0;
+                    if (ut >= t0) sc = (ut < t0 + t1) ? 1 : ((C == 3 && ut < tot) ? 2 : 0);
+                    lp_mul(acc, sc == 0 ? t0 : (sc == 1 ? t1 : t2));
+                    sw[q] |= (uint32_t)sc << (h * 8);
+                    atomicAdd(tcs + j * 12 + cfg * 3 + sc, 1);
+                    if (xs != SB_NA) {
+                        int* t = sc == 0 ? tcg : (sc == 1 ? czr : cfr);
+                        atomicAdd(t + j * S + xs, 1);
+                    }
+                }
+            }
+            *reinterpret_cast<uint4*>(k.src + (size_t)n * d.ldx + f0) = make_uint4(sw[0], sw[1], sw[2], sw[3]);
+        }
+        __syncthreads();
+        // flush + clear: the block's counters are contiguous runs of the global tables
+        const int nf = min(16, F - f0);
+        for (int i = threadIdx.x; i < T; i += blockDim.x) {
+            const int v = tab[i];
+            tab[i] = 0;
+            if (i < bS) {
+                if (i < nf * S) k.cg[(size_t)f0 * S + i] = v;
+            } else if (i < bS + 192) {
+                const int r = i - bS;
+                if (r < nf * 12) k.cs[(size_t)f0 * 12 + r] = v;
+            } else {
+                const int r = i - bS - 192;
+                const int t = r / bS, e = r - t * bS;
+                if (e < nf * S) {
+                    if (t < d.Z) k.cz[(size_t)t * FS + (size_t)f0 * S + e] = v;
+                    else k.cf[(size_t)(t - d.Z) * FS + (size_t)f0 * S + e] = v;
+                }
+            }
+        }
+        __syncthreads();
+    }
+    return block_sum(lp_value(acc), red);
+}
+
+__device__ __forceinline__ double resample_sources(const DevData& d, const Chain& k, RngKey key, uint64_t step, double* red) {
+    return k.cnt_tab ? resample_all_sources_blocked(d, k, key, step, red, k.cnt_tab)
+                     : resample_all_sources(d, k, key, step, red);
 }
 
 // ---- shared scratch of the step kernel -----------------------------------------------------------
@@ -362,7 +464,7 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
     __syncthreads();
     prior += dprior;
     geo = geo_new;
-    if (d.sample_source) ll = resample_all_sources(d, k, key, step, sh.red);      // :859-862 (on accept only)
+    if (d.sample_source) ll = resample_sources(d, k, key, step, sh.red);          // :859-862 (on accept only)
     else ll += dll;
     return true;
 }
@@ -636,7 +738,10 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
     double* prim_key = reinterpret_cast<double*>(freeb + sp.nwords + (sp.nwords & 1));
     unsigned char* prim_tree = reinterpret_cast<unsigned char*>(prim_key + sp.prim_cap);
 
-    const Chain k = chain_view(st, sp, chain);
+    Chain kv = chain_view(st, sp, chain);
+    if (sp.work_scratch) kv.scratch = reinterpret_cast<double*>(step_smem + sp.work_off);
+    if (sp.work_counts) kv.cnt_tab = reinterpret_cast<int*>(step_smem + sp.work_off);
+    const Chain& k = kv;
     const unsigned gchain = (unsigned)(sp.chain_offset + chain);
     const RngKey key = {sp.seed_lo ^ (gchain * 0x9E3779B9u), sp.seed_hi ^ gchain};
     double ll = st.ll[chain], prior = st.prior[chain], geo = st.geo[chain];
@@ -659,7 +764,7 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
                                         prim_tree, sh);
                 break;
             case SB_OP_GIBBS_SOURCES:
-                ll = resample_all_sources(d, k, key, step, sh.red);
+                ll = resample_sources(d, k, key, step, sh.red);
                 break;
             case SB_OP_GIBBS_WEIGHTS:
                 op_gibbs_weights(d, k, key, step, ll, sh);
