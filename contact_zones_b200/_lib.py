@@ -8,7 +8,7 @@ import os
 
 import numpy as np
 
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'csrc', 'libsbayes_b200.so')
+LIB_PATH = os.environ.get('SBAYES_B200_LIB') or os.path.join(os.path.dirname(os.path.abspath(__file__)), 'csrc', 'libsbayes_b200.so')      # override: instrumented builds
 
 SB_N_OPS = 12
 SB_F_INHERITANCE, SB_F_SAMPLE_SOURCE, SB_F_WARMUP = 1, 2, 4

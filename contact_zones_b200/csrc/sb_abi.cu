@@ -170,6 +170,15 @@ int sb_create(sb_ctx** out, int device, const sb_dims* dims) {
     return SB_OK;
 }
 
+#ifdef SB_PROF
+extern "C" int sb_prof_read(unsigned long long* out, int reset) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, sb_prof, sizeof(unsigned long long) * 16);
+    if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(sb_prof, z, sizeof(z)); }
+    return 0;
+}
+#endif
+
 int sb_destroy(sb_ctx* ctx) {
     if (!ctx) return SB_OK;
     cudaSetDevice(ctx->device);
@@ -761,6 +770,8 @@ int sb_set_operators(sb_ctx* ctx, const sb_operator_cfg* cfg, const double* p_gr
     sp.prec_z = cfg->precision_p_zones; sp.prec_f = cfg->precision_p_families;
     sp.min_size = cfg->min_size;
     sp.frac = cfg->gibbs_feature_fraction;
+    sp.s_magic = (unsigned)((((uint64_t)1 << 32) + (uint64_t)d.S - 1) / (uint64_t)d.S);
+    if ((uint64_t)d.F * d.S >= ((uint64_t)1 << 27)) FAIL(SB_E_ARG, "F*S too large for the step kernel");
     sp.seed_lo = (uint32_t)cfg->seed; sp.seed_hi = (uint32_t)(cfg->seed >> 32);
     int r = ensure_step_scratch(ctx);
     if (r != SB_OK) return r;
@@ -863,7 +874,7 @@ int sb_move_log_q(sb_ctx* ctx, int chain, int kind, int zone, int site_new, int 
 }
 
 int sb_rng_sample(sb_ctx* ctx, int kind, double alpha, uint64_t seed, int n, double* out) {
-    if (!ctx || !out || n < 1 || (kind != 0 && kind != 1) || (kind == 1 && !(alpha > 0.0))) return SB_E_ARG;
+    if (!ctx || !out || n < 1 || kind < 0 || kind > 2 || (kind == 1 && !(alpha > 0.0))) return SB_E_ARG;
     CK(cudaSetDevice(ctx->device));
     double* dout;
     CK(cudaMalloc((void**)&dout, (size_t)n * sizeof(double)));

@@ -151,5 +151,38 @@ __device__ __forceinline__ int block_sum_i(int v, int* red) {
     return red[32];
 }
 
+// ---------------------------------------------------------------------------------------------
+// Table-driven natural logarithm for the step kernel.  fp64 throughput per SM is a quarter of the issue rate, and
+// libm's log() costs ~60 fp64 instructions; this one costs ~10.  x = 2^e * m, m in [1,2); the top 7 mantissa bits
+// pick c_k = 1 + (k + 1/2)/128 from a 128-entry table of (1/c_k rounded, -log of that rounded value), so
+// log x = e ln2 + log(c_k) + log1p(r),  r = m * (1/c_k) - 1,  |r| <= 2^-8, degree-7 Taylor (remainder < 1e-20).
+// Absolute error <= ~3e-16 + 1e-16 |log x| -- the sampler only sums these into log-likelihoods of magnitude >= 1,
+// where the 1e-9 relative parity bound leaves > 6 orders of head-room.  Non-positive, subnormal, inf and NaN inputs
+// go to log().
+// ---------------------------------------------------------------------------------------------
+#define SB_FLOG_N 128
+__device__ __forceinline__ void flog_init(double2* tab) {      // call by the whole CTA, then __syncthreads()
+    for (int k = threadIdx.x; k < SB_FLOG_N; k += blockDim.x) {
+        const double inv = 1.0 / (1.0 + ((double)k + 0.5) * (1.0 / SB_FLOG_N));
+        tab[k] = make_double2(inv, -log(inv));
+    }
+}
+__device__ __forceinline__ double flog(double x, const double2* __restrict__ tab) {
+    const int hi = __double2hiint(x);
+    if ((unsigned)(hi - 0x00100000) >= 0x7fe00000u) return log(x);
+    const int e = (hi >> 20) - 1023;
+    const double m = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(x));
+    const double2 t = tab[(hi >> 13) & (SB_FLOG_N - 1)];
+    const double r = fma(m, t.x, -1.0);
+    double p = fma(r, 1.0 / 7.0, -1.0 / 6.0);
+    p = fma(p, r, 0.2);
+    p = fma(p, r, -0.25);
+    p = fma(p, r, 1.0 / 3.0);
+    p = fma(p, r, -0.5);
+    const double l = fma(p * r, r, r);
+    const double ef = (double)e;
+    return fma(ef, 6.93147180369123816490e-01, fma(ef, 1.90821492927058770002e-10, t.y + l));   // ln2 = hi + lo
+}
+
 // xlogy semantics of scipy (dirichlet._logpdf): 0 * log(0) = 0
 __device__ __forceinline__ double xlogy_d(double a, double p) { return a == 0.0 ? 0.0 : a * log(p); }

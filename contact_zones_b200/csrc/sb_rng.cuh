@@ -66,11 +66,76 @@ __device__ __forceinline__ int rng_int(RngKey key, uint64_t step, uint32_t purpo
 }
 
 // Gamma(alpha, 1), Marsaglia & Tsang (2000).  alpha < 1 uses Gamma(alpha+1) * U^(1/alpha).
-// One Philox block per attempt: words 0-1 -> 53-bit radius uniform, word 2 -> Box-Muller angle, word 3 -> accept
-// uniform.  The candidate normal x is evaluated with fp32 transcendentals (logf / sqrtf / cospif: relative error
-// ~1e-7 on x, i.e. a 1e-7 perturbation of the proposal density -- five orders below the Monte-Carlo error of any run)
-// and then treated as an exact fp64 number, so everything downstream (v, the accept test, the variate) is fp64.
-// The log-form accept test is decided in fp32 when its margin is clear and in fp64 otherwise.
+// One Philox block per attempt: word 0 -> Box-Muller radius, word 1 -> angle, words 2-3 -> the accept uniforms of the
+// two normals, which are both tried before a new block is drawn (so a whole warp rarely needs a second attempt:
+// 1 - (1 - 0.05^2)^32 ~ 8 %).  The candidate normals are evaluated with fp32 transcendentals (logf / sqrtf /
+// sincospif: relative error ~1e-7 on x, i.e. a 1e-7 perturbation of the proposal density -- orders of magnitude below
+// the Monte-Carlo error of any run; the radius uniform has 32 bits, so |x| <= 6.8) and then treated as exact fp64
+// numbers: v, the accept test and the variate are fp64.  The log-form accept test is decided by a fast fp32 estimate
+// when its margin is clear and in fp64 otherwise.
+__device__ __forceinline__ bool mt_accept(double x, double u, double c, double d, double& out) {
+    // written without early exits so that two candidates can be interleaved by the compiler
+    const double v1 = 1.0 + c * x;
+    const double v = v1 * v1 * v1;
+    const double x2 = x * x;
+    out = d * v;
+    const bool pos = v1 > 0.0;
+    const bool squeeze = u < 1.0 - 0.0331 * x2 * x2;
+    const float hx = (float)(0.5 * x2), df = (float)d, omv = (float)(1.0 - v);
+    const float lu = __logf((float)u), lv = __logf(fabsf((float)v));
+    const float rhs = hx + df * (omv + lv);
+    // fp32 error budget: __logf is good to 2^-21 absolute near 1 and a few ulp elsewhere
+    const float margin = 4e-6f * (fabsf(lu) + hx + df * (fabsf(omv) + fabsf(lv))) + 2e-6f * df + 4e-6f;
+    const bool clear = fabsf(lu - rhs) > margin;
+    bool acc = squeeze || (clear && lu < rhs);
+    if (pos && !squeeze && !clear) acc = log(u) < 0.5 * x2 + d * (1.0 - v + log(v));
+    return pos && acc;
+}
+
+// Two independent Gamma draws in lock-step (same streams as two rng_gamma calls with alpha >= 1): the two dependency
+// chains are laid side by side in one instruction stream, which is what hides their latency -- the step kernel runs
+// one CTA of 16 warps per SM, far too few to hide a ~350-instruction dependent chain by warp switching alone.
+// valid_x = false skips that draw (result 0).
+struct MtCand { double x0, x1, u0, u1; };
+__device__ __forceinline__ MtCand mt_candidates(RngKey key, uint64_t step, uint32_t purpose, uint32_t attempt, uint32_t index) {
+    uint32_t o[4];
+    philox4x32((uint32_t)step, (uint32_t)(step >> 32), (purpose << 24) | attempt, index, key.k0, key.k1, o);
+    const float r = sqrtf(-2.0f * logf(((float)o[0] + 0.5f) * 2.3283064365386963e-10f));
+    float sn, cs;
+    sincospif(((float)(o[1] >> 8) + 0.5f) * (2.0f / 16777216.0f), &sn, &cs);
+    MtCand m;
+    m.x0 = (double)(r * cs); m.x1 = (double)(r * sn);
+    m.u0 = ((double)o[2] + 0.5) * (1.0 / 4294967296.0);
+    m.u1 = ((double)o[3] + 0.5) * (1.0 / 4294967296.0);
+    return m;
+}
+__device__ __forceinline__ double mt_scale(double alpha, double& d) {
+    d = alpha - 1.0 / 3.0;
+    const double nd = 9.0 * d;
+    const double c = (double)rsqrtf((float)nd);
+    return c * fma(-0.5 * nd, c * c, 1.5);
+}
+__device__ __forceinline__ void rng_gamma2(RngKey key, uint64_t step, uint32_t purpose_a, uint32_t index_a, double alpha_a,
+                                           bool valid_a, uint32_t purpose_b, uint32_t index_b, double alpha_b,
+                                           bool valid_b, double& ga, double& gb) {
+    double da, db;
+    const double ca = mt_scale(valid_a ? alpha_a : 1.0, da), cb = mt_scale(valid_b ? alpha_b : 1.0, db);
+    bool need_a = valid_a, need_b = valid_b;
+    ga = 0.0; gb = 0.0;
+    for (uint32_t attempt = 0; attempt < 64u && (need_a || need_b); ++attempt) {
+        const MtCand ma = mt_candidates(key, step, purpose_a, attempt, index_a);
+        const MtCand mb = mt_candidates(key, step, purpose_b, attempt, index_b);
+        double a0, a1, b0, b1;
+        const bool ka0 = mt_accept(ma.x0, ma.u0, ca, da, a0), kb0 = mt_accept(mb.x0, mb.u0, cb, db, b0);
+        const bool ka1 = mt_accept(ma.x1, ma.u1, ca, da, a1), kb1 = mt_accept(mb.x1, mb.u1, cb, db, b1);
+        if (need_a && (ka0 || ka1)) { ga = ka0 ? a0 : a1; need_a = false; }
+        if (need_b && (kb0 || kb1)) { gb = kb0 ? b0 : b1; need_b = false; }
+    }
+    if (need_a) ga = da;
+    if (need_b) gb = db;
+}
+
+// Single draw (same stream as rng_gamma2 for that (purpose, index)); alpha < 1 uses Gamma(alpha+1) * U^(1/alpha).
 __device__ double rng_gamma(RngKey key, uint64_t step, uint32_t purpose, uint32_t index, double alpha) {
     double boost = 1.0;
     if (alpha < 1.0) {
@@ -78,35 +143,27 @@ __device__ double rng_gamma(RngKey key, uint64_t step, uint32_t purpose, uint32_
         boost = pow(b.u0, 1.0 / alpha);
         alpha += 1.0;
     }
-    const double d = alpha - 1.0 / 3.0;
-    const double c = rsqrt(9.0 * d);
-    for (uint32_t attempt = 0; attempt < 128u; ++attempt) {
-        uint32_t o[4];
-        philox4x32((uint32_t)step, (uint32_t)(step >> 32), (purpose << 24) | attempt, index, key.k0, key.k1, o);
-        const float u0 = (float)u53(o[0], o[1]);                               // in (0, 1]
-        const float r = sqrtf(-2.0f * logf(u0));
-        const double x = (double)(r * cospif(((float)(o[2] >> 8) + 0.5f) * (2.0f / 16777216.0f)));
-        const double u = ((double)o[3] + 0.5) * (1.0 / 4294967296.0);
-        double v = 1.0 + c * x;
-        if (v <= 0.0) continue;
-        v = v * v * v;
-        const double x2 = x * x;
-        if (u < 1.0 - 0.0331 * x2 * x2) return boost * d * v;                   // squeeze
-        const float lu = logf((float)u), lv = logf((float)v);
-        const float rhs = (float)(0.5 * x2) + (float)d * ((float)(1.0 - v) + lv);
-        const float margin = 2e-6f * (fabsf(lu) + (float)(0.5 * x2) + (float)d * (fabsf((float)(1.0 - v)) + fabsf(lv))) + 1e-6f;
-        bool acc;
-        if (fabsf(lu - rhs) > margin) acc = lu < rhs;
-        else acc = log(u) < 0.5 * x2 + d * (1.0 - v + log(v));
-        if (acc) return boost * d * v;
+    double d;
+    const double c = mt_scale(alpha, d);
+    for (uint32_t attempt = 0; attempt < 64u; ++attempt) {
+        const MtCand m = mt_candidates(key, step, purpose, attempt, index);
+        double g;
+        if (mt_accept(m.x0, m.u0, c, d, g)) return boost * g;
+        if (mt_accept(m.x1, m.u1, c, d, g)) return boost * g;
     }
-    return boost * d;   // unreachable in practice (acceptance > 95 % per attempt)
+    return boost * d;   // unreachable in practice (acceptance > 95 % per candidate)
 }
 
-// debug / parity surface of K6 (sb_rng_sample): n independent draws, kind 0 = uniform(0,1), 1 = Gamma(alpha, 1)
+// debug / parity surface of K6 (sb_rng_sample): n independent draws, kind 0 = uniform(0,1), 1 = Gamma(alpha, 1),
+// 2 = flog((1 + u_i) * 2^(i % 121 - 60)) with u_i the kind-0 draw (accuracy check of the table-driven logarithm)
 __global__ void rng_sample_kernel(int kind, double alpha, uint32_t seed_lo, uint32_t seed_hi, int n, double* out) {
+    __shared__ double2 tab[SB_FLOG_N];
+    flog_init(tab);
+    __syncthreads();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const RngKey key = {seed_lo, seed_hi};
-    out[i] = kind == 0 ? rng_uniform(key, 0, RP_GAMMA, (uint32_t)i) : rng_gamma(key, 0, RP_GAMMA, (uint32_t)i, alpha);
+    if (kind == 1) { out[i] = rng_gamma(key, 0, RP_GAMMA, (uint32_t)i, alpha); return; }
+    const double u = rng_uniform(key, 0, RP_GAMMA, (uint32_t)i);
+    out[i] = kind == 0 ? u : flog(ldexp(1.0 + u, i % 121 - 60), tab);
 }

@@ -16,6 +16,16 @@
 
 #define STEP_THREADS 512
 
+// optional phase timing (build with -DSB_PROF): cycles of CTA 0 / thread 0 accumulated per marker
+#ifdef SB_PROF
+__device__ unsigned long long sb_prof[16];
+#define PROF_T(var) long long var = clock64()
+#define PROF_ADD(slot, a, b) do { if (threadIdx.x == 0 && blockIdx.x == 0) sb_prof[slot] += (unsigned long long)((b) - (a)); } while (0)
+#else
+#define PROF_T(var)
+#define PROF_ADD(slot, a, b)
+#endif
+
 struct StepParams {
     int n_ops;
     int op_ids[SB_N_OPS];
@@ -29,6 +39,7 @@ struct StepParams {
     const int* max_size;      // [chains]
     int nwords;               // words of one site bitmap
     int prim_cap;             // member capacity of the Prim scratch
+    unsigned s_magic;         // ceil(2^32 / S): i / S == __umulhi(i, s_magic) for i < 2^27
     int work_off;             // byte offset of the shared work area in the dynamic smem (16 B aligned)
     int work_scratch;         // != 0: the Gibbs scratch ([F][max(S,12)] doubles) lives in the work area
     int work_counts;          // != 0: resample_all_sources keeps per-feature-block count tables in the work area
@@ -125,6 +136,7 @@ struct Chain {
     double* ppg; double* ppf;
     double* scratch; int* tmp;
     int* cnt_tab;       // shared-memory count tables of resample_all_sources_blocked, or null
+    const double2* flt; // shared-memory table of flog()
 };
 __device__ __forceinline__ Chain chain_view(const ChainArrays& st, const StepParams& sp, int c) {
     Chain k;
@@ -138,6 +150,7 @@ __device__ __forceinline__ Chain chain_view(const ChainArrays& st, const StepPar
     k.ppg = st.prior_pg + c * st.s_prior_pg; k.ppf = st.prior_pf + c * st.s_prior_pf;
     k.scratch = sp.scratch + c * sp.s_scratch; k.tmp = sp.tmp_members + c * sp.s_tmp;
     k.cnt_tab = nullptr;
+    k.flt = nullptr;
     return k;
 }
 
@@ -163,7 +176,7 @@ __device__ double site_zone_delta(const DevData& d, const Chain& k, int site, in
         const int xs = d.x[(size_t)site * d.ldx + f];
         if (xs == SB_NA) continue;
         const double* wrow = k.wn + (size_t)f * 12;
-        acc += log(cell_mix(d, k, f, xs, zid_new, fam, wrow)) - log(cell_mix(d, k, f, xs, zid_old, fam, wrow));
+        acc += flog(cell_mix(d, k, f, xs, zid_new, fam, wrow) / cell_mix(d, k, f, xs, zid_old, fam, wrow), k.flt);
     }
     return block_sum(acc, red);
 }
@@ -442,8 +455,8 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
     if (d.warmup && d.sample_source) {
         accept = true;      // warm-up forces as_gibbs=True in gibbs_sample_sources => log_q = -inf => accept (:1293-1296)
     } else {
-        const double mh = dll - (log(q) - log(q_back)) + dprior;                  // mcmc_generative.py:345-349
-        accept = log(rng_uniform(key, step, RP_ACCEPT, 0)) < mh;                  // :318
+        const double mh = dll - flog(q / q_back, k.flt) + dprior;                 // mcmc_generative.py:345-349
+        accept = flog(rng_uniform(key, step, RP_ACCEPT, 0), k.flt) < mh;          // :318
     }
     if (!accept) return false;
 
@@ -486,40 +499,51 @@ __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, u
                                  StepShared& sh) {
     // fixed = choice(['inheritance', 'contact'])  (:249)
     const bool fixed_inheritance = rng_uniform(key, step, RP_FIXED, 0) < 0.5;
-    // phase A (one thread per feature): draw the new weights, stage their normalisations in the scratch
+    // phase A (one thread per feature): the two Gammas of the feature's Beta / Dirichlet draw in lock-step, then the
+    // new weight row, staged in the scratch ([0,3F))
+    const int a = (d.C == 2) ? 1 : (fixed_inheritance ? 1 : 2);   // cfg of the "only this component" sites; also column x
     for (int f = threadIdx.x; f < d.F; f += blockDim.x) {
         const int* cs = k.cs + (size_t)f * 12;
+        int c0, c1;
+        if (d.C == 2) { c0 = cs[3 + 0]; c1 = cs[3 + 1]; }                  // counts over sites with a zone (:239-243)
+        else { c0 = cs[a * 3 + a] + cs[9 + a];                             // c_x over has_zone / has_family sites
+               c1 = cs[a * 3 + 0] + cs[9 + 0]; }                           // c_univ            (:256-259, 283-286)
+        double g0, g1;
+        rng_gamma2(key, step, RP_BETA_A, (uint32_t)f, 1.0 + (double)c0, true, RP_BETA_B, (uint32_t)f, 1.0 + (double)c1,
+                   true, g0, g1);
         double* w = k.w + (size_t)f * 3;
+        double v[3] = {w[0], w[1], d.C == 3 ? w[2] : 0.0};
         if (d.C == 2) {
-            // counts over sites with a zone (:239-243): cfg = 1
-            const double g0 = rng_gamma(key, step, RP_BETA_A, f, 1.0 + (double)cs[3 + 0]);
-            const double g1 = rng_gamma(key, step, RP_BETA_B, f, 1.0 + (double)cs[3 + 1]);
-            const double s = g0 + g1;
-            w[0] = g0 / s; w[1] = g1 / s;
+            v[0] = g0; v[1] = g1;                           // Dir(1 + counts) = normalised Gammas
         } else {
-            // counts over has_zone sites (cfg 1,3) or has_family sites (cfg 2,3)   (:256-259, 283-286)
-            const int a = fixed_inheritance ? 1 : 2;       // cfg of the "only this component" sites; also the column x
-            const int c_univ = cs[a * 3 + 0] + cs[9 + 0];
-            const int c_x = cs[a * 3 + a] + cs[9 + a];
-            const double gx = rng_gamma(key, step, RP_BETA_A, f, 1.0 + (double)c_x);
-            const double gu = rng_gamma(key, step, RP_BETA_B, f, 1.0 + (double)c_univ);
-            const double ax = gx / (gx + gu);              // ~ Beta(1 + c_x, 1 + c_univ)      (:262-265, 289-292)
-            const double w0 = w[0];
-            double v[3] = {w0, w[1], w[2]};
-            v[a] = ax * w0 / (1.0 - ax);                    // :270, 297
-            const double s = (v[0] + v[1]) + v[2];          // normalize(w_new) :271, 298
-            w[0] = v[0] / s; w[1] = v[1] / s; w[2] = v[2] / s;
+            const double ax = g0 / (g0 + g1);               // ~ Beta(1 + c_x, 1 + c_univ)      (:262-265, 289-292)
+            v[a] = ax * v[0] / (1.0 - ax);                  // :270, 297
         }
-        wnorm_row(w, k.scratch + (size_t)f * 12, d.C);
+        const double s = (v[0] + v[1]) + v[2];              // normalize(w_new) :271, 298
+        for (int c = 0; c < 3; ++c) {
+            v[c] /= s;
+            w[c] = v[c];
+            k.scratch[(size_t)3 * f + c] = v[c];
+        }
     }
     __syncthreads();
-    // phase B (one thread per table entry): complete-data likelihood change  sum cnt_src * log(w~_new / w~_old)
+    // phase C (one thread per non-constant entry of the normalised table): w~_new and the complete-data likelihood
+    // change  sum cnt_src * log(w~_new / w~_old).  Entries of impossible (cfg, component) pairs stay 0 and cfg 0 stays
+    // (1, 0, 0) for ever, so only 7 (C = 3) or 2 (C = 2) entries per feature are live.
+    const int live = d.C == 3 ? 7 : 2;
     double dll = 0.0;
-    for (int i = threadIdx.x; i < d.F * 12; i += blockDim.x) {
-        const double nw = k.scratch[i], old = k.wn[i];
-        const int c = k.cs[i];
-        if (c > 0 && nw != old) dll += (double)c * log(nw / old);
-        k.wn[i] = nw;
+    for (int i = threadIdx.x; i < live * d.F; i += blockDim.x) {
+        const int f = i / live, e = i - f * live;
+        const int idx = e < 2 ? 3 + e : (e < 4 ? (e == 2 ? 6 : 8) : 5 + e);      // 3,4 | 6,8 | 9,10,11
+        const int cfg = idx / 3, c = idx - cfg * 3;
+        const double* v = k.scratch + (size_t)3 * f;
+        const double tot = (v[0] + ((cfg & 1) ? v[1] : 0.0)) + ((cfg & 2) ? v[2] : 0.0);      // wnorm_row's order
+        const double nw = v[c] / tot;
+        const size_t o = (size_t)f * 12 + idx;
+        const double old = k.wn[o];
+        const int n = k.cs[o];
+        if (n > 0 && nw != old) dll += (double)n * flog(nw / old, k.flt);
+        k.wn[o] = nw;
     }
     ll += block_sum(dll, sh.red);
 }
@@ -534,30 +558,35 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
                                 const double* alpha, const double* lnorm, double* pcache,
                                 double& ll, double& prior, StepShared& sh) {
     const int S = d.S, FS = d.F * d.S;
-    // phase 1: Gamma draws (one thread per (feature, state))
+    PROF_T(t0);
+    // phase 0: feature subset (one draw per feature); marker -1 in the feature's first scratch slot = not selected
+    for (int f = threadIdx.x; f < d.F; f += blockDim.x)
+        k.scratch[(size_t)f * S] = (use_subset && !(rng_uniform(key, step, RP_SUBSET, f) < sp.frac)) ? -1.0 : 0.0;
+    __syncthreads();
+    // phase 1: Gamma draws, one thread per (feature, state)
     for (int i = threadIdx.x; i < FS; i += blockDim.x) {
-        const int f = i / S, s = i - f * S;
-        double g = -1.0;      // -1 = feature not selected
-        if (!use_subset || rng_uniform(key, step, RP_SUBSET, f) < sp.frac) {
-            g = 0.0;
-            if (d.app_mask[f] >> s & 1u)
-                g = rng_gamma(key, step, RP_GAMMA, i, (pc ? pc[i] : 1.0) + (double)cnt[i]);
-        }
+        const int f = (int)__umulhi((unsigned)i, sp.s_magic), s = i - f * S;
+        if (k.scratch[(size_t)f * S] < 0.0) continue;      // a selected feature's slot only ever holds values >= 0
+        double g = 0.0;
+        if (d.app_mask[f] >> s & 1u)
+            g = rng_gamma(key, step, RP_GAMMA, i, (pc ? pc[i] : 1.0) + (double)cnt[i]);
         k.scratch[i] = g;
     }
+    PROF_T(t1);
     __syncthreads();
+    PROF_T(t2);
     // phase 2: normalise, write, accumulate the likelihood delta -- one thread per (feature, state); the S threads of a
     // row each form the row total in the same order, so they agree bit for bit
     double dll = 0.0, dpr = 0.0;
     for (int i = threadIdx.x; i < FS; i += blockDim.x) {
-        const int f = i / S, s = i - f * S;
+        const int f = (int)__umulhi((unsigned)i, sp.s_magic), s = i - f * S;
         const double* g = k.scratch + (size_t)f * S;
         if (g[0] < 0.0 || !(d.app_mask[f] >> s & 1u)) continue;
         double tot = 0.0;
         for (int t = 0; t < S; ++t) tot += g[t];
         const double pn = g[s] / tot;
         const int c = cnt[i];
-        if (c > 0) dll += (double)c * log(pn / p[i]);
+        if (c > 0) dll += (double)c * flog(pn / p[i], k.flt);
         p[i] = pn;
     }
     if (alpha) {
@@ -569,8 +598,11 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
             pcache[f] = v;
         }
     }
+    PROF_T(t3);
     ll += block_sum(dll, sh.red);
     if (alpha) prior += block_sum(dpr, sh.red);
+    PROF_T(t4);
+    PROF_ADD(0, t0, t1); PROF_ADD(1, t1, t2); PROF_ADD(2, t2, t3); PROF_ADD(3, t3, t4);
 }
 
 // ---- K7d: alter_* operators (source-free mode), zone_sampling.py:408-612 --------------------------
@@ -639,7 +671,7 @@ __device__ double column_delta(const DevData& d, const Chain& k, int f, const in
             if (zid >= 0) nw += w[1] * zt;
             if (fam >= 0) nw += w[2] * ft;
         }
-        acc += log(nw) - log(old);
+        acc += flog(nw / old, k.flt);
     }
     return block_sum(acc, red);
 }
@@ -662,7 +694,7 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
         }
         __syncthreads();
         dll = column_delta(d, k, f, nullptr, d.N, wrow_new, -1, 0, 0, 0, 0.0, 0.0, sh.red);
-        const bool accept = log(rng_uniform(key, step, RP_ACCEPT, 0)) < dll - lqr;
+        const bool accept = flog(rng_uniform(key, step, RP_ACCEPT, 0), k.flt) < dll - lqr;
         if (accept) {
             __syncthreads();
             if (threadIdx.x == 0) {
@@ -713,7 +745,7 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
         new_prior_term = t;
         dprior = t - *pcache;
     }
-    const bool accept = log(rng_uniform(key, step, RP_ACCEPT, 0)) < dll - lqr + dprior;
+    const bool accept = flog(rng_uniform(key, step, RP_ACCEPT, 0), k.flt) < dll - lqr + dprior;
     if (accept) {
         __syncthreads();
         if (threadIdx.x == 0) {
@@ -741,23 +773,26 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
     Chain kv = chain_view(st, sp, chain);
     if (sp.work_scratch) kv.scratch = reinterpret_cast<double*>(step_smem + sp.work_off);
     if (sp.work_counts) kv.cnt_tab = reinterpret_cast<int*>(step_smem + sp.work_off);
+    __shared__ double2 flog_tab[SB_FLOG_N];
+    flog_init(flog_tab);
+    __syncthreads();
+    kv.flt = flog_tab;
     const Chain& k = kv;
     const unsigned gchain = (unsigned)(sp.chain_offset + chain);
     const RngKey key = {sp.seed_lo ^ (gchain * 0x9E3779B9u), sp.seed_hi ^ gchain};
     double ll = st.ll[chain], prior = st.prior[chain], geo = st.geo[chain];
     const uint64_t step0 = st.step[chain];
-    unsigned long long acc[SB_N_OPS], rej[SB_N_OPS];
-#pragma unroll
-    for (int i = 0; i < SB_N_OPS; ++i) { acc[i] = 0ull; rej[i] = 0ull; }
 
     for (long long it = 0; it < n_steps; ++it) {
         const uint64_t step = step0 + (uint64_t)it;
+        PROF_T(ts0);
         // operator choice: np.random.choice(fn_operators, p=p_operators)  (mcmc_generative.py:294)
         const double uo = rng_uniform(key, step, RP_OP, 0);
         int oi = 0;
         while (oi < sp.n_ops - 1 && uo >= sp.op_cdf[oi]) ++oi;
         const int op = sp.op_ids[oi];
         bool accepted = true;
+        PROF_T(ts1);
         switch (op) {
             case SB_OP_SHRINK_ZONE: case SB_OP_GROW_ZONE: case SB_OP_SWAP_ZONE:
                 accepted = op_zone_move(d, sp, k, op, chain, key, step, ll, prior, geo, nbr, freeb, prim_key,
@@ -791,16 +826,15 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
                 accepted = op_alter(d, sp, k, op, key, step, ll, prior, sh);
                 break;
         }
-        if (accepted) ++acc[op]; else ++rej[op];
+        PROF_T(ts2);
+        if (threadIdx.x == 0) ++(accepted ? st.acc : st.rej)[(size_t)chain * SB_N_OPS + op];
         __syncthreads();
+        PROF_T(ts3);
+        PROF_ADD(4, ts0, ts1); PROF_ADD(5, ts1, ts2); PROF_ADD(6, ts2, ts3);
     }
     if (threadIdx.x == 0) {
         st.ll[chain] = ll; st.prior[chain] = prior; st.geo[chain] = geo;
         st.step[chain] = step0 + (uint64_t)n_steps;
-        for (int i = 0; i < SB_N_OPS; ++i) {
-            st.acc[(size_t)chain * SB_N_OPS + i] += acc[i];
-            st.rej[(size_t)chain * SB_N_OPS + i] += rej[i];
-        }
     }
 }
 

@@ -49,3 +49,15 @@ def test_beta_and_dirichlet_from_gammas(eng):
     assert np.allclose(p.mean(axis=0), alphas / alphas.sum(), atol=4e-3)
     a0 = alphas.sum()
     assert np.allclose(p.var(axis=0), alphas * (a0 - alphas) / (a0 ** 2 * (a0 + 1)), rtol=0.05)
+
+
+def test_table_log_accuracy(eng):
+    """flog() of the step kernel (sb_common.cuh) against numpy over 120 binades: absolute error <= 4e-16 + one ulp of the
+    result (the final e*ln2 + ... fma rounds once at the magnitude of the result)."""
+    n = 121 * 2000
+    u = eng.rng_sample('uniform', n, seed=9)
+    x = np.ldexp(1.0 + u, np.arange(n) % 121 - 60)
+    got = eng.rng_sample('flog', n, seed=9)
+    ref = np.log(x)
+    err = np.abs(got - ref)
+    assert np.all(err <= 4e-16 + np.spacing(np.abs(ref))), float(np.max(err - np.spacing(np.abs(ref))))
