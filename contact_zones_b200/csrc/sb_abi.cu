@@ -795,6 +795,35 @@ int sb_set_operators(sb_ctx* ctx, const sb_operator_cfg* cfg, const double* p_gr
         CK(cudaFuncSetAttribute(mcmc_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->step_smem));
         CK(cudaFuncSetAttribute(move_log_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->step_smem));
     }
+    // team (thread-block cluster) size: as many CTAs per chain as the SM count allows, each with at least one
+    // 16-feature block of work; SBAYES_B200_TEAM overrides (1, 2, 4 or 8)
+    {
+        int sms = 0;
+        CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
+        int team = 1;
+        for (int t = 8; t >= 2; t >>= 1)
+            if (nc * t <= sms && d.F >= 16 * t) { team = t; break; }
+        if (const char* env = getenv("SBAYES_B200_TEAM")) {
+            const int t = atoi(env);
+            if (t == 1 || t == 2 || t == 4 || t == 8) team = t;
+        }
+        if (d.sample_source && !sp.work_counts) team = 1;     // the global-atomics source sweep is single-CTA
+        while (team > 1) {      // the hardware must be able to co-schedule the cluster
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3((unsigned)(nc * team), 1, 1);
+            cfg.blockDim = dim3(STEP_THREADS, 1, 1);
+            cfg.dynamicSmemBytes = ctx->step_smem;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = (unsigned)team; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr; cfg.numAttrs = 1;
+            int n_clusters = 0;
+            if (cudaOccupancyMaxActiveClusters(&n_clusters, mcmc_step_kernel, &cfg) == cudaSuccess && n_clusters >= 1) break;
+            cudaGetLastError();
+            team >>= 1;
+        }
+        sp.team = team;
+    }
     ctx->has_ops = true;
     return SB_OK;
 }
@@ -804,8 +833,22 @@ int sb_run(sb_ctx* ctx, int64_t n_steps) {
     CK(cudaSetDevice(ctx->device));
     if (!ctx->has_ops) FAIL(SB_E_STATE, "sb_set_operators has not been called");
     if (n_steps == 0) return SB_OK;
-    mcmc_step_kernel<<<ctx->dims.n_chains, STEP_THREADS, ctx->step_smem, ctx->stream>>>(ctx->d, ctx->st, ctx->sp,
-                                                                                       (long long)n_steps);
+    {
+        // one thread-block cluster (team) of sp.team CTAs per chain
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)(ctx->dims.n_chains * ctx->sp.team), 1, 1);
+        cfg.blockDim = dim3(STEP_THREADS, 1, 1);
+        cfg.dynamicSmemBytes = ctx->step_smem;
+        cfg.stream = ctx->stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = (unsigned)ctx->sp.team;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        CK(cudaLaunchKernelEx(&cfg, mcmc_step_kernel, ctx->d, ctx->st, ctx->sp, (long long)n_steps));
+    }
     ++ctx->launches;
     ctx->steps_done += n_steps;
     CK(cudaGetLastError());

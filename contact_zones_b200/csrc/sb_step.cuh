@@ -13,6 +13,8 @@
 #include "sb_rng.cuh"
 #include "sb_eval.cuh"
 #include "../../include/sbayes_b200.h"
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
 
 #define STEP_THREADS 512
 
@@ -40,6 +42,7 @@ struct StepParams {
     int nwords;               // words of one site bitmap
     int prim_cap;             // member capacity of the Prim scratch
     unsigned s_magic;         // ceil(2^32 / S): i / S == __umulhi(i, s_magic) for i < 2^27
+    int team;                 // CTAs per chain (thread-block cluster size): 1, 2, 4 or 8
     int work_off;             // byte offset of the shared work area in the dynamic smem (16 B aligned)
     int work_scratch;         // != 0: the Gibbs scratch ([F][max(S,12)] doubles) lives in the work area
     int work_counts;          // != 0: resample_all_sources keeps per-feature-block count tables in the work area
@@ -126,6 +129,66 @@ __device__ void build_nbr_bits(const DevData& d, const int8_t* zone_id, const in
     }
     __syncthreads();
 }
+
+// ---- a chain is owned by a TEAM of CTAs (one thread-block cluster) -----------------------------------------------
+// With n_chains <= SMs / 2 a single CTA per chain leaves most of the GPU idle, and the step kernel is bound by the
+// instruction issue rate of its one SM.  A team of `size` CTAs splits every data-parallel phase of a step (Gamma draws,
+// table updates, the source sweep, column deltas); all CTAs take the same block-uniform decisions (counter-based RNG),
+// keep identical running ll / prior in registers, and meet in cluster barriers that also order their global-memory
+// traffic: between a write by one CTA and a read of that location by another there is always a team barrier.
+struct Team {
+    int rank, size;
+    double* slot;       // StepShared::tslot of this CTA
+    unsigned turn;
+};
+__device__ __forceinline__ void team_sync(const Team& t) {
+    if (t.size > 1) cg::this_cluster().sync(); else __syncthreads();
+}
+// contiguous share [lo, hi) of n items for this CTA
+__device__ __forceinline__ void team_share(const Team& t, int n, int& lo, int& hi) {
+    const int per = (n + t.size - 1) / t.size;
+    lo = min(n, t.rank * per);
+    hi = min(n, lo + per);
+}
+// Sum of a and b over all threads of all CTAs of the team, identical in every thread (fixed order: block tree, then
+// ranks 0..size-1).  Contains one team barrier; everything the CTAs wrote before it is visible after it.
+__device__ void team_exchange(double& a, double& b, double* red, Team& t) {     // a, b: this CTA's block sums
+    double* mine = t.slot + 2 * (t.turn & 1u);
+    ++t.turn;
+    if (threadIdx.x == 0) { mine[0] = a; mine[1] = b; }
+    cg::cluster_group cl = cg::this_cluster();
+    cl.sync();
+    if (threadIdx.x < 32) {
+        const int lane = threadIdx.x;
+        double va = 0.0, vb = 0.0;
+        if (lane < t.size) {
+            const double* peer = cl.map_shared_rank(mine, lane);
+            va = peer[0]; vb = peer[1];
+        }
+        double sa = 0.0, sb = 0.0;
+        for (int r = 0; r < t.size; ++r) {
+            sa += __shfl_sync(0xffffffffu, va, r);
+            sb += __shfl_sync(0xffffffffu, vb, r);
+        }
+        if (lane == 0) { red[0] = sa; red[1] = sb; }
+    }
+    __syncthreads();
+    a = red[0]; b = red[1];
+}
+__device__ __forceinline__ void team_sum2(double& a, double& b, double* red, Team& t) {
+    a = block_sum(a, red);
+    b = block_sum(b, red);
+    if (t.size > 1) team_exchange(a, b, red, t);
+}
+__device__ __forceinline__ double team_sum(double v, double* red, Team& t) {
+    v = block_sum(v, red);
+    if (t.size > 1) {
+        double z = 0.0;
+        team_exchange(v, z, red, t);
+    }
+    return v;
+}
+
 
 // ---- per-chain view ------------------------------------------------------------------------------
 struct Chain {
@@ -250,7 +313,7 @@ __device__ double resample_all_sources(const DevData& d, const Chain& k, RngKey 
 // live in shared memory, are filled with shared atomics and flushed with plain coalesced stores -- no global atomics,
 // no zeroing pass.  One Philox block serves four cells (32-bit uniforms).
 __device__ double resample_all_sources_blocked(const DevData& d, const Chain& k, RngKey key, uint64_t step, double* red,
-                                               int* tab) {
+                                               int* tab, Team& tm) {
     const int S = d.S, F = d.F, C = d.C, N = d.N;
     const size_t FS = (size_t)F * S;
     const int bS = 16 * S;
@@ -260,11 +323,13 @@ __device__ double resample_all_sources_blocked(const DevData& d, const Chain& k,
     int* tcf = tcz + d.Z * bS;          // [Fam][16][S]
     const int T = bS * (1 + d.Z + d.Fam) + 192;
     const int nb = d.ldx >> 4;
+    int fb_lo, fb_hi;
+    team_share(tm, nb, fb_lo, fb_hi);                   // each CTA of the team sweeps its own feature blocks
     for (int i = threadIdx.x; i < T; i += blockDim.x) tab[i] = 0;
     __syncthreads();
     LogProd acc;
     lp_init(acc);
-    for (int fb = 0; fb < nb; ++fb) {
+    for (int fb = fb_lo; fb < fb_hi; ++fb) {
         const int f0 = fb << 4;
         for (int n = threadIdx.x; n < N; n += blockDim.x) {
             const uint4 xv = *reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + f0);
@@ -334,11 +399,13 @@ __device__ double resample_all_sources_blocked(const DevData& d, const Chain& k,
         }
         __syncthreads();
     }
-    return block_sum(lp_value(acc), red);
+    return team_sum(lp_value(acc), red, tm);
 }
 
-__device__ __forceinline__ double resample_sources(const DevData& d, const Chain& k, RngKey key, uint64_t step, double* red) {
-    return k.cnt_tab ? resample_all_sources_blocked(d, k, key, step, red, k.cnt_tab)
+// (the global-atomics variant is only used by one-CTA teams: sb_set_operators picks team = 1 when the tables do not fit)
+__device__ __forceinline__ double resample_sources(const DevData& d, const Chain& k, RngKey key, uint64_t step, double* red,
+                                                   Team& tm) {
+    return k.cnt_tab ? resample_all_sources_blocked(d, k, key, step, red, k.cnt_tab, tm)
                      : resample_all_sources(d, k, key, step, red);
 }
 
@@ -348,6 +415,7 @@ struct StepShared {
     int redi[33];
     int pick;           // bits_select result
     double dshare[4];
+    double tslot[4];    // this CTA's partial sums of the team reductions (double-buffered pair), read by the peers
 };
 
 // prior terms that depend on the zones: size prior (model.py:932-972) and geo prior (:1096-1139, last zone only)
@@ -381,7 +449,7 @@ __device__ __forceinline__ double grow_q(bool in_nbr, int n_free, int n_nbr, dou
 __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain& k, int kind, int chain,
                              RngKey key, uint64_t step, double& ll, double& prior, double& geo,
                              unsigned* nbr, unsigned* freeb, double* prim_key, unsigned char* prim_tree,
-                             StepShared& sh) {
+                             StepShared& sh, Team& tm, bool& synced) {
     const double rho = sp.p_grow[chain];
     const int max_size = sp.max_size[chain];
     const int z = rng_int(key, step, RP_ZONE, 0, d.Z);
@@ -460,8 +528,10 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
     }
     if (!accept) return false;
 
-    __syncthreads();
-    if (threadIdx.x == 0) {
+    // Proposal and decision above are computed redundantly (and identically) by every CTA of the team from the old
+    // state.  Barrier 1: nobody reads the old zone state any more; rank 0 writes; barrier 2: everybody sees the new one.
+    team_sync(tm);
+    if (threadIdx.x == 0 && tm.rank == 0) {
         if (site_removed >= 0) {
             int i = 0;
             while (mem[i] != site_removed) ++i;
@@ -474,10 +544,11 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
         }
         k.zsize[z] = new_size;
     }
-    __syncthreads();
+    team_sync(tm);
+    synced = true;
     prior += dprior;
     geo = geo_new;
-    if (d.sample_source) ll = resample_sources(d, k, key, step, sh.red);          // :859-862 (on accept only)
+    if (d.sample_source) ll = resample_sources(d, k, key, step, sh.red, tm);      // :859-862 (on accept only)
     else ll += dll;
     return true;
 }
@@ -496,13 +567,15 @@ __device__ __forceinline__ double weight_ll_row(const int* cs_row, const double*
 // gibbs_sample_weights (zone_sampling.py:222-331).  Always accepted (incl. quirk Q2: with inheritance the
 // per-feature MH decision is overwritten by `sample_new.weights = w_new`, :325-327).
 __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, uint64_t step, double& ll,
-                                 StepShared& sh) {
+                                 StepShared& sh, Team& tm) {
     // fixed = choice(['inheritance', 'contact'])  (:249)
     const bool fixed_inheritance = rng_uniform(key, step, RP_FIXED, 0) < 0.5;
     // phase A (one thread per feature): the two Gammas of the feature's Beta / Dirichlet draw in lock-step, then the
     // new weight row, staged in the scratch ([0,3F))
     const int a = (d.C == 2) ? 1 : (fixed_inheritance ? 1 : 2);   // cfg of the "only this component" sites; also column x
-    for (int f = threadIdx.x; f < d.F; f += blockDim.x) {
+    int f_lo, f_hi;
+    team_share(tm, d.F, f_lo, f_hi);                    // each CTA of the team owns a contiguous range of features
+    for (int f = f_lo + threadIdx.x; f < f_hi; f += blockDim.x) {
         const int* cs = k.cs + (size_t)f * 12;
         int c0, c1;
         if (d.C == 2) { c0 = cs[3 + 0]; c1 = cs[3 + 1]; }                  // counts over sites with a zone (:239-243)
@@ -532,7 +605,7 @@ __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, u
     // (1, 0, 0) for ever, so only 7 (C = 3) or 2 (C = 2) entries per feature are live.
     const int live = d.C == 3 ? 7 : 2;
     double dll = 0.0;
-    for (int i = threadIdx.x; i < live * d.F; i += blockDim.x) {
+    for (int i = live * f_lo + threadIdx.x; i < live * f_hi; i += blockDim.x) {
         const int f = i / live, e = i - f * live;
         const int idx = e < 2 ? 3 + e : (e < 4 ? (e == 2 ? 6 : 8) : 5 + e);      // 3,4 | 6,8 | 9,10,11
         const int cfg = idx / 3, c = idx - cfg * 3;
@@ -545,7 +618,7 @@ __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, u
         if (n > 0 && nw != old) dll += (double)n * flog(nw / old, k.flt);
         k.wn[o] = nw;
     }
-    ll += block_sum(dll, sh.red);
+    ll += team_sum(dll, sh.red, tm);
 }
 
 // Shared body of gibbs_sample_p_global / p_zones / p_families (zone_sampling.py:334-406):
@@ -556,15 +629,18 @@ __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, u
 __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Chain& k, RngKey key, uint64_t step,
                                 double* p, const int* cnt, const double* pc, bool use_subset,
                                 const double* alpha, const double* lnorm, double* pcache,
-                                double& ll, double& prior, StepShared& sh) {
-    const int S = d.S, FS = d.F * d.S;
+                                double& ll, double& prior, StepShared& sh, Team& tm) {
+    const int S = d.S;
+    int f_lo, f_hi;
+    team_share(tm, d.F, f_lo, f_hi);                    // whole rows per CTA: the row totals stay CTA-local
+    const int i_lo = f_lo * S, i_hi = f_hi * S;
     PROF_T(t0);
     // phase 0: feature subset (one draw per feature); marker -1 in the feature's first scratch slot = not selected
-    for (int f = threadIdx.x; f < d.F; f += blockDim.x)
+    for (int f = f_lo + threadIdx.x; f < f_hi; f += blockDim.x)
         k.scratch[(size_t)f * S] = (use_subset && !(rng_uniform(key, step, RP_SUBSET, f) < sp.frac)) ? -1.0 : 0.0;
     __syncthreads();
     // phase 1: Gamma draws, one thread per (feature, state)
-    for (int i = threadIdx.x; i < FS; i += blockDim.x) {
+    for (int i = i_lo + threadIdx.x; i < i_hi; i += blockDim.x) {
         const int f = (int)__umulhi((unsigned)i, sp.s_magic), s = i - f * S;
         if (k.scratch[(size_t)f * S] < 0.0) continue;      // a selected feature's slot only ever holds values >= 0
         double g = 0.0;
@@ -578,7 +654,7 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
     // phase 2: normalise, write, accumulate the likelihood delta -- one thread per (feature, state); the S threads of a
     // row each form the row total in the same order, so they agree bit for bit
     double dll = 0.0, dpr = 0.0;
-    for (int i = threadIdx.x; i < FS; i += blockDim.x) {
+    for (int i = i_lo + threadIdx.x; i < i_hi; i += blockDim.x) {
         const int f = (int)__umulhi((unsigned)i, sp.s_magic), s = i - f * S;
         const double* g = k.scratch + (size_t)f * S;
         if (g[0] < 0.0 || !(d.app_mask[f] >> s & 1u)) continue;
@@ -591,7 +667,7 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
     }
     if (alpha) {
         __syncthreads();
-        for (int f = threadIdx.x; f < d.F; f += blockDim.x) {
+        for (int f = f_lo + threadIdx.x; f < f_hi; f += blockDim.x) {
             if (k.scratch[(size_t)f * S] < 0.0) continue;
             const double v = dirichlet_row(p + (size_t)f * S, alpha + (size_t)f * S, lnorm[f], d.app_mask[f], S);
             dpr += v - pcache[f];
@@ -599,8 +675,13 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
         }
     }
     PROF_T(t3);
-    ll += block_sum(dll, sh.red);
-    if (alpha) prior += block_sum(dpr, sh.red);
+    if (alpha) {
+        team_sum2(dll, dpr, sh.red, tm);
+        ll += dll;
+        prior += dpr;
+    } else {
+        ll += team_sum(dll, sh.red, tm);
+    }
     PROF_T(t4);
     PROF_ADD(0, t0, t1); PROF_ADD(1, t1, t2); PROF_ADD(2, t2, t3); PROF_ADD(3, t3, t4);
 }
@@ -643,11 +724,13 @@ __device__ __forceinline__ int nth_state(uint32_t mask, int j) {
 // weight row (wrow_new) or one probability row (which = 0 global / 1 zone z / 2 family fam; states s0,s1 -> v0,v1).
 __device__ double column_delta(const DevData& d, const Chain& k, int f, const int* sites, int n_sites,
                                const double* wrow_new, int which, int tab, int s0, int s1, double v0, double v1,
-                               double* red) {
+                               double* red, Team& tm) {
     const double* wrow = k.wn + (size_t)f * 12;
     const size_t FS = (size_t)d.F * d.S;
     double acc = 0.0;
-    for (int i = threadIdx.x; i < n_sites; i += blockDim.x) {
+    int i_lo, i_hi;
+    team_share(tm, n_sites, i_lo, i_hi);
+    for (int i = i_lo + threadIdx.x; i < i_hi; i += blockDim.x) {
         const int n = sites ? sites[i] : i;
         const int xs = sites ? d.x[(size_t)n * d.ldx + f] : d.xT[(size_t)f * d.ldn + n];
         if (xs == SB_NA) continue;
@@ -673,12 +756,12 @@ __device__ double column_delta(const DevData& d, const Chain& k, int f, const in
         }
         acc += flog(nw / old, k.flt);
     }
-    return block_sum(acc, red);
+    return team_sum(acc, red, tm);      // barrier: every read of the old state (the callers read before calling) is done
 }
 
 // alter_weights / alter_p_global / alter_p_zones / alter_p_families (zone_sampling.py:408-612). Returns accepted.
 __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k, int op, RngKey key, uint64_t step,
-                         double& ll, double& prior, StepShared& sh) {
+                         double& ll, double& prior, StepShared& sh, Team& tm, bool& synced) {
     const int f = rng_int(key, step, RP_FEATURE, 0, d.F);            // np.random.choice(range(n_features))
     double lqr, n0, n1, dll, dprior = 0.0;
     if (op == SB_OP_ALTER_WEIGHTS) {
@@ -693,11 +776,12 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
             wnorm_row(v, wrow_new, d.C);
         }
         __syncthreads();
-        dll = column_delta(d, k, f, nullptr, d.N, wrow_new, -1, 0, 0, 0, 0.0, 0.0, sh.red);
+        dll = column_delta(d, k, f, nullptr, d.N, wrow_new, -1, 0, 0, 0, 0.0, 0.0, sh.red, tm);
         const bool accept = flog(rng_uniform(key, step, RP_ACCEPT, 0), k.flt) < dll - lqr;
+        synced = !accept;       // a rejected proposal wrote nothing after the reduction's barrier
         if (accept) {
             __syncthreads();
-            if (threadIdx.x == 0) {
+            if (threadIdx.x == 0 && tm.rank == 0) {
                 w[a] = n0; w[b] = n1;
                 for (int i = 0; i < 12; ++i) k.wn[(size_t)f * 12 + i] = wrow_new[i];
             }
@@ -735,20 +819,21 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
         }
     }
     pair_proposal(key, step, row[s0], row[s1], kappa, n0, n1, lqr);
-    dll = column_delta(d, k, f, sites, n_sites, nullptr, which, tab, s0, s1, n0, n1, sh.red);
     double new_prior_term = 0.0;
     if (alpha) {
-        // Dirichlet prior of the changed row with the two entries replaced
+        // Dirichlet prior of the changed row with the two entries replaced (read before the reduction's barrier)
         double t = *lnorm;
         for (int s = 0; s < d.S; ++s)
             if (mask >> s & 1u) t += xlogy_d(alpha[s] - 1.0, s == s0 ? n0 : (s == s1 ? n1 : row[s]));
         new_prior_term = t;
         dprior = t - *pcache;
     }
+    dll = column_delta(d, k, f, sites, n_sites, nullptr, which, tab, s0, s1, n0, n1, sh.red, tm);
     const bool accept = flog(rng_uniform(key, step, RP_ACCEPT, 0), k.flt) < dll - lqr + dprior;
+    synced = !accept;
     if (accept) {
         __syncthreads();
-        if (threadIdx.x == 0) {
+        if (threadIdx.x == 0 && tm.rank == 0) {
             row[s0] = n0; row[s1] = n1;
             if (alpha) *pcache = new_prior_term;
         }
@@ -764,7 +849,8 @@ __global__ void __launch_bounds__(STEP_THREADS)
 mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
     extern __shared__ unsigned char step_smem[];
     __shared__ StepShared sh;
-    const int chain = blockIdx.x;
+    const int chain = blockIdx.x / sp.team;             // one cluster of sp.team CTAs per chain (cluster dims (team,1,1))
+    Team tm = {(int)(blockIdx.x % sp.team), sp.team, sh.tslot, 0u};
     unsigned* nbr = reinterpret_cast<unsigned*>(step_smem);
     unsigned* freeb = nbr + sp.nwords;
     double* prim_key = reinterpret_cast<double*>(freeb + sp.nwords + (sp.nwords & 1));
@@ -792,26 +878,31 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
         while (oi < sp.n_ops - 1 && uo >= sp.op_cdf[oi]) ++oi;
         const int op = sp.op_ids[oi];
         bool accepted = true;
+        bool synced = false;    // the operator ended in a team barrier that followed all of its global writes
         PROF_T(ts1);
         switch (op) {
             case SB_OP_SHRINK_ZONE: case SB_OP_GROW_ZONE: case SB_OP_SWAP_ZONE:
                 accepted = op_zone_move(d, sp, k, op, chain, key, step, ll, prior, geo, nbr, freeb, prim_key,
-                                        prim_tree, sh);
+                                        prim_tree, sh, tm, synced);
                 break;
             case SB_OP_GIBBS_SOURCES:
-                ll = resample_sources(d, k, key, step, sh.red);
+                ll = resample_sources(d, k, key, step, sh.red, tm);
+                synced = true;
                 break;
             case SB_OP_GIBBS_WEIGHTS:
-                op_gibbs_weights(d, k, key, step, ll, sh);
+                op_gibbs_weights(d, k, key, step, ll, sh, tm);
+                synced = true;
                 break;
             case SB_OP_GIBBS_P_GLOBAL:
                 gibbs_table_row(d, sp, k, key, step, k.pg, k.cg, d.gibbs_g, true,
-                                d.pg_type == 1 ? d.alpha_g : nullptr, d.lnorm_g, k.ppg, ll, prior, sh);
+                                d.pg_type == 1 ? d.alpha_g : nullptr, d.lnorm_g, k.ppg, ll, prior, sh, tm);
+                synced = true;
                 break;
             case SB_OP_GIBBS_P_ZONES: {
                 const size_t o = (size_t)rng_int(key, step, RP_ZONE, 0, d.Z) * d.F * d.S;
                 gibbs_table_row(d, sp, k, key, step, k.pz + o, k.cz + o, nullptr, false, nullptr, nullptr, nullptr,
-                                ll, prior, sh);
+                                ll, prior, sh, tm);
+                synced = true;
                 break;
             }
             case SB_OP_GIBBS_P_FAMILIES: {
@@ -819,23 +910,26 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
                 const size_t o = (size_t)fam * d.F * d.S;
                 gibbs_table_row(d, sp, k, key, step, k.pf + o, k.cf + o, d.gibbs_f + o, true,
                                 d.pf_type == 1 ? d.alpha_f + o : nullptr, d.lnorm_f + (size_t)fam * d.F,
-                                k.ppf + (size_t)fam * d.F, ll, prior, sh);
+                                k.ppf + (size_t)fam * d.F, ll, prior, sh, tm);
+                synced = true;
                 break;
             }
             default:
-                accepted = op_alter(d, sp, k, op, key, step, ll, prior, sh);
+                accepted = op_alter(d, sp, k, op, key, step, ll, prior, sh, tm, synced);
                 break;
         }
         PROF_T(ts2);
-        if (threadIdx.x == 0) ++(accepted ? st.acc : st.rej)[(size_t)chain * SB_N_OPS + op];
-        __syncthreads();
+        if (threadIdx.x == 0 && tm.rank == 0) ++(accepted ? st.acc : st.rej)[(size_t)chain * SB_N_OPS + op];
+        // step boundary: the next step's writes must not overtake this step's reads in a slower CTA of the team
+        if (synced) __syncthreads(); else team_sync(tm);
         PROF_T(ts3);
         PROF_ADD(4, ts0, ts1); PROF_ADD(5, ts1, ts2); PROF_ADD(6, ts2, ts3);
     }
-    if (threadIdx.x == 0) {
+    if (threadIdx.x == 0 && tm.rank == 0) {
         st.ll[chain] = ll; st.prior[chain] = prior; st.geo[chain] = geo;
         st.step[chain] = step0 + (uint64_t)n_steps;
     }
+    if (tm.size > 1) cg::this_cluster().sync();         // keep every CTA's shared memory alive until the last peer read
 }
 
 // ---- forced zone move: (log_q, log_q_back) without touching the state (parity of :704-933) --------
