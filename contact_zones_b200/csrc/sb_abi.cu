@@ -15,6 +15,13 @@
 #include <string>
 #include <vector>
 
+// pinned upload staging buffer of sb_set_state
+struct Staging {
+    unsigned char* buf = nullptr;
+    cudaEvent_t done = nullptr;
+    bool pending = false;
+};
+
 struct sb_ctx {
     int device = 0;
     sb_dims dims{};
@@ -39,6 +46,9 @@ struct sb_ctx {
     int* d_maxsize = nullptr;
     size_t step_smem = 0;
     std::vector<int> h_zone_size;    // [chains][Z] host mirror kept by set_state (shape checks only)
+    struct Staging stage[2];         // pinned upload staging (sb_set_state)
+    size_t stage_bytes = 0;
+    int stage_next = 0;
 };
 
 #define CK(call)                                                                                  \
@@ -184,6 +194,10 @@ int sb_destroy(sb_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->own_stream) cudaStreamSynchronize(ctx->own_stream);
     for (void* p : ctx->allocs) cudaFree(p);
+    for (Staging& sg : ctx->stage) {
+        if (sg.done) { cudaEventSynchronize(sg.done); cudaEventDestroy(sg.done); }
+        if (sg.buf) cudaFreeHost(sg.buf);
+    }
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
     return SB_OK;
@@ -408,6 +422,29 @@ static int recount_chain(sb_ctx* ctx, int chain) {
     return SB_OK;
 }
 
+// Upload path: the caller's arrays are packed into a pinned staging buffer (two of them, used alternately, so that
+// packing chain c+1 overlaps the DMA of chain c), every device array is filled by one asynchronous copy from there,
+// and the call returns without a stream synchronisation -- the borrowed host pointers are not touched after return.
+static size_t align16(size_t v) { return (v + 15) & ~(size_t)15; }
+
+static int staging_acquire(sb_ctx* ctx, size_t bytes, Staging** out) {
+    if (ctx->stage_bytes < bytes) {
+        for (Staging& sg : ctx->stage) {
+            if (sg.pending) { CK(cudaEventSynchronize(sg.done)); sg.pending = false; }
+            if (sg.buf) cudaFreeHost(sg.buf);
+            sg.buf = nullptr;
+            CK(cudaMallocHost((void**)&sg.buf, bytes));
+            if (!sg.done) CK(cudaEventCreateWithFlags(&sg.done, cudaEventDisableTiming));
+        }
+        ctx->stage_bytes = bytes;
+    }
+    Staging& sg = ctx->stage[ctx->stage_next];
+    ctx->stage_next ^= 1;
+    if (sg.pending) { CK(cudaEventSynchronize(sg.done)); sg.pending = false; }
+    *out = &sg;
+    return SB_OK;
+}
+
 int sb_set_state(sb_ctx* ctx, int chain, const uint8_t* zones, const double* weights, const double* p_global,
                  const double* p_zones, const double* p_families, const uint8_t* source) {
     if (!ctx) return SB_E_ARG;
@@ -421,37 +458,80 @@ int sb_set_state(sb_ctx* ctx, int chain, const uint8_t* zones, const double* wei
         FAIL(SB_E_ARG, "sb_set_state: missing array");
     if (d.sample_source && !source) FAIL(SB_E_ARG, "sb_set_state: SAMPLE_SOURCE context needs a source array");
 
-    std::vector<int8_t> zid(st.s_zone_id, -1);
-    std::vector<int> members((size_t)Z * N, 0), sizes(Z > 0 ? Z : 1, 0);
-    for (int z = 0; z < Z; ++z)
+    // layout of one chain image in the staging buffer
+    const size_t FS = (size_t)F * S;
+    const size_t o_zid = 0;
+    const size_t o_mem = align16(o_zid + st.s_zone_id);
+    const size_t o_siz = align16(o_mem + (size_t)Z * N * sizeof(int));
+    const size_t o_w = align16(o_siz + (size_t)(Z > 0 ? Z : 1) * sizeof(int));
+    const size_t o_pg = align16(o_w + (size_t)F * 3 * sizeof(double));
+    const size_t o_pz = o_pg + FS * sizeof(double);
+    const size_t o_pf = o_pz + (size_t)Z * FS * sizeof(double);
+    const size_t o_src = align16(o_pf + (size_t)Fam * FS * sizeof(double));
+    const size_t total = o_src + (d.sample_source ? (size_t)N * d.ldx : 0);
+    Staging* sg;
+    r = staging_acquire(ctx, total, &sg);
+    if (r != SB_OK) return r;
+    unsigned char* b = sg->buf;
+
+    int8_t* zid = reinterpret_cast<int8_t*>(b + o_zid);
+    int* members = reinterpret_cast<int*>(b + o_mem);
+    int* sizes = reinterpret_cast<int*>(b + o_siz);
+    memset(zid, 0xff, st.s_zone_id);                       // -1
+    for (int z = 0; z < Z; ++z) {
+        int m = 0;
+        const uint8_t* row = zones + (size_t)z * N;
+        int* mrow = members + (size_t)z * N;
         for (int n = 0; n < N; ++n)
-            if (zones[(size_t)z * N + n]) {
+            if (row[n]) {
                 if (zid[n] >= 0) FAIL(SB_E_OVERLAP, "sb_set_state: zones overlap (a site belongs to two zones)");
                 zid[n] = (int8_t)z;
-                members[(size_t)z * N + sizes[z]++] = n;
+                mrow[m++] = n;
             }
-    H2D(st.zone_id + chain * st.s_zone_id, zid.data(), zid.size());
-    H2D(st.zone_members + chain * st.s_zone_members, members.data(), members.size());
-    H2D(st.zone_size + chain * st.s_zone_size, sizes.data(), sizes.size());
-    for (int z = 0; z < Z; ++z) ctx->h_zone_size[chain * st.s_zone_size + z] = sizes[z];
-
-    std::vector<double> w3((size_t)F * 3, 0.0);
-    for (int f = 0; f < F; ++f)
-        for (int c = 0; c < C; ++c) w3[(size_t)f * 3 + c] = weights[(size_t)f * C + c];
-    H2D(st.weights + chain * st.s_weights, w3.data(), w3.size());
-    H2D(st.p_global + chain * st.s_p_global, p_global, (size_t)F * S);
-    if (Z > 0) H2D(st.p_zones + chain * st.s_p_zones, p_zones, (size_t)Z * F * S);
-    if (d.inheritance) H2D(st.p_fam + chain * st.s_p_fam, p_families, (size_t)Fam * F * S);
-    if (d.sample_source) {
-        std::vector<uint8_t> hs((size_t)N * d.ldx, 0);
-        for (int n = 0; n < N; ++n)
-            for (int f = 0; f < F; ++f) {
-                const uint8_t s = source[(size_t)n * F + f];
-                if (s >= C) FAIL(SB_E_ARG, "sb_set_state: source component out of range");
-                hs[(size_t)n * d.ldx + f] = s;
-            }
-        H2D(st.source + chain * st.s_source, hs.data(), hs.size());
+        for (int n = m; n < N; ++n) mrow[n] = 0;
+        sizes[z] = m;
     }
+    double* w3 = reinterpret_cast<double*>(b + o_w);
+    for (int f = 0; f < F; ++f)
+        for (int c = 0; c < 3; ++c) w3[(size_t)f * 3 + c] = c < C ? weights[(size_t)f * C + c] : 0.0;
+    memcpy(b + o_pg, p_global, FS * sizeof(double));
+    if (Z > 0) memcpy(b + o_pz, p_zones, (size_t)Z * FS * sizeof(double));
+    if (d.inheritance) memcpy(b + o_pf, p_families, (size_t)Fam * FS * sizeof(double));
+    if (d.sample_source) {
+        unsigned char* hs = b + o_src;
+        unsigned bad = 0;
+        for (int n = 0; n < N; ++n) {
+            const uint8_t* srow = source + (size_t)n * F;
+            unsigned char* drow = hs + (size_t)n * d.ldx;
+            memcpy(drow, srow, (size_t)F);
+            memset(drow + F, 0, (size_t)(d.ldx - F));
+            unsigned char mx = 0;
+            for (int f = 0; f < F; ++f) mx = srow[f] > mx ? srow[f] : mx;      // vectorises (pmaxub)
+            bad |= (unsigned)(mx >= C);
+        }
+        if (bad) FAIL(SB_E_ARG, "sb_set_state: source component out of range");
+    }
+
+    cudaStream_t sm = ctx->stream;
+    CK(cudaMemcpyAsync(st.zone_id + chain * st.s_zone_id, zid, st.s_zone_id, cudaMemcpyHostToDevice, sm));
+    if (Z > 0) {
+        CK(cudaMemcpyAsync(st.zone_members + chain * st.s_zone_members, members, (size_t)Z * N * sizeof(int),
+                           cudaMemcpyHostToDevice, sm));
+        CK(cudaMemcpyAsync(st.zone_size + chain * st.s_zone_size, sizes, (size_t)Z * sizeof(int), cudaMemcpyHostToDevice, sm));
+    }
+    for (int z = 0; z < Z; ++z) ctx->h_zone_size[chain * st.s_zone_size + z] = sizes[z];
+    CK(cudaMemcpyAsync(st.weights + chain * st.s_weights, w3, (size_t)F * 3 * sizeof(double), cudaMemcpyHostToDevice, sm));
+    CK(cudaMemcpyAsync(st.p_global + chain * st.s_p_global, b + o_pg, FS * sizeof(double), cudaMemcpyHostToDevice, sm));
+    if (Z > 0)
+        CK(cudaMemcpyAsync(st.p_zones + chain * st.s_p_zones, b + o_pz, (size_t)Z * FS * sizeof(double),
+                           cudaMemcpyHostToDevice, sm));
+    if (d.inheritance)
+        CK(cudaMemcpyAsync(st.p_fam + chain * st.s_p_fam, b + o_pf, (size_t)Fam * FS * sizeof(double),
+                           cudaMemcpyHostToDevice, sm));
+    if (d.sample_source)
+        CK(cudaMemcpyAsync(st.source + chain * st.s_source, b + o_src, (size_t)N * d.ldx, cudaMemcpyHostToDevice, sm));
+    CK(cudaEventRecord(sg->done, sm));
+    sg->pending = true;
     dim3 grid((F + 127) / 128, 1);
     wnorm_kernel<<<grid, 128, 0, ctx->stream>>>(d, st, chain);
     ++ctx->launches;
