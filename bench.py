@@ -180,6 +180,21 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------------
+def k1_traffic():
+    """DRAM bytes per launch of K1 at N=20000 from the committed `ncu --set full` summary (profiles/), or None."""
+    import glob
+    import re
+    files = sorted(glob.glob(os.path.join(ROOT, 'profiles', 'r*_k1_ncu_full_N20000.txt')))
+    if not files:
+        return None
+    tot, unit = 0.0, {'byte': 1.0, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}
+    for line in open(files[-1]):
+        m = re.match(r'dram__bytes_(read|write)\.sum\s+([0-9.,]+)\s+(\w+)', line)
+        if m:
+            tot += float(m.group(2).replace(',', '')) * unit.get(m.group(3), 1.0)
+    return tot or None
+
+
 def measured_peak():
     try:
         return float(json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))['hbm_gbs']), 'measured'
@@ -258,6 +273,9 @@ def run_gpu_arm(args, rank, world, local_rank):
 
     torch.cuda.set_device(local_rank)
     if world > 1:
+        # NCCL prints its version banner on stdout at NCCL_DEBUG=VERSION; stdout carries exactly one JSON line
+        if os.environ.get('NCCL_DEBUG', '').upper() in ('', 'VERSION'):
+            os.environ['NCCL_DEBUG'] = 'WARN'
         dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
     # torch.cuda.Event only sees torch's current stream: make a real (non-legacy) stream current and hand the
     # same stream to the C ABI, so that events, flushes, NCCL and our kernels are ordered on one stream
@@ -370,7 +388,7 @@ def run_gpu_arm(args, rank, world, local_rank):
         peak, how = measured_peak()
         roof = {'bound': 'hbm', 'kernel': 'lh_table_kernel<2> (K1, source-free) on 256 chains x 20000 x 100 x 4',
                 'achieved': top['gbs_mean'], 'peak': peak, 'peak_source': how, 'unit': 'GB/s',
-                'frac': top['gbs_mean'] / peak, 'traffic': None,
+                'frac': top['gbs_mean'] / peak, 'traffic': k1_traffic(),
                 'bytes_per_launch': top['bytes_per_launch'], 'us_per_launch': top['us_mean']}
     if world > 1:
         dist.barrier()
