@@ -289,21 +289,17 @@ def run_gpu_arm(args, rank, world, local_rank):
                  n_chains=nc, inheritance=True, sample_source=True, device=local_rank, chain_offset=rank * nc)
     eng.set_stream(stream)
     states = [d_state(data, 100 + rank * nc + c) for c in range(nc)]
-    host = []
-    for s in states:       # pinned host copies of every chain state (the e2e leg uploads from these)
-        h = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for k, v in
-             dict(zones=s['zones'].astype(np.uint8), weights=s['weights'], p_global=s['p_global'][0],
-                  p_zones=s['p_zones'], p_families=s['p_families'],
-                  source=np.argmax(s['source'], -1).astype(np.uint8)).items()}
-        host.append(h)
+    # pinned host image of all chain states, stacked along the chain axis (the e2e leg uploads from these every step)
+    host = {k: torch.from_numpy(np.ascontiguousarray(np.stack(v))).pin_memory() for k, v in dict(
+        zones=[s['zones'].astype(np.uint8) for s in states], weights=[s['weights'] for s in states],
+        p_global=[s['p_global'][0] for s in states], p_zones=[s['p_zones'] for s in states],
+        p_families=[s['p_families'] for s in states],
+        source=[np.argmax(s['source'], -1).astype(np.uint8) for s in states]).items()}
 
     def upload():
-        n = 0
-        for c, h in enumerate(host):
-            eng.set_state(c, h['zones'].numpy(), h['weights'].numpy(), h['p_global'].numpy(), h['p_zones'].numpy(),
-                          h['p_families'].numpy(), h['source'].numpy())
-            n += sum(t.numel() * t.element_size() for t in h.values())
-        return n
+        eng.set_states(0, host['zones'].numpy(), host['weights'].numpy(), host['p_global'].numpy(),
+                       host['p_zones'].numpy(), host['p_families'].numpy(), host['source'].numpy())
+        return sum(t.numel() * t.element_size() for t in host.values())
 
     upload()
     eng.eval()

@@ -407,20 +407,22 @@ static int check_chain(sb_ctx* ctx, int chain) {
     return SB_OK;
 }
 
-static int recount_chain(sb_ctx* ctx, int chain) {
+static int recount_chains(sb_ctx* ctx, int chain, int n) {
     const DevData& d = ctx->d;
     ChainArrays& st = ctx->st;
-    CK(cudaMemsetAsync(st.cnt_glob + chain * st.s_cnt_glob, 0, st.s_cnt_glob * sizeof(int), ctx->stream));
-    CK(cudaMemsetAsync(st.cnt_zone + chain * st.s_cnt_zone, 0, st.s_cnt_zone * sizeof(int), ctx->stream));
-    CK(cudaMemsetAsync(st.cnt_fam + chain * st.s_cnt_fam, 0, st.s_cnt_fam * sizeof(int), ctx->stream));
-    CK(cudaMemsetAsync(st.cnt_src + chain * st.s_cnt_src, 0, st.s_cnt_src * sizeof(int), ctx->stream));
+    const size_t nn = (size_t)n;
+    CK(cudaMemsetAsync(st.cnt_glob + chain * st.s_cnt_glob, 0, nn * st.s_cnt_glob * sizeof(int), ctx->stream));
+    CK(cudaMemsetAsync(st.cnt_zone + chain * st.s_cnt_zone, 0, nn * st.s_cnt_zone * sizeof(int), ctx->stream));
+    CK(cudaMemsetAsync(st.cnt_fam + chain * st.s_cnt_fam, 0, nn * st.s_cnt_fam * sizeof(int), ctx->stream));
+    CK(cudaMemsetAsync(st.cnt_src + chain * st.s_cnt_src, 0, nn * st.s_cnt_src * sizeof(int), ctx->stream));
     if (!d.sample_source) return SB_OK;
-    dim3 grid(ctx->n_tiles, 1);
+    dim3 grid(ctx->n_tiles, n);
     count_kernel<<<grid, 256, 0, ctx->stream>>>(d, st, chain, ctx->sites_per_tile);
     ++ctx->launches;
     CK(cudaGetLastError());
     return SB_OK;
 }
+static int recount_chain(sb_ctx* ctx, int chain) { return recount_chains(ctx, chain, 1); }
 
 // Upload path: the caller's arrays are packed into a pinned staging buffer (two of them, used alternately, so that
 // packing chain c+1 overlaps the DMA of chain c), every device array is filled by one asynchronous copy from there,
@@ -445,12 +447,11 @@ static int staging_acquire(sb_ctx* ctx, size_t bytes, Staging** out) {
     return SB_OK;
 }
 
-int sb_set_state(sb_ctx* ctx, int chain, const uint8_t* zones, const double* weights, const double* p_global,
-                 const double* p_zones, const double* p_families, const uint8_t* source) {
-    if (!ctx) return SB_E_ARG;
-    CK(cudaSetDevice(ctx->device));
-    int r = check_chain(ctx, chain);
-    if (r != SB_OK) return r;
+// n consecutive chains from arrays stacked along a leading chain axis.  Staging layout = device layout (array-major,
+// per-chain strides st.s_*), so every device array is filled by ONE copy whatever n is.
+static int set_states_impl(sb_ctx* ctx, int chain, int n, const uint8_t* zones, const double* weights,
+                           const double* p_global, const double* p_zones, const double* p_families,
+                           const uint8_t* source) {
     const DevData& d = ctx->d;
     ChainArrays& st = ctx->st;
     const int N = d.N, F = d.F, S = d.S, Z = d.Z, C = d.C, Fam = d.Fam;
@@ -458,85 +459,109 @@ int sb_set_state(sb_ctx* ctx, int chain, const uint8_t* zones, const double* wei
         FAIL(SB_E_ARG, "sb_set_state: missing array");
     if (d.sample_source && !source) FAIL(SB_E_ARG, "sb_set_state: SAMPLE_SOURCE context needs a source array");
 
-    // layout of one chain image in the staging buffer
     const size_t FS = (size_t)F * S;
     const size_t o_zid = 0;
-    const size_t o_mem = align16(o_zid + st.s_zone_id);
-    const size_t o_siz = align16(o_mem + (size_t)Z * N * sizeof(int));
-    const size_t o_w = align16(o_siz + (size_t)(Z > 0 ? Z : 1) * sizeof(int));
-    const size_t o_pg = align16(o_w + (size_t)F * 3 * sizeof(double));
-    const size_t o_pz = o_pg + FS * sizeof(double);
-    const size_t o_pf = o_pz + (size_t)Z * FS * sizeof(double);
-    const size_t o_src = align16(o_pf + (size_t)Fam * FS * sizeof(double));
-    const size_t total = o_src + (d.sample_source ? (size_t)N * d.ldx : 0);
+    const size_t o_mem = align16(o_zid + (size_t)n * st.s_zone_id);
+    const size_t o_siz = align16(o_mem + (size_t)n * st.s_zone_members * sizeof(int));
+    const size_t o_w = align16(o_siz + (size_t)n * st.s_zone_size * sizeof(int));
+    const size_t o_pg = align16(o_w + (size_t)n * st.s_weights * sizeof(double));
+    const size_t o_pz = o_pg + (size_t)n * st.s_p_global * sizeof(double);
+    const size_t o_pf = o_pz + (size_t)n * st.s_p_zones * sizeof(double);
+    const size_t o_src = align16(o_pf + (size_t)n * st.s_p_fam * sizeof(double));
+    const size_t total = o_src + (size_t)n * st.s_source;
     Staging* sg;
-    r = staging_acquire(ctx, total, &sg);
+    int r = staging_acquire(ctx, total, &sg);
     if (r != SB_OK) return r;
     unsigned char* b = sg->buf;
 
-    int8_t* zid = reinterpret_cast<int8_t*>(b + o_zid);
-    int* members = reinterpret_cast<int*>(b + o_mem);
-    int* sizes = reinterpret_cast<int*>(b + o_siz);
-    memset(zid, 0xff, st.s_zone_id);                       // -1
-    for (int z = 0; z < Z; ++z) {
-        int m = 0;
-        const uint8_t* row = zones + (size_t)z * N;
-        int* mrow = members + (size_t)z * N;
-        for (int n = 0; n < N; ++n)
-            if (row[n]) {
-                if (zid[n] >= 0) FAIL(SB_E_OVERLAP, "sb_set_state: zones overlap (a site belongs to two zones)");
-                zid[n] = (int8_t)z;
-                mrow[m++] = n;
-            }
-        for (int n = m; n < N; ++n) mrow[n] = 0;
-        sizes[z] = m;
-    }
-    double* w3 = reinterpret_cast<double*>(b + o_w);
-    for (int f = 0; f < F; ++f)
-        for (int c = 0; c < 3; ++c) w3[(size_t)f * 3 + c] = c < C ? weights[(size_t)f * C + c] : 0.0;
-    memcpy(b + o_pg, p_global, FS * sizeof(double));
-    if (Z > 0) memcpy(b + o_pz, p_zones, (size_t)Z * FS * sizeof(double));
-    if (d.inheritance) memcpy(b + o_pf, p_families, (size_t)Fam * FS * sizeof(double));
-    if (d.sample_source) {
-        unsigned char* hs = b + o_src;
-        unsigned bad = 0;
-        for (int n = 0; n < N; ++n) {
-            const uint8_t* srow = source + (size_t)n * F;
-            unsigned char* drow = hs + (size_t)n * d.ldx;
-            memcpy(drow, srow, (size_t)F);
-            memset(drow + F, 0, (size_t)(d.ldx - F));
-            unsigned char mx = 0;
-            for (int f = 0; f < F; ++f) mx = srow[f] > mx ? srow[f] : mx;      // vectorises (pmaxub)
-            bad |= (unsigned)(mx >= C);
+    for (int c = 0; c < n; ++c) {
+        int8_t* zid = reinterpret_cast<int8_t*>(b + o_zid) + (size_t)c * st.s_zone_id;
+        int* members = reinterpret_cast<int*>(b + o_mem) + (size_t)c * st.s_zone_members;
+        int* sizes = reinterpret_cast<int*>(b + o_siz) + (size_t)c * st.s_zone_size;
+        memset(zid, 0xff, st.s_zone_id);                       // -1
+        sizes[0] = 0;
+        for (int z = 0; z < Z; ++z) {
+            int m = 0;
+            const uint8_t* row = zones + ((size_t)c * Z + z) * N;
+            int* mrow = members + (size_t)z * N;
+            for (int i = 0; i < N; ++i)
+                if (row[i]) {
+                    if (zid[i] >= 0) FAIL(SB_E_OVERLAP, "sb_set_state: zones overlap (a site belongs to two zones)");
+                    zid[i] = (int8_t)z;
+                    mrow[m++] = i;
+                }
+            for (int i = m; i < N; ++i) mrow[i] = 0;
+            sizes[z] = m;
+            ctx->h_zone_size[(size_t)(chain + c) * st.s_zone_size + z] = m;
         }
-        if (bad) FAIL(SB_E_ARG, "sb_set_state: source component out of range");
+        double* w3 = reinterpret_cast<double*>(b + o_w) + (size_t)c * st.s_weights;
+        const double* wc = weights + (size_t)c * F * C;
+        for (int f = 0; f < F; ++f)
+            for (int k = 0; k < 3; ++k) w3[(size_t)f * 3 + k] = k < C ? wc[(size_t)f * C + k] : 0.0;
+        memcpy(b + o_pg + (size_t)c * FS * sizeof(double), p_global + (size_t)c * FS, FS * sizeof(double));
+        if (Z > 0)
+            memcpy(b + o_pz + (size_t)c * Z * FS * sizeof(double), p_zones + (size_t)c * Z * FS, (size_t)Z * FS * sizeof(double));
+        if (d.inheritance)
+            memcpy(b + o_pf + (size_t)c * Fam * FS * sizeof(double), p_families + (size_t)c * Fam * FS,
+                   (size_t)Fam * FS * sizeof(double));
+        if (d.sample_source) {
+            unsigned char* hs = b + o_src + (size_t)c * st.s_source;
+            unsigned bad = 0;
+            for (int i = 0; i < N; ++i) {
+                const uint8_t* srow = source + ((size_t)c * N + i) * F;
+                unsigned char* drow = hs + (size_t)i * d.ldx;
+                memcpy(drow, srow, (size_t)F);
+                memset(drow + F, 0, (size_t)(d.ldx - F));
+                unsigned char mx = 0;
+                for (int f = 0; f < F; ++f) mx = srow[f] > mx ? srow[f] : mx;      // vectorises (pmaxub)
+                bad |= (unsigned)(mx >= C);
+            }
+            if (bad) FAIL(SB_E_ARG, "sb_set_state: source component out of range");
+        }
     }
 
     cudaStream_t sm = ctx->stream;
-    CK(cudaMemcpyAsync(st.zone_id + chain * st.s_zone_id, zid, st.s_zone_id, cudaMemcpyHostToDevice, sm));
+    const size_t nn = (size_t)n;
+    CK(cudaMemcpyAsync(st.zone_id + chain * st.s_zone_id, b + o_zid, nn * st.s_zone_id, cudaMemcpyHostToDevice, sm));
     if (Z > 0) {
-        CK(cudaMemcpyAsync(st.zone_members + chain * st.s_zone_members, members, (size_t)Z * N * sizeof(int),
+        CK(cudaMemcpyAsync(st.zone_members + chain * st.s_zone_members, b + o_mem, nn * st.s_zone_members * sizeof(int),
                            cudaMemcpyHostToDevice, sm));
-        CK(cudaMemcpyAsync(st.zone_size + chain * st.s_zone_size, sizes, (size_t)Z * sizeof(int), cudaMemcpyHostToDevice, sm));
+        CK(cudaMemcpyAsync(st.zone_size + chain * st.s_zone_size, b + o_siz, nn * st.s_zone_size * sizeof(int),
+                           cudaMemcpyHostToDevice, sm));
     }
-    for (int z = 0; z < Z; ++z) ctx->h_zone_size[chain * st.s_zone_size + z] = sizes[z];
-    CK(cudaMemcpyAsync(st.weights + chain * st.s_weights, w3, (size_t)F * 3 * sizeof(double), cudaMemcpyHostToDevice, sm));
-    CK(cudaMemcpyAsync(st.p_global + chain * st.s_p_global, b + o_pg, FS * sizeof(double), cudaMemcpyHostToDevice, sm));
+    CK(cudaMemcpyAsync(st.weights + chain * st.s_weights, b + o_w, nn * st.s_weights * sizeof(double), cudaMemcpyHostToDevice, sm));
+    CK(cudaMemcpyAsync(st.p_global + chain * st.s_p_global, b + o_pg, nn * FS * sizeof(double), cudaMemcpyHostToDevice, sm));
     if (Z > 0)
-        CK(cudaMemcpyAsync(st.p_zones + chain * st.s_p_zones, b + o_pz, (size_t)Z * FS * sizeof(double),
-                           cudaMemcpyHostToDevice, sm));
+        CK(cudaMemcpyAsync(st.p_zones + chain * st.s_p_zones, b + o_pz, nn * Z * FS * sizeof(double), cudaMemcpyHostToDevice, sm));
     if (d.inheritance)
-        CK(cudaMemcpyAsync(st.p_fam + chain * st.s_p_fam, b + o_pf, (size_t)Fam * FS * sizeof(double),
-                           cudaMemcpyHostToDevice, sm));
+        CK(cudaMemcpyAsync(st.p_fam + chain * st.s_p_fam, b + o_pf, nn * Fam * FS * sizeof(double), cudaMemcpyHostToDevice, sm));
     if (d.sample_source)
-        CK(cudaMemcpyAsync(st.source + chain * st.s_source, b + o_src, (size_t)N * d.ldx, cudaMemcpyHostToDevice, sm));
+        CK(cudaMemcpyAsync(st.source + chain * st.s_source, b + o_src, nn * st.s_source, cudaMemcpyHostToDevice, sm));
     CK(cudaEventRecord(sg->done, sm));
     sg->pending = true;
-    dim3 grid((F + 127) / 128, 1);
+    dim3 grid((F + 127) / 128, n);
     wnorm_kernel<<<grid, 128, 0, ctx->stream>>>(d, st, chain);
     ++ctx->launches;
     CK(cudaGetLastError());
-    return recount_chain(ctx, chain);
+    return recount_chains(ctx, chain, n);
+}
+
+int sb_set_state(sb_ctx* ctx, int chain, const uint8_t* zones, const double* weights, const double* p_global,
+                 const double* p_zones, const double* p_families, const uint8_t* source) {
+    if (!ctx) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    int r = check_chain(ctx, chain);
+    if (r != SB_OK) return r;
+    return set_states_impl(ctx, chain, 1, zones, weights, p_global, p_zones, p_families, source);
+}
+
+int sb_set_states(sb_ctx* ctx, int chain_begin, int n_chains, const uint8_t* zones, const double* weights,
+                  const double* p_global, const double* p_zones, const double* p_families, const uint8_t* source) {
+    if (!ctx) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    if (chain_begin < 0 || n_chains < 1 || chain_begin + n_chains > ctx->dims.n_chains) FAIL(SB_E_ARG, "chain range out of bounds");
+    if (!ctx->has_data) FAIL(SB_E_STATE, "sb_upload_data has not been called");
+    return set_states_impl(ctx, chain_begin, n_chains, zones, weights, p_global, p_zones, p_families, source);
 }
 
 int sb_get_state(sb_ctx* ctx, int chain, uint8_t* zones, double* weights, double* p_global, double* p_zones,

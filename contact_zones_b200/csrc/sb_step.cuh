@@ -52,6 +52,16 @@ struct StepParams {
     size_t s_tmp;
 };
 
+// ---- shared scratch of the step kernel -----------------------------------------------------------
+#define STEP_WARPS (STEP_THREADS / 32)
+struct StepShared {
+    double red[33];
+    int redi[33];
+    int pick;           // bits_select result
+    double dshare[4];
+    double wpart[2][2][STEP_WARPS];   // per-warp partial sums of the team reductions (double-buffered pair), read by peers
+};
+
 // ---- site bitmaps in shared memory -----------------------------------------------------------
 __device__ __forceinline__ void bits_clear(unsigned* bits, int nwords) {
     for (int i = threadIdx.x; i < nwords; i += blockDim.x) bits[i] = 0u;
@@ -138,8 +148,7 @@ __device__ void build_nbr_bits(const DevData& d, const int8_t* zone_id, const in
 // traffic: between a write by one CTA and a read of that location by another there is always a team barrier.
 struct Team {
     int rank, size;
-    double* slot;       // StepShared::tslot of this CTA
-    unsigned turn;
+    unsigned turn;      // parity of the reduction buffer (advances identically in every CTA)
 };
 __device__ __forceinline__ void team_sync(const Team& t) {
     if (t.size > 1) cg::this_cluster().sync(); else __syncthreads();
@@ -150,45 +159,49 @@ __device__ __forceinline__ void team_share(const Team& t, int n, int& lo, int& h
     lo = min(n, t.rank * per);
     hi = min(n, lo + per);
 }
-// Sum of a and b over all threads of all CTAs of the team, identical in every thread (fixed order: block tree, then
-// ranks 0..size-1).  Contains one team barrier; everything the CTAs wrote before it is visible after it.
-__device__ void team_exchange(double& a, double& b, double* red, Team& t) {     // a, b: this CTA's block sums
-    double* mine = t.slot + 2 * (t.turn & 1u);
+// Sum of a and b over all threads of `scope` CTAs (1 = this CTA only, else the whole team), identical in every
+// thread: warp tree, then the per-warp partials of all CTAs in fixed (rank, warp) order.  ONE barrier -- for the team
+// scope a cluster barrier, so everything the CTAs wrote before the call is visible to all of them after it.  The
+// partials are double-buffered: a buffer is rewritten two reductions later, after the barrier in between.
+__device__ __forceinline__ void sum2_scope(double& a, double& b, StepShared& sh, Team& t, int scope) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    a = warp_sum(a);
+    b = warp_sum(b);
+    double* slot = &sh.wpart[t.turn & 1u][0][0];
     ++t.turn;
-    if (threadIdx.x == 0) { mine[0] = a; mine[1] = b; }
-    cg::cluster_group cl = cg::this_cluster();
-    cl.sync();
-    if (threadIdx.x < 32) {
-        const int lane = threadIdx.x;
-        double va = 0.0, vb = 0.0;
-        if (lane < t.size) {
-            const double* peer = cl.map_shared_rank(mine, lane);
-            va = peer[0]; vb = peer[1];
+    if (lane == 0) { slot[w] = a; slot[STEP_WARPS + w] = b; }
+    double sa = 0.0, sb = 0.0;
+    if (scope > 1) {
+        cg::cluster_group cl = cg::this_cluster();
+#ifdef SB_RELAXED_BARRIER      // timing experiment only: no release/acquire, hence no L1 invalidation
+        asm volatile("barrier.cluster.arrive.relaxed.aligned;\n" ::: "memory");
+        asm volatile("barrier.cluster.wait.aligned;\n" ::: "memory");
+#else
+        cl.sync();
+#endif
+        for (int r = 0; r < scope; ++r) {
+            const double* peer = cl.map_shared_rank(slot, r);
+            sa += warp_sum(lane < STEP_WARPS ? peer[lane] : 0.0);
+            sb += warp_sum(lane < STEP_WARPS ? peer[STEP_WARPS + lane] : 0.0);
         }
-        double sa = 0.0, sb = 0.0;
-        for (int r = 0; r < t.size; ++r) {
-            sa += __shfl_sync(0xffffffffu, va, r);
-            sb += __shfl_sync(0xffffffffu, vb, r);
-        }
-        if (lane == 0) { red[0] = sa; red[1] = sb; }
+    } else {
+        __syncthreads();
+        sa = warp_sum(lane < STEP_WARPS ? slot[lane] : 0.0);
+        sb = warp_sum(lane < STEP_WARPS ? slot[STEP_WARPS + lane] : 0.0);
     }
-    __syncthreads();
-    a = red[0]; b = red[1];
+    a = sa; b = sb;
 }
-__device__ __forceinline__ void team_sum2(double& a, double& b, double* red, Team& t) {
-    a = block_sum(a, red);
-    b = block_sum(b, red);
-    if (t.size > 1) team_exchange(a, b, red, t);
-}
-__device__ __forceinline__ double team_sum(double v, double* red, Team& t) {
-    v = block_sum(v, red);
-    if (t.size > 1) {
-        double z = 0.0;
-        team_exchange(v, z, red, t);
-    }
+__device__ __forceinline__ void team_sum2(double& a, double& b, StepShared& sh, Team& t) { sum2_scope(a, b, sh, t, t.size); }
+__device__ __forceinline__ double team_sum(double v, StepShared& sh, Team& t) {
+    double z = 0.0;
+    sum2_scope(v, z, sh, t, t.size);
     return v;
 }
-
+__device__ __forceinline__ double cta_sum(double v, StepShared& sh, Team& t) {      // this CTA only
+    double z = 0.0;
+    sum2_scope(v, z, sh, t, 1);
+    return v;
+}
 
 // ---- per-chain view ------------------------------------------------------------------------------
 struct Chain {
@@ -232,7 +245,8 @@ __device__ __forceinline__ double cell_mix(const DevData& d, const Chain& k, int
 // K5a: log marginal-likelihood change of ONE site whose zone assignment changes zid_old -> zid_new
 // (either may be -1).  Sum over features of log mix_new - log mix_old; NA cells contribute 0 in both the
 // source-free likelihood (model.py:247) and the source-marginalised Hastings ratio.
-__device__ double site_zone_delta(const DevData& d, const Chain& k, int site, int zid_old, int zid_new, double* red) {
+__device__ double site_zone_delta(const DevData& d, const Chain& k, int site, int zid_old, int zid_new, StepShared& sh,
+                                  Team& tm) {
     const int fam = d.inheritance ? d.fam_id[site] : -1;
     double acc = 0.0;
     for (int f = threadIdx.x; f < d.F; f += blockDim.x) {
@@ -241,7 +255,7 @@ __device__ double site_zone_delta(const DevData& d, const Chain& k, int site, in
         const double* wrow = k.wn + (size_t)f * 12;
         acc += flog(cell_mix(d, k, f, xs, zid_new, fam, wrow) / cell_mix(d, k, f, xs, zid_old, fam, wrow), k.flt);
     }
-    return block_sum(acc, red);
+    return cta_sum(acc, sh, tm);        // every CTA of the team evaluates the whole delta (F terms) itself
 }
 
 // ---- K7a: resample every source cell from its posterior, rebuild all count tables, return the new
@@ -312,7 +326,7 @@ __device__ double resample_all_sources(const DevData& d, const Chain& k, RngKey 
 // site); the counters of the block's features ([16][S] global, [16][12] source, [Z][16][S] zone, [Fam][16][S] family)
 // live in shared memory, are filled with shared atomics and flushed with plain coalesced stores -- no global atomics,
 // no zeroing pass.  One Philox block serves four cells (32-bit uniforms).
-__device__ double resample_all_sources_blocked(const DevData& d, const Chain& k, RngKey key, uint64_t step, double* red,
+__device__ double resample_all_sources_blocked(const DevData& d, const Chain& k, RngKey key, uint64_t step, StepShared& sh,
                                                int* tab, Team& tm) {
     const int S = d.S, F = d.F, C = d.C, N = d.N;
     const size_t FS = (size_t)F * S;
@@ -399,24 +413,15 @@ __device__ double resample_all_sources_blocked(const DevData& d, const Chain& k,
         }
         __syncthreads();
     }
-    return team_sum(lp_value(acc), red, tm);
+    return team_sum(lp_value(acc), sh, tm);
 }
 
 // (the global-atomics variant is only used by one-CTA teams: sb_set_operators picks team = 1 when the tables do not fit)
-__device__ __forceinline__ double resample_sources(const DevData& d, const Chain& k, RngKey key, uint64_t step, double* red,
-                                                   Team& tm) {
-    return k.cnt_tab ? resample_all_sources_blocked(d, k, key, step, red, k.cnt_tab, tm)
-                     : resample_all_sources(d, k, key, step, red);
+__device__ __forceinline__ double resample_sources(const DevData& d, const Chain& k, RngKey key, uint64_t step,
+                                                   StepShared& sh, Team& tm) {
+    return k.cnt_tab ? resample_all_sources_blocked(d, k, key, step, sh, k.cnt_tab, tm)
+                     : resample_all_sources(d, k, key, step, sh.red);
 }
-
-// ---- shared scratch of the step kernel -----------------------------------------------------------
-struct StepShared {
-    double red[33];
-    int redi[33];
-    int pick;           // bits_select result
-    double dshare[4];
-    double tslot[4];    // this CTA's partial sums of the team reductions (double-buffered pair), read by the peers
-};
 
 // prior terms that depend on the zones: size prior (model.py:932-972) and geo prior (:1096-1139, last zone only)
 __device__ __forceinline__ double size_prior_of(const DevData& d, const int* zsize, int z_changed, int new_size) {
@@ -499,8 +504,8 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
 
     // likelihood ratio of the moved site(s)
     double dll = 0.0;
-    if (site_new >= 0) dll += site_zone_delta(d, k, site_new, -1, z, sh.red);
-    if (site_removed >= 0) dll += site_zone_delta(d, k, site_removed, z, -1, sh.red);
+    if (site_new >= 0) dll += site_zone_delta(d, k, site_new, -1, z, sh, tm);
+    if (site_removed >= 0) dll += site_zone_delta(d, k, site_removed, z, -1, sh, tm);
 
     // prior ratio: only the size and geo terms depend on the zones
     const int new_size = size + (site_new >= 0 ? 1 : 0) - (site_removed >= 0 ? 1 : 0);
@@ -548,7 +553,7 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
     synced = true;
     prior += dprior;
     geo = geo_new;
-    if (d.sample_source) ll = resample_sources(d, k, key, step, sh.red, tm);      // :859-862 (on accept only)
+    if (d.sample_source) ll = resample_sources(d, k, key, step, sh, tm);          // :859-862 (on accept only)
     else ll += dll;
     return true;
 }
@@ -618,7 +623,7 @@ __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, u
         if (n > 0 && nw != old) dll += (double)n * flog(nw / old, k.flt);
         k.wn[o] = nw;
     }
-    ll += team_sum(dll, sh.red, tm);
+    ll += team_sum(dll, sh, tm);
 }
 
 // Shared body of gibbs_sample_p_global / p_zones / p_families (zone_sampling.py:334-406):
@@ -635,6 +640,56 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
     team_share(tm, d.F, f_lo, f_hi);                    // whole rows per CTA: the row totals stay CTA-local
     const int i_lo = f_lo * S, i_hi = f_hi * S;
     PROF_T(t0);
+    double dll = 0.0, dpr = 0.0;
+    const int bd = blockDim.x;
+    constexpr int R = 4;                                 // items per thread held in registers
+    if (tm.size > 1 && i_hi - i_lo <= R * bd) {
+        // Fast path: a thread's (feature, state) items stay in registers across the phases, and everything it needs
+        // from global memory (counts, prior pseudo-counts, old probabilities) is requested up front in one batch --
+        // after a team barrier these loads come from L2, and one overlapped round trip replaces several serial ones.
+        int fi[R], ci[R];
+        double al[R], po[R];
+        bool app[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int i = i_lo + (int)threadIdx.x + r * bd;
+            const bool in = i < i_hi;
+            fi[r] = in ? (int)__umulhi((unsigned)i, sp.s_magic) : f_lo;
+            app[r] = in && (d.app_mask[fi[r]] >> (i - fi[r] * S) & 1u);
+            ci[r] = app[r] ? cnt[i] : 0;
+            al[r] = (app[r] && pc) ? pc[i] : 1.0;
+            po[r] = app[r] ? p[i] : 1.0;
+        }
+        // phase 0: feature subset (one draw per feature); marker -1 in the feature's first scratch slot = not selected
+        for (int f = f_lo + threadIdx.x; f < f_hi; f += bd)
+            k.scratch[(size_t)f * S] = (use_subset && !(rng_uniform(key, step, RP_SUBSET, f) < sp.frac)) ? -1.0 : 0.0;
+        __syncthreads();
+        // phase 1: Gamma draws (a selected feature's first slot only ever holds values >= 0, so the test is stable)
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int i = i_lo + (int)threadIdx.x + r * bd;
+            if (i >= i_hi || k.scratch[(size_t)fi[r] * S] < 0.0) continue;
+            k.scratch[i] = app[r] ? rng_gamma(key, step, RP_GAMMA, i, al[r] + (double)ci[r]) : 0.0;
+        }
+        PROF_T(t1);
+        __syncthreads();
+        PROF_T(t2);
+        // phase 2: normalise, write, accumulate the likelihood delta; the S threads of a row each form the row total
+        // in the same order, so they agree bit for bit
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int i = i_lo + (int)threadIdx.x + r * bd;
+            const double* g = k.scratch + (size_t)fi[r] * S;
+            if (!app[r] || g[0] < 0.0) continue;
+            double tot = 0.0;
+            for (int t = 0; t < S; ++t) tot += g[t];
+            const double pn = g[i - fi[r] * S] / tot;
+            if (ci[r] > 0) dll += (double)ci[r] * flog(pn / po[r], k.flt);
+            p[i] = pn;
+        }
+        PROF_T(t3);
+        PROF_ADD(0, t0, t1); PROF_ADD(1, t1, t2); PROF_ADD(2, t2, t3);
+    } else {
     // phase 0: feature subset (one draw per feature); marker -1 in the feature's first scratch slot = not selected
     for (int f = f_lo + threadIdx.x; f < f_hi; f += blockDim.x)
         k.scratch[(size_t)f * S] = (use_subset && !(rng_uniform(key, step, RP_SUBSET, f) < sp.frac)) ? -1.0 : 0.0;
@@ -648,12 +703,8 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
             g = rng_gamma(key, step, RP_GAMMA, i, (pc ? pc[i] : 1.0) + (double)cnt[i]);
         k.scratch[i] = g;
     }
-    PROF_T(t1);
     __syncthreads();
-    PROF_T(t2);
-    // phase 2: normalise, write, accumulate the likelihood delta -- one thread per (feature, state); the S threads of a
-    // row each form the row total in the same order, so they agree bit for bit
-    double dll = 0.0, dpr = 0.0;
+    // phase 2: normalise, write, accumulate the likelihood delta -- one thread per (feature, state)
     for (int i = i_lo + threadIdx.x; i < i_hi; i += blockDim.x) {
         const int f = (int)__umulhi((unsigned)i, sp.s_magic), s = i - f * S;
         const double* g = k.scratch + (size_t)f * S;
@@ -665,6 +716,7 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
         if (c > 0) dll += (double)c * flog(pn / p[i], k.flt);
         p[i] = pn;
     }
+    }
     if (alpha) {
         __syncthreads();
         for (int f = f_lo + threadIdx.x; f < f_hi; f += blockDim.x) {
@@ -674,16 +726,16 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
             pcache[f] = v;
         }
     }
-    PROF_T(t3);
+    PROF_T(t3b);
     if (alpha) {
-        team_sum2(dll, dpr, sh.red, tm);
+        team_sum2(dll, dpr, sh, tm);
         ll += dll;
         prior += dpr;
     } else {
-        ll += team_sum(dll, sh.red, tm);
+        ll += team_sum(dll, sh, tm);
     }
     PROF_T(t4);
-    PROF_ADD(0, t0, t1); PROF_ADD(1, t1, t2); PROF_ADD(2, t2, t3); PROF_ADD(3, t3, t4);
+    PROF_ADD(3, t3b, t4);
 }
 
 // ---- K7d: alter_* operators (source-free mode), zone_sampling.py:408-612 --------------------------
@@ -724,7 +776,7 @@ __device__ __forceinline__ int nth_state(uint32_t mask, int j) {
 // weight row (wrow_new) or one probability row (which = 0 global / 1 zone z / 2 family fam; states s0,s1 -> v0,v1).
 __device__ double column_delta(const DevData& d, const Chain& k, int f, const int* sites, int n_sites,
                                const double* wrow_new, int which, int tab, int s0, int s1, double v0, double v1,
-                               double* red, Team& tm) {
+                               StepShared& sh, Team& tm) {
     const double* wrow = k.wn + (size_t)f * 12;
     const size_t FS = (size_t)d.F * d.S;
     double acc = 0.0;
@@ -756,7 +808,7 @@ __device__ double column_delta(const DevData& d, const Chain& k, int f, const in
         }
         acc += flog(nw / old, k.flt);
     }
-    return team_sum(acc, red, tm);      // barrier: every read of the old state (the callers read before calling) is done
+    return team_sum(acc, sh, tm);       // barrier: every read of the old state (the callers read before calling) is done
 }
 
 // alter_weights / alter_p_global / alter_p_zones / alter_p_families (zone_sampling.py:408-612). Returns accepted.
@@ -776,7 +828,7 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
             wnorm_row(v, wrow_new, d.C);
         }
         __syncthreads();
-        dll = column_delta(d, k, f, nullptr, d.N, wrow_new, -1, 0, 0, 0, 0.0, 0.0, sh.red, tm);
+        dll = column_delta(d, k, f, nullptr, d.N, wrow_new, -1, 0, 0, 0, 0.0, 0.0, sh, tm);
         const bool accept = flog(rng_uniform(key, step, RP_ACCEPT, 0), k.flt) < dll - lqr;
         synced = !accept;       // a rejected proposal wrote nothing after the reduction's barrier
         if (accept) {
@@ -828,7 +880,7 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
         new_prior_term = t;
         dprior = t - *pcache;
     }
-    dll = column_delta(d, k, f, sites, n_sites, nullptr, which, tab, s0, s1, n0, n1, sh.red, tm);
+    dll = column_delta(d, k, f, sites, n_sites, nullptr, which, tab, s0, s1, n0, n1, sh, tm);
     const bool accept = flog(rng_uniform(key, step, RP_ACCEPT, 0), k.flt) < dll - lqr + dprior;
     synced = !accept;
     if (accept) {
@@ -850,7 +902,7 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
     extern __shared__ unsigned char step_smem[];
     __shared__ StepShared sh;
     const int chain = blockIdx.x / sp.team;             // one cluster of sp.team CTAs per chain (cluster dims (team,1,1))
-    Team tm = {(int)(blockIdx.x % sp.team), sp.team, sh.tslot, 0u};
+    Team tm = {(int)(blockIdx.x % sp.team), sp.team, 0u};
     unsigned* nbr = reinterpret_cast<unsigned*>(step_smem);
     unsigned* freeb = nbr + sp.nwords;
     double* prim_key = reinterpret_cast<double*>(freeb + sp.nwords + (sp.nwords & 1));
@@ -886,7 +938,7 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
                                         prim_tree, sh, tm, synced);
                 break;
             case SB_OP_GIBBS_SOURCES:
-                ll = resample_sources(d, k, key, step, sh.red, tm);
+                ll = resample_sources(d, k, key, step, sh, tm);
                 synced = true;
                 break;
             case SB_OP_GIBBS_WEIGHTS:
@@ -919,7 +971,8 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
                 break;
         }
         PROF_T(ts2);
-        if (threadIdx.x == 0 && tm.rank == 0) ++(accepted ? st.acc : st.rej)[(size_t)chain * SB_N_OPS + op];
+        if (threadIdx.x == 0 && tm.rank == 0)      // fire-and-forget reduction: nobody waits for the L2 round trip
+            atomicAdd((accepted ? st.acc : st.rej) + (size_t)chain * SB_N_OPS + op, 1ull);
         // step boundary: the next step's writes must not overtake this step's reads in a slower CTA of the team
         if (synced) __syncthreads(); else team_sync(tm);
         PROF_T(ts3);

@@ -138,6 +138,24 @@ class Engine:
             raise ValueError('a SAMPLE_SOURCE engine needs a source array')
         self._check(self.lib.sb_set_state(self._ctx, int(chain), ptr(zones), ptr(w), ptr(pg), ptr(pz), ptr(pf), ptr(src)))
 
+    def set_states(self, chain_begin, zones, weights, p_global, p_zones, p_families=None, source=None):
+        """Bulk form of `set_state`: arrays stacked along a leading chain axis, one call for all of them."""
+        zones = np.asarray(zones)
+        n = zones.shape[0]
+        zones = as_c(zones.reshape(n, self.Z, self.N), np.uint8)
+        w = as_c(np.asarray(weights).reshape(n, self.F, self.C), np.float64)
+        pg = as_c(np.asarray(p_global).reshape(n, self.F, self.S), np.float64)
+        pz = as_c(np.asarray(p_zones).reshape(n, self.Z, self.F, self.S), np.float64)
+        pf = as_c(np.asarray(p_families).reshape(n, self.Fam, self.F, self.S), np.float64) if self.inheritance else None
+        src = None
+        if self.sample_source:
+            if source is None:
+                raise ValueError('a SAMPLE_SOURCE engine needs a source array')
+            source = np.asarray(source)
+            src = as_c(np.argmax(source, axis=-1) if source.ndim == 4 else source, np.uint8).reshape(n, self.N, self.F)
+        self._check(self.lib.sb_set_states(self._ctx, int(chain_begin), int(n), ptr(zones), ptr(w), ptr(pg), ptr(pz),
+                                           ptr(pf), ptr(src)))
+
     def get_state(self, chain, one_hot_source=True, fields=None):
         """Device image of chain -> the `Sample` arrays.  `fields` limits the read-back (e.g. ('zones', 'weights'))."""
         want = (lambda k: fields is None or k in fields)

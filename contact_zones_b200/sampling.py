@@ -354,8 +354,13 @@ class ZoneMCMC(object):
     def _initialise_chains(self):
         """Initial samples of this rank's chains -> device; the initial source sweep runs on all chains at once."""
         eng = self._open_engine()
-        for lc in range(self.shard.n_local):
-            _dev.upload_sample(eng, lc, self._initial_sample_host(self.shard.offset + lc))
+        smp = [self._initial_sample_host(self.shard.offset + lc) for lc in range(self.shard.n_local)]
+        if smp:      # one bulk upload (sb_set_states); the sources are redrawn on the device right below
+            eng.set_states(0, np.stack([s.zones for s in smp]), np.stack([s.weights for s in smp]),
+                           np.stack([s.p_global for s in smp]), np.stack([s.p_zones for s in smp]),
+                           np.stack([s.p_families for s in smp]) if self.inheritance else None,
+                           np.zeros((len(smp), self.n_sites, self.n_features), np.uint8)
+                           if self.model.sample_source else None)
         if self.model.sample_source:          # the reference always redraws the sources (zone_sampling.py:1226-1231)
             self._source_sweep(eng, seed=self.seed ^ 0x5DEECE66D)
         eng.eval()

@@ -120,6 +120,11 @@ int sb_set_priors(sb_ctx* ctx, const sb_prior_cfg* cfg,
 /* ---- per-chain state: the device image of a `Sample` (zone_sampling.py:49-115) ------------------ */
 int sb_set_state(sb_ctx* ctx, int chain, const uint8_t* zones, const double* weights, const double* p_global,
                  const double* p_zones, const double* p_families, const uint8_t* source /* or NULL */);
+/* n_chains consecutive chains in one call: the same arrays stacked along a leading chain axis (C-contiguous).  One
+ * host->device copy per device array whatever n_chains is -- the bulk form of `for c in chains: generate_initial_sample`
+ * (mcmc_generative.py:166-171). */
+int sb_set_states(sb_ctx* ctx, int chain_begin, int n_chains, const uint8_t* zones, const double* weights,
+                  const double* p_global, const double* p_zones, const double* p_families, const uint8_t* source);
 int sb_get_state(sb_ctx* ctx, int chain, uint8_t* zones, double* weights, double* p_global,
                  double* p_zones, double* p_families, uint8_t* source /* any may be NULL */);
 int sb_copy_state(sb_ctx* ctx, int dst_chain, int src_chain);

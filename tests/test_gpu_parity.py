@@ -169,3 +169,47 @@ def test_large_shape_properties(built_lib):
     assert np.array_equal(cnt['cnt_fam'][7], orc.state_counts_family(data.features, st['source'], fam[7]))
     assert np.array_equal(cnt['cnt_src_fam'], orc.source_counts(st['source'], fam.any(0)))
     eng.close()
+
+
+def test_bulk_upload_equals_single_uploads(built_lib):
+    """sb_set_states (arrays stacked along the chain axis) == sb_set_state chain by chain: identical evaluation,
+    count tables and read-back."""
+    from contact_zones_b200 import synthetic
+    c = load_case('C_samerica_like')
+    g = c['g']
+    data_ns = type('D', (), {})()
+    rng = np.random.default_rng(4)
+    n = 5
+    zones, src = [], []
+    for i in range(n):
+        z = np.zeros_like(g['zones'])
+        perm = rng.permutation(c['N'])
+        for k in range(c['Z']):
+            z[k, perm[k * 6:(k + 1) * 6]] = True
+        zones.append(z)
+        s = rng.integers(0, c['C'], size=(c['N'], c['F'])).astype(np.uint8)
+        s[~z.any(axis=0)] = np.where(s[~z.any(axis=0)] == 1, 0, s[~z.any(axis=0)])          # no zone -> not contact
+        s[~c['families'].any(axis=0)] = np.where(s[~c['families'].any(axis=0)] == 2, 0, s[~c['families'].any(axis=0)])
+        src.append(s)
+    w = rng.dirichlet(np.ones(c['C']), size=(n, c['F']))
+    pg = np.stack([g['p_global'][0]] * n)
+    pz = np.stack([g['p_zones'][rng.permutation(c['Z'])] for _ in range(n)])
+    pf = np.stack([c['p_families']] * n)
+    a = make_engine(c, n_chains=n)
+    b = make_engine(c, n_chains=n)
+    a.set_states(0, np.stack(zones), w, pg, pz, pf, np.stack(src))
+    for i in range(n):
+        b.set_state(i, zones[i], w[i], pg[i], pz[i], pf[i], src[i])
+    ra, rb = a.eval(), b.eval()
+    for x, y in zip(ra, rb):
+        assert np.array_equal(x, y)
+    assert len(set(np.round(ra[0], 6))) == n                       # the chains really differ
+    for i in (0, n - 1):
+        ca, cb = a.counts(i), b.counts(i)
+        for k in ca:
+            assert np.array_equal(ca[k], cb[k]), k
+        sa, sb = a.get_state(i), b.get_state(i)
+        for k in sa:
+            assert np.array_equal(sa[k], sb[k]), k
+        assert np.array_equal(sa['zones'], zones[i]) and np.array_equal(np.argmax(sa['source'], -1), src[i])
+    a.close(); b.close()
