@@ -13,6 +13,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 // pinned upload staging buffer of sb_set_state
@@ -474,7 +475,9 @@ static int set_states_impl(sb_ctx* ctx, int chain, int n, const uint8_t* zones, 
     if (r != SB_OK) return r;
     unsigned char* b = sg->buf;
 
-    for (int c = 0; c < n; ++c) {
+    // packing is host memory bandwidth: spread the chains over a few threads when there are many
+    std::vector<int> h_sizes((size_t)n * st.s_zone_size, 0);
+    auto pack = [&](int c) -> int {
         int8_t* zid = reinterpret_cast<int8_t*>(b + o_zid) + (size_t)c * st.s_zone_id;
         int* members = reinterpret_cast<int*>(b + o_mem) + (size_t)c * st.s_zone_members;
         int* sizes = reinterpret_cast<int*>(b + o_siz) + (size_t)c * st.s_zone_size;
@@ -486,13 +489,13 @@ static int set_states_impl(sb_ctx* ctx, int chain, int n, const uint8_t* zones, 
             int* mrow = members + (size_t)z * N;
             for (int i = 0; i < N; ++i)
                 if (row[i]) {
-                    if (zid[i] >= 0) FAIL(SB_E_OVERLAP, "sb_set_state: zones overlap (a site belongs to two zones)");
+                    if (zid[i] >= 0) return SB_E_OVERLAP;
                     zid[i] = (int8_t)z;
                     mrow[m++] = i;
                 }
             for (int i = m; i < N; ++i) mrow[i] = 0;
             sizes[z] = m;
-            ctx->h_zone_size[(size_t)(chain + c) * st.s_zone_size + z] = m;
+            h_sizes[(size_t)c * st.s_zone_size + z] = m;
         }
         double* w3 = reinterpret_cast<double*>(b + o_w) + (size_t)c * st.s_weights;
         const double* wc = weights + (size_t)c * F * C;
@@ -516,9 +519,31 @@ static int set_states_impl(sb_ctx* ctx, int chain, int n, const uint8_t* zones, 
                 for (int f = 0; f < F; ++f) mx = srow[f] > mx ? srow[f] : mx;      // vectorises (pmaxub)
                 bad |= (unsigned)(mx >= C);
             }
-            if (bad) FAIL(SB_E_ARG, "sb_set_state: source component out of range");
+            if (bad) return SB_E_ARG;
         }
+        return SB_OK;
+    };
+
+    int status = SB_OK;
+    const int n_thr = std::min<int>({n / 4, 8, (int)std::max(1u, std::thread::hardware_concurrency())});
+    if (n_thr <= 1) {
+        for (int c = 0; c < n && status == SB_OK; ++c) status = pack(c);
+    } else {
+        std::vector<int> rc(n_thr, SB_OK);
+        std::vector<std::thread> pool;
+        for (int t = 0; t < n_thr; ++t)
+            pool.emplace_back([&, t]() {
+                for (int c = t; c < n; c += n_thr) {
+                    const int e = pack(c);
+                    if (e != SB_OK) { rc[t] = e; return; }
+                }
+            });
+        for (auto& th : pool) th.join();
+        for (int e : rc) if (e != SB_OK) status = e;
     }
+    if (status == SB_E_OVERLAP) FAIL(SB_E_OVERLAP, "sb_set_state: zones overlap (a site belongs to two zones)");
+    if (status != SB_OK) FAIL(SB_E_ARG, "sb_set_state: source component out of range");
+    for (size_t i = 0; i < h_sizes.size(); ++i) ctx->h_zone_size[(size_t)chain * st.s_zone_size + i] = h_sizes[i];
 
     cudaStream_t sm = ctx->stream;
     const size_t nn = (size_t)n;
