@@ -39,7 +39,10 @@ def engine_for(data, n_zones, inheritance, sample_source, n_chains=1, with_cost=
     states = getattr(data, 'states', None)       # test/test_model.py:76-80 passes a stub with features + families only
     if states is None:
         states = np.ones(np.asarray(data.features).shape[1:], dtype=bool)
-    eng = Engine(data.features, states, data.families if inheritance else None, adj, cost,
+    feats = getattr(data, 'features_idx', None)        # uint8 state index straight from the encoder (data.py)
+    if feats is None:
+        feats = data.features
+    eng = Engine(feats, states, data.families if inheritance else None, adj, cost,
                  n_zones=n_zones, n_chains=n_chains, inheritance=inheritance, sample_source=sample_source, warmup=warmup,
                  device=device, chain_offset=chain_offset)
     eng.prior_token = None

@@ -123,7 +123,10 @@ class ZoneMCMC(object):
         self.n_states_by_feature = np.sum(data.states, axis=-1)
         self.network = data.network
         self.adj_mat = self.network['adj_mat']
-        self.locations = self.network.get('locations') if isinstance(self.network, dict) else None
+        try:
+            self.locations = self.network['locations']
+        except (KeyError, AttributeError, TypeError):
+            self.locations = None
         self.p_grow_connected = p_grow_connected
         self.min_size, self.max_size = model.min_size, model.max_size
         self.initial_size = initial_size

@@ -100,3 +100,26 @@ def test_mcmc_facade_writes_reference_files(built_lib, tmp_path):
     assert abs(float(row['posterior']) - float(row['likelihood']) - float(row['prior'])) < 1e-6
     z = parse_area_columns(areas[0])
     assert z.shape == (c['Z'], c['N']) and int(row['size_a0']) == z[0].sum()
+
+
+def test_cli_end_to_end(built_lib, tmp_path):
+    """`python -m contact_zones_b200 config.json` on a CSV dataset: counts priors, cost-based geo prior from a cost
+    file, inheritance, warm-up, sampling, result files (sbayes/cli.py:30-84)."""
+    from test_data_loading import write_dataset
+    from contact_zones_b200.cli import main
+    from contact_zones_b200.results import parse_area_columns
+    write_dataset(tmp_path, n=60, seed=3)
+    last = main(config=tmp_path / 'config.json', experiment_name='cli_run', custom_settings={'mcmc': {'SEED': 4}})
+    out = tmp_path / 'results' / 'cli_run'
+    assert (out / 'experiment.log').exists()
+    stats = (out / 'n2' / 'stats_n2_0.txt').read_text().splitlines()
+    areas = (out / 'n2' / 'areas_n2_0.txt').read_text().splitlines()
+    assert len(stats) == 5 and len(areas) == 4
+    hdr = stats[0].split('\t')
+    assert 'w_inheritance_f_bin' in hdr and 'alpha_f_tri_c' in hdr and 'gamma_a2_f_four_z' in hdr and 'beta_Beta_f_col_red' in hdr
+    z = parse_area_columns(areas[-1])
+    assert z.shape == (2, 60) and (z.sum(axis=1) >= 3).all() and (z.sum(axis=0) <= 1).all()
+    vals = [dict(zip(hdr, r.split('\t'))) for r in stats[1:]]
+    assert all(np.isfinite(float(v['likelihood'])) and np.isfinite(float(v['prior'])) for v in vals)
+    assert float(vals[0]['prior']) != 0.0                                  # counts + cost-based priors are active
+    assert last.zones.shape == (2, 60) and last.source.shape == (60, 4, 3)
