@@ -1,0 +1,123 @@
+"""GPU: structural invariants of the step kernel K8 through the C ABI.
+
+* every operator on its own keeps the incrementally maintained log-likelihood / log-prior / count tables equal to a
+  from-scratch evaluation (K1, K2, K3, K4) and the zone book-keeping consistent (disjoint zones, MIN_M <= size <= MAX_M);
+* a chain's trajectory depends on (seed, global chain id) only -- not on how chains are sharded over contexts;
+* teams of 1, 2 and 4 CTAs per chain (thread-block clusters) walk the same trajectory: the team size only changes the
+  order of fp64 partial sums (1e-16 relative), which cannot flip an accept decision within a few hundred steps."""
+import os
+
+import numpy as np
+import pytest
+
+from helpers import PRECISION, load_case, make_engine, set_golden_state
+
+pytestmark = pytest.mark.gpu
+
+GIBBS = ['gibbs_sample_sources', 'gibbs_sample_weights', 'gibbs_sample_p_global', 'gibbs_sample_p_zones',
+         'gibbs_sample_p_families']
+ALTER = ['alter_weights', 'alter_p_global', 'alter_p_zones', 'alter_p_families']
+ZONE = ['grow_zone', 'shrink_zone', 'swap_zone']
+
+
+def check_consistency(eng, c, n_chains, sample_source, min_size, max_size):
+    ll_run, pr_run = eng.chain_scalars()
+    cnt_run = [eng.counts(ch, recount=False) for ch in range(n_chains)] if sample_source else None
+    ll_new, pr_new, _ = eng.eval()
+    assert np.allclose(ll_run, ll_new, rtol=1e-9), (ll_run, ll_new)
+    assert np.allclose(pr_run, pr_new, rtol=1e-9, atol=1e-9), (pr_run, pr_new)
+    for ch in range(n_chains):
+        z = eng.get_state(ch, fields=('zones',))['zones']
+        assert (z.sum(axis=0) <= 1).all()
+        assert (z.sum(axis=1) >= min(min_size, c['g']['zones'].sum(1).min())).all() and (z.sum(axis=1) <= max_size).all()
+        if sample_source:
+            new = eng.counts(ch, recount=True)
+            for k in new:
+                if new[k] is not None:
+                    assert np.array_equal(cnt_run[ch][k], new[k]), (ch, k)
+
+
+@pytest.mark.parametrize('name', ['B_balkan_like', 'D_small'])
+@pytest.mark.parametrize('sample_source', [True, False])
+def test_each_operator_keeps_running_values_exact(name, sample_source, built_lib):
+    c = load_case(name)
+    n_chains = 3
+    eng = make_engine(c, n_chains=n_chains, sample_source=sample_source)
+    for ch in range(n_chains):
+        set_golden_state(eng, c, ch, with_source=sample_source)
+    eng.eval()
+    ops = ZONE + (GIBBS if sample_source else ALTER)
+    if not c['inheritance']:
+        ops = [o for o in ops if 'families' not in o]
+    for i, op in enumerate(ops):
+        eng.set_operators({op: 1.0}, PRECISION, min_size=3, max_size=25, p_grow_connected=0.85, seed=100 + i)
+        eng.run(40 if op == 'gibbs_sample_sources' else 300)
+        check_consistency(eng, c, n_chains, sample_source, 3, 25)
+    acc, rej = eng.op_stats()
+    from contact_zones_b200 import _lib
+    tot = acc + rej
+    for op in ops:
+        assert (tot[:, _lib.OP_IDS[op]] == (40 if op == 'gibbs_sample_sources' else 300)).all(), op
+    for op in GIBBS:
+        if op in ops:
+            assert (rej[:, _lib.OP_IDS[op]] == 0).all()              # Gibbs operators are always accepted
+    for op in ('grow_zone', 'swap_zone', 'alter_p_zones'):
+        if op in ops:
+            assert acc[:, _lib.OP_IDS[op]].sum() > 0, op                 # ... and the MH ones do move
+    eng.close()
+
+
+def _run_chains(c, n_chains, chain_offset, steps, ops, sample_source=True, team=None):
+    old = os.environ.get('SBAYES_B200_TEAM')
+    if team is not None:
+        os.environ['SBAYES_B200_TEAM'] = str(team)
+    try:
+        eng = make_engine(c, n_chains=n_chains, sample_source=sample_source, chain_offset=chain_offset)
+        for ch in range(n_chains):
+            set_golden_state(eng, c, ch, with_source=sample_source)
+        eng.eval()
+        eng.set_operators(ops, PRECISION, min_size=3, max_size=25, p_grow_connected=0.85, seed=77)
+        eng.run(steps)
+        out = [eng.get_state(ch, one_hot_source=False) for ch in range(n_chains)]
+        ll, pr = eng.chain_scalars()
+        eng.close()
+        return out, ll, pr
+    finally:
+        if team is not None:
+            if old is None:
+                os.environ.pop('SBAYES_B200_TEAM', None)
+            else:
+                os.environ['SBAYES_B200_TEAM'] = old
+
+
+MIX = {'shrink_zone': 0.1, 'grow_zone': 0.1, 'swap_zone': 0.05, 'gibbs_sample_weights': 0.3, 'gibbs_sample_p_global': 0.1,
+       'gibbs_sample_p_zones': 0.25, 'gibbs_sample_p_families': 0.1}
+
+
+def test_trajectories_do_not_depend_on_sharding(built_lib):
+    c = load_case('D_small')
+    full, ll_f, _ = _run_chains(c, 4, 0, 400, MIX, team=2)
+    part, ll_p, _ = _run_chains(c, 2, 2, 400, MIX, team=2)
+    assert np.array_equal(ll_f[2:], ll_p)
+    for a, b in zip(full[2:], part):
+        for k in a:
+            if a[k] is not None:
+                assert np.array_equal(a[k], b[k]), k
+    assert not np.array_equal(full[0]['zones'], full[1]['zones'])         # different chains do differ
+
+
+@pytest.mark.parametrize('sample_source', [True, False])
+def test_team_sizes_walk_the_same_trajectory(sample_source, built_lib):
+    c = load_case('D_small')
+    ops = MIX if sample_source else {'shrink_zone': 0.1, 'grow_zone': 0.1, 'swap_zone': 0.05, 'alter_weights': 0.3,
+                                     'alter_p_global': 0.1, 'alter_p_zones': 0.25, 'alter_p_families': 0.1}
+    ref, ll_ref, pr_ref = _run_chains(c, 2, 0, 300, ops, sample_source, team=1)
+    for team in (2, 4):
+        got, ll, pr = _run_chains(c, 2, 0, 300, ops, sample_source, team=team)
+        assert np.allclose(ll, ll_ref, rtol=1e-10) and np.allclose(pr, pr_ref, rtol=1e-10, atol=1e-10), team
+        for a, b in zip(ref, got):
+            assert np.array_equal(a['zones'], b['zones']), team
+            if sample_source:
+                assert np.array_equal(a['source'], b['source']), team
+            assert np.allclose(a['p_zones'], b['p_zones'], rtol=1e-12, atol=0), team
+            assert np.allclose(a['weights'], b['weights'], rtol=1e-12, atol=0), team
