@@ -99,6 +99,26 @@ def cpu_measure(pool, cores, proposals_per_proc):
     return cores * proposals_per_proc / dt, dt
 
 
+def cpu_likelihood(n_eval=3):
+    """One full likelihood evaluation (Likelihood.__call__(caching=False), model.py:145-184, as restated by the oracle)
+    of ONE chain on the roofline shape E at N=20000, single thread -- SURVEY.md 8(d)."""
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+    import sbayes_oracle as orc                  # checker / CPU baseline only
+    from contact_zones_b200 import synthetic
+    e = E_SHAPE
+    data = synthetic.make_data(e['N'], e['F'], e['S'], n_families=0, seed=2, with_dist=False)
+    st = synthetic.random_state(data, e['Z'], e['zone_size'], False, False, seed=10)
+    fam = np.zeros((0, e['N']), bool)
+    best = float('inf')
+    for _ in range(n_eval):
+        t0 = time.perf_counter()
+        orc.log_likelihood(data.features, fam, False, st['zones'], st['weights'], st['p_global'], st['p_zones'], None)
+        best = min(best, time.perf_counter() - t0)
+    nbytes = b_lh(e['N'], e['F'], e['S'], e['Z'], 0, 2, 0, 0)
+    return {'likelihood_eval_ms': 1e3 * best, 'likelihood_gbs': nbytes / best / 1e9,
+            'likelihood_sample': f'1 chain x {e["N"]} x {e["F"]} x {e["S"]}, 1 thread, best of {n_eval}'}
+
+
 def cpu_name():
     try:
         for line in open('/proc/cpuinfo'):
@@ -270,6 +290,7 @@ def run_gpu_arm(args, rank, world, local_rank):
         cpu = {'value': v, 'unit': 'proposals/s', 'cores': cores, 'kind': 'port', 'cpu': cpu_name(),
                'sample': f'{cores} processes x 1 chain x {args.cpu_proposals} proposals on shape D in {dt:.1f} s '
                          f'(oracle port of ZoneMCMC.step)'}
+        cpu.update(cpu_likelihood())
 
     torch.cuda.set_device(local_rank)
     if world > 1:

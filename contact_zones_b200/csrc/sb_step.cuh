@@ -17,6 +17,7 @@
 namespace cg = cooperative_groups;
 
 #define STEP_THREADS 512
+#define SB_W_STRIDE 24        // scratch doubles per feature in op_gibbs_weights: 3 new w | 10 old w~ | 10 counts
 
 // optional phase timing (build with -DSB_PROF): cycles of CTA 0 / thread 0 accumulated per marker
 #ifdef SB_PROF
@@ -580,28 +581,45 @@ __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, u
     const int a = (d.C == 2) ? 1 : (fixed_inheritance ? 1 : 2);   // cfg of the "only this component" sites; also column x
     int f_lo, f_hi;
     team_share(tm, d.F, f_lo, f_hi);                    // each CTA of the team owns a contiguous range of features
+    // Everything a feature needs from global memory (its 12 source counts, 3 weights, 12 old normalised weights) is
+    // requested in one batch at the top; the live entries are staged in the scratch (stride SB_W_STRIDE doubles per
+    // feature: new weights | old w~ | counts), so phase C touches global memory only to store.
     for (int f = f_lo + threadIdx.x; f < f_hi; f += blockDim.x) {
-        const int* cs = k.cs + (size_t)f * 12;
+        const int4* cs4 = reinterpret_cast<const int4*>(k.cs + (size_t)f * 12);
+        const int4 ca = cs4[0], cb = cs4[1], cc = cs4[2];
+        const int cs[12] = {ca.x, ca.y, ca.z, ca.w, cb.x, cb.y, cb.z, cb.w, cc.x, cc.y, cc.z, cc.w};
+        double* w = k.w + (size_t)f * 3;
+        double v[3] = {w[0], w[1], d.C == 3 ? w[2] : 0.0};
+        const double2* wn2 = reinterpret_cast<const double2*>(k.wn + (size_t)f * 12);
+        double* stage = k.scratch + (size_t)f * SB_W_STRIDE;
+#pragma unroll
+        for (int q = 1; q < 6; ++q) {                       // entries 2..11 (entries 0..2 = cfg 0 are constant)
+            const double2 t = wn2[q];
+            stage[3 + 2 * q - 2] = t.x;                     // old w~[idx] at stage[3 + idx - 2]
+            stage[3 + 2 * q - 1] = t.y;
+        }
+#pragma unroll
+        for (int i = 2; i < 12; ++i) stage[13 + i - 2] = (double)cs[i];       // counts at stage[13 + idx - 2]
         int c0, c1;
         if (d.C == 2) { c0 = cs[3 + 0]; c1 = cs[3 + 1]; }                  // counts over sites with a zone (:239-243)
-        else { c0 = cs[a * 3 + a] + cs[9 + a];                             // c_x over has_zone / has_family sites
-               c1 = cs[a * 3 + 0] + cs[9 + 0]; }                           // c_univ            (:256-259, 283-286)
+        else if (a == 1) { c0 = cs[4] + cs[10]; c1 = cs[3] + cs[9]; }      // c_x, c_univ over has_zone sites (:256-259)
+        else { c0 = cs[8] + cs[11]; c1 = cs[6] + cs[9]; }                  // ... over has_family sites     (:283-286)
         double g0, g1;
         rng_gamma2(key, step, RP_BETA_A, (uint32_t)f, 1.0 + (double)c0, true, RP_BETA_B, (uint32_t)f, 1.0 + (double)c1,
                    true, g0, g1);
-        double* w = k.w + (size_t)f * 3;
-        double v[3] = {w[0], w[1], d.C == 3 ? w[2] : 0.0};
         if (d.C == 2) {
             v[0] = g0; v[1] = g1;                           // Dir(1 + counts) = normalised Gammas
         } else {
             const double ax = g0 / (g0 + g1);               // ~ Beta(1 + c_x, 1 + c_univ)      (:262-265, 289-292)
-            v[a] = ax * v[0] / (1.0 - ax);                  // :270, 297
+            const double nv = ax * v[0] / (1.0 - ax);       // :270, 297
+            if (a == 1) v[1] = nv; else v[2] = nv;
         }
         const double s = (v[0] + v[1]) + v[2];              // normalize(w_new) :271, 298
+#pragma unroll
         for (int c = 0; c < 3; ++c) {
             v[c] /= s;
             w[c] = v[c];
-            k.scratch[(size_t)3 * f + c] = v[c];
+            stage[c] = v[c];
         }
     }
     __syncthreads();
@@ -614,14 +632,12 @@ __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, u
         const int f = i / live, e = i - f * live;
         const int idx = e < 2 ? 3 + e : (e < 4 ? (e == 2 ? 6 : 8) : 5 + e);      // 3,4 | 6,8 | 9,10,11
         const int cfg = idx / 3, c = idx - cfg * 3;
-        const double* v = k.scratch + (size_t)3 * f;
+        const double* v = k.scratch + (size_t)f * SB_W_STRIDE;
         const double tot = (v[0] + ((cfg & 1) ? v[1] : 0.0)) + ((cfg & 2) ? v[2] : 0.0);      // wnorm_row's order
         const double nw = v[c] / tot;
-        const size_t o = (size_t)f * 12 + idx;
-        const double old = k.wn[o];
-        const int n = k.cs[o];
-        if (n > 0 && nw != old) dll += (double)n * flog(nw / old, k.flt);
-        k.wn[o] = nw;
+        const double old = v[3 + idx - 2], n = v[13 + idx - 2];
+        if (n > 0.0 && nw != old) dll += n * flog(nw / old, k.flt);
+        k.wn[(size_t)f * 12 + idx] = nw;
     }
     ll += team_sum(dll, sh, tm);
 }
