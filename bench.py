@@ -166,11 +166,26 @@ def workload_config(args, world):
 # clocks
 # ---------------------------------------------------------------------------------------------------------
 class ClockSampler:
+    """SM clock and throttle reasons sampled DURING the timed region: NVML polled every 5 ms from a thread (the
+    nvidia-smi loop of the profiling recipe cannot sample faster than ~100 ms; it stays as the fallback)."""
     Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
          'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+    BITS = {0x8: 'hw_slowdown', 0x40: 'hw_thermal_slowdown', 0x20: 'sw_thermal_slowdown', 0x4: 'sw_power_cap',
+            0x80: 'hw_power_brake_slowdown'}
 
     def __init__(self, index):
-        self.rows, self.proc = [], None
+        self.rows, self.proc, self.nvml, self.stop = [], None, None, False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+            self.t = threading.Thread(target=self._poll, daemon=True)
+            self.t.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(['nvidia-smi', f'--id={index}', f'--query-gpu={self.Q}',
                                           '--format=csv,noheader,nounits', '-lms', '100'], stdout=subprocess.PIPE,
@@ -180,11 +195,31 @@ class ClockSampler:
         except OSError:
             self.proc = None
 
+    def _poll(self):
+        nv = self.nvml
+        while not self.stop:
+            try:
+                mhz = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                self.rows.append((time.perf_counter(), mhz, mask))
+            except Exception:
+                pass
+            time.sleep(0.005)
+
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append((time.perf_counter(), [c.strip() for c in line.split(',')]))
 
     def summary(self, t0, t1):
+        if self.nvml is not None:
+            self.stop = True
+            rows = [r for r in self.rows if t0 <= r[0] <= t1] or self.rows[-3:]
+            mask = 0
+            for r in rows:
+                mask |= r[2]
+            return {'sm_mhz': float(np.median([r[1] for r in rows])) if rows else None, 'sm_max_mhz': self.max_mhz,
+                    'reasons': sorted(n for b, n in self.BITS.items() if mask & b), 'samples': len(rows),
+                    'source': 'nvml, 5 ms period'}
         if self.proc is None:
             return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
         self.proc.terminate()
@@ -194,7 +229,7 @@ class ClockSampler:
         names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
         reasons = sorted({names[i] for r in rows for i in range(4) if len(r) > 2 + i and r[2 + i] == 'Active'})
         return {'sm_mhz': float(np.median(sm)) if sm else None, 'sm_max_mhz': max(mx) if mx else None,
-                'reasons': reasons, 'samples': len(rows)}
+                'reasons': reasons, 'samples': len(rows), 'source': 'nvidia-smi -lms 100'}
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -267,6 +302,39 @@ def likelihood_leg(torch, device, n_launch=60, sizes=(500, 2000, 20000)):
                     'll_chain0': float(ll[0])})
         eng.close()
     return out
+
+
+def source_free_leg(torch, args, data, states, device, stream, n_launch=3):
+    """Shape D with SAMPLE_SOURCE = false: zone moves + alter_weights / alter_p_* (mcmc_setup.py:87-95), device-timed."""
+    from contact_zones_b200.engine import Engine
+    nc = args.chains
+    eng = Engine(state_idx(data), data.states, data.families, data.network['adj_mat'], None, n_zones=D_SHAPE['Z'],
+                 n_chains=nc, inheritance=True, sample_source=False, device=device)
+    eng.set_stream(stream)
+    for c, s in enumerate(states):
+        eng.set_state(c, s['zones'], s['weights'], s['p_global'], s['p_zones'], s['p_families'], None)
+    eng.eval()
+    ops = {'shrink_zone': .02, 'grow_zone': .02, 'swap_zone': .01, 'alter_weights': .4, 'alter_p_global': .05,
+           'alter_p_zones': .4, 'alter_p_families': .1}
+    eng.set_operators(ops, PRECISION, min_size=3, max_size=50, p_grow_connected=0.85, seed=args.seed)
+    eng.run(args.mcmc_steps)
+    ms = []
+    for _ in range(n_launch):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        eng.run(args.mcmc_steps)
+        b.record()
+        torch.cuda.synchronize()
+        ms.append(a.elapsed_time(b))
+    ll_run, _ = eng.chain_scalars()
+    ll_new, _, _ = eng.eval()
+    acc, rej = eng.op_stats()
+    eng.close()
+    t = float(np.mean(ms))
+    return {'value': nc * args.mcmc_steps / (t * 1e-3), 'unit': 'proposals/s', 'ms_per_launch': t, 'launches': n_launch,
+            'us_per_proposal_per_chain': 1e3 * t / args.mcmc_steps, 'operators': ops,
+            'accept_rate': float(acc.sum() / max(1, acc.sum() + rej.sum())),
+            'll_drift_rel': float(np.max(np.abs(ll_run - ll_new) / np.abs(ll_new)))}
 
 
 def state_idx(data):
@@ -397,6 +465,11 @@ def run_gpu_arm(args, rank, world, local_rank):
     e2e_value = proposals / te.item()
     eng.close()
 
+    # ---- SAMPLE_SOURCE = false: the Metropolis alter_* operators on the same data (SURVEY 8(d) wants both modes) --
+    variants = None
+    if rank == 0 and not args.no_variants:
+        variants = {'sample_source_false': source_free_leg(torch, args, data, states, local_rank, stream)}
+
     # ---- likelihood roofline leg (rank 0) ---------------------------------------------------------------
     roof = sweep = None
     if rank == 0 and not args.no_likelihood_leg:
@@ -424,7 +497,7 @@ def run_gpu_arm(args, rank, world, local_rank):
         'll_drift_rel': drift,
         'acceptance': {k: float(acc[:, i].sum() / max(1, acc[:, i].sum() + rej[:, i].sum()))
                        for k, i in (('shrink_zone', 0), ('grow_zone', 1), ('swap_zone', 2))},
-        'roofline': roof, 'likelihood_sweep': sweep, 'cpu_baseline': cpu,
+        'roofline': roof, 'likelihood_sweep': sweep, 'sampler_variants': variants, 'cpu_baseline': cpu,
     }
     print(json.dumps(line), flush=True)
 
@@ -442,6 +515,7 @@ def main():
     ap.add_argument('--seed', type=int, default=1)
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-likelihood-leg', action='store_true')
+    ap.add_argument('--no-variants', action='store_true')
     args = ap.parse_args()
     rank = int(os.environ.get('RANK', 0))
     world = int(os.environ.get('WORLD_SIZE', 1))

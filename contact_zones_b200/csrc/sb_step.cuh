@@ -55,12 +55,17 @@ struct StepParams {
 
 // ---- shared scratch of the step kernel -----------------------------------------------------------
 #define STEP_WARPS (STEP_THREADS / 32)
+#define SB_MAX_TEAM 8
 struct StepShared {
     double red[33];
     int redi[33];
     int pick;           // bits_select result
     double dshare[4];
     double wpart[2][2][STEP_WARPS];   // per-warp partial sums of the team reductions (double-buffered pair), read by peers
+    // mailboxes of the asynchronous team reduction: every warp of every CTA of the team deposits its (a, b) pair here
+    // with st.async, which also counts the bytes on the mbarrier of the same parity
+    double2 mail[2][SB_MAX_TEAM * STEP_WARPS];
+    unsigned long long mail_bar[2];
 };
 
 // ---- site bitmaps in shared memory -----------------------------------------------------------
@@ -150,6 +155,7 @@ __device__ void build_nbr_bits(const DevData& d, const int8_t* zone_id, const in
 struct Team {
     int rank, size;
     unsigned turn;      // parity of the reduction buffer (advances identically in every CTA)
+    unsigned mturn;     // uses of the mailboxes so far (buffer = mturn & 1, mbarrier phase parity = (mturn >> 1) & 1)
 };
 __device__ __forceinline__ void team_sync(const Team& t) {
     if (t.size > 1) cg::this_cluster().sync(); else __syncthreads();
@@ -178,7 +184,10 @@ __device__ __forceinline__ void sum2_scope(double& a, double& b, StepShared& sh,
         asm volatile("barrier.cluster.arrive.relaxed.aligned;\n" ::: "memory");
         asm volatile("barrier.cluster.wait.aligned;\n" ::: "memory");
 #else
+        PROF_T(tb0);
         cl.sync();
+        PROF_T(tb1);
+        PROF_ADD(11, tb0, tb1);
 #endif
         for (int r = 0; r < scope; ++r) {
             const double* peer = cl.map_shared_rank(slot, r);
@@ -201,6 +210,82 @@ __device__ __forceinline__ double team_sum(double v, StepShared& sh, Team& t) {
 __device__ __forceinline__ double cta_sum(double v, StepShared& sh, Team& t) {      // this CTA only
     double z = 0.0;
     sum2_scope(v, z, sh, t, 1);
+    return v;
+}
+
+// ---- asynchronous team reduction (Gibbs operators) -----------------------------------------------
+// The barrier-based reduction above costs a cluster barrier whose release half waits until the CTA's global stores
+// have reached L2 and whose acquire half invalidates L1 (CCTL.IVALL) -- ~1000 cycles of a ~11000-cycle Gibbs step,
+// plus L2 instead of L1 latency for the next step's loads.  The Gibbs operators do not need either: a CTA only reads
+// and writes ITS OWN feature range of the chain's tables there.  So their reductions exchange the per-warp partials
+// with st.async (remote shared-memory store that signals an mbarrier in the receiving CTA): no fence on global
+// memory, one DSMEM hop, and every CTA sums the same mailbox image in the same order.  What a Gibbs operator wrote
+// is published to the team lazily, by a full team barrier in front of the next operator that reads across feature
+// ranges (`dirty` in mcmc_step_kernel).
+//   Buffer reuse: use n+2 of a mailbox is written by a peer only after it completed use n+1, which needs the n+1
+// deposits of ALL warps of this CTA, each made after that warp finished reading use n.  Thread 0 re-arms the
+// mbarrier (expect_tx of the next use) as soon as its own wait returned; early deposits only make the pending
+// transaction count transiently negative.
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mail_arm(StepShared& sh, const Team& t, int buf) {
+    const uint32_t bytes = (uint32_t)(t.size * STEP_WARPS * sizeof(double2));
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_addr(&sh.mail_bar[buf])), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mail_init(StepShared& sh, const Team& t) {     // whole CTA, once per launch
+    if (t.size == 1) return;
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(smem_addr(&sh.mail_bar[0])) : "memory");
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(smem_addr(&sh.mail_bar[1])) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        mail_arm(sh, t, 0);
+        mail_arm(sh, t, 1);
+    }
+    cg::this_cluster().sync();          // nobody deposits before every mbarrier of the team exists
+}
+template <bool TWO>
+__device__ __forceinline__ void team_sum_async_impl(double& a, double& b, StepShared& sh, Team& t) {
+    if (t.size == 1) { sum2_scope(a, b, sh, t, 1); return; }
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    a = warp_sum(a);
+    if (TWO) b = warp_sum(b);
+    const int buf = (int)(t.mturn & 1u);
+    const uint32_t parity = (t.mturn >> 1) & 1u;
+    ++t.mturn;
+    const uint32_t bar = smem_addr(&sh.mail_bar[buf]);
+    if (lane < t.size) {                // lane r deposits this warp's pair in CTA r (its own CTA included)
+        uint32_t rslot, rbar;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rslot)
+                     : "r"(smem_addr(&sh.mail[buf][t.rank * STEP_WARPS + w])), "r"(lane));
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rbar) : "r"(bar), "r"(lane));
+        asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f64 [%0], {%1, %2}, [%3];"
+                     :: "r"(rslot), "d"(a), "d"(b), "r"(rbar) : "memory");
+    }
+    PROF_T(tm0);
+    uint32_t done;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    } while (!done);
+    PROF_T(tm1);
+    PROF_ADD(12, tm0, tm1);
+    if (threadIdx.x == 0) mail_arm(sh, t, buf);
+    const int n = t.size * STEP_WARPS;
+    double sa = 0.0, sb = 0.0;
+    for (int e = lane; e < n; e += 32) {
+        const double2 v = sh.mail[buf][e];
+        sa += v.x;
+        sb += v.y;
+    }
+    a = warp_sum(sa);
+    if (TWO) b = warp_sum(sb);
+}
+__device__ __forceinline__ void team_sum2_async(double& a, double& b, StepShared& sh, Team& t) {
+    team_sum_async_impl<true>(a, b, sh, t);
+}
+__device__ __forceinline__ double team_sum_async(double v, StepShared& sh, Team& t) {
+    double z = 0.0;
+    team_sum_async_impl<false>(v, z, sh, t);
     return v;
 }
 
@@ -560,14 +645,34 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
 }
 
 // ---- K7c: Gibbs operators on the count tables ----------------------------------------------------
-// complete-data log-likelihood terms that depend on the weights of feature f:
-//   sum_{cfg,c} cnt_src[f][cfg][c] * log w~[f][cfg][c]        (cells with count 0 contribute nothing)
-__device__ __forceinline__ double weight_ll_row(const int* cs_row, const double* wn_row) {
-    double t = 0.0;
-#pragma unroll
-    for (int i = 0; i < 12; ++i)
-        if (cs_row[i] > 0) t += (double)cs_row[i] * log(wn_row[i]);
-    return t;
+// Phase C of op_gibbs_weights for one entry of the normalised table: returns cnt * log(w~_new / w~_old) and stores
+// w~_new.  Branch-free, so that the two items a thread may own are interleaved by the compiler.
+template <int LIVE>
+__device__ __forceinline__ double weights_entry(const Chain& k, int i, bool valid) {
+    const int f = i / LIVE, e = i - f * LIVE;
+    const int idx = LIVE == 2 ? 3 + e : (e < 2 ? 3 + e : (e < 4 ? (e == 2 ? 6 : 8) : 5 + e));      // 3,4 | 6,8 | 9,10,11
+    const int cfg = idx / 3, c = idx - cfg * 3;
+    const double* v = k.scratch + (size_t)f * SB_W_STRIDE;
+    const double tot = (v[0] + ((cfg & 1) ? v[1] : 0.0)) + ((cfg & 2) ? v[2] : 0.0);      // wnorm_row's order
+    const double nw = v[c] / tot;
+    const double old = v[3 + idx - 2], n = v[13 + idx - 2];
+    const bool on = valid && n > 0.0 && nw != old;
+    const double lr = flog(on ? nw / old : 1.0, k.flt);
+    if (valid) k.wn[(size_t)f * 12 + idx] = nw;
+    return on ? n * lr : 0.0;
+}
+template <int LIVE>
+__device__ __forceinline__ double weights_phase_c(const Chain& k, int f_lo, int f_hi) {
+    const int end = LIVE * f_hi, bd = blockDim.x;
+    double dll = 0.0;
+    for (int i = LIVE * f_lo + threadIdx.x; i < end; i += 2 * bd) {
+        const int i2 = i + bd;
+        const bool two = i2 < end;
+        const double a = weights_entry<LIVE>(k, i, true);
+        const double b = weights_entry<LIVE>(k, two ? i2 : i, two);
+        dll += a + b;
+    }
+    return dll;
 }
 
 // gibbs_sample_weights (zone_sampling.py:222-331).  Always accepted (incl. quirk Q2: with inheritance the
@@ -581,6 +686,7 @@ __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, u
     const int a = (d.C == 2) ? 1 : (fixed_inheritance ? 1 : 2);   // cfg of the "only this component" sites; also column x
     int f_lo, f_hi;
     team_share(tm, d.F, f_lo, f_hi);                    // each CTA of the team owns a contiguous range of features
+    PROF_T(tw0);
     // Everything a feature needs from global memory (its 12 source counts, 3 weights, 12 old normalised weights) is
     // requested in one batch at the top; the live entries are staged in the scratch (stride SB_W_STRIDE doubles per
     // feature: new weights | old w~ | counts), so phase C touches global memory only to store.
@@ -622,24 +728,17 @@ __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, u
             stage[c] = v[c];
         }
     }
+    PROF_T(tw1);
     __syncthreads();
+    PROF_T(tw2);
     // phase C (one thread per non-constant entry of the normalised table): w~_new and the complete-data likelihood
     // change  sum cnt_src * log(w~_new / w~_old).  Entries of impossible (cfg, component) pairs stay 0 and cfg 0 stays
     // (1, 0, 0) for ever, so only 7 (C = 3) or 2 (C = 2) entries per feature are live.
-    const int live = d.C == 3 ? 7 : 2;
-    double dll = 0.0;
-    for (int i = live * f_lo + threadIdx.x; i < live * f_hi; i += blockDim.x) {
-        const int f = i / live, e = i - f * live;
-        const int idx = e < 2 ? 3 + e : (e < 4 ? (e == 2 ? 6 : 8) : 5 + e);      // 3,4 | 6,8 | 9,10,11
-        const int cfg = idx / 3, c = idx - cfg * 3;
-        const double* v = k.scratch + (size_t)f * SB_W_STRIDE;
-        const double tot = (v[0] + ((cfg & 1) ? v[1] : 0.0)) + ((cfg & 2) ? v[2] : 0.0);      // wnorm_row's order
-        const double nw = v[c] / tot;
-        const double old = v[3 + idx - 2], n = v[13 + idx - 2];
-        if (n > 0.0 && nw != old) dll += n * flog(nw / old, k.flt);
-        k.wn[(size_t)f * 12 + idx] = nw;
-    }
-    ll += team_sum(dll, sh, tm);
+    const double dll = d.C == 3 ? weights_phase_c<7>(k, f_lo, f_hi) : weights_phase_c<2>(k, f_lo, f_hi);
+    PROF_T(tw3);
+    ll += team_sum_async(dll, sh, tm);
+    PROF_T(tw4);
+    PROF_ADD(7, tw0, tw1); PROF_ADD(8, tw1, tw2); PROF_ADD(9, tw2, tw3); PROF_ADD(10, tw3, tw4);
 }
 
 // Shared body of gibbs_sample_p_global / p_zones / p_families (zone_sampling.py:334-406):
@@ -744,11 +843,11 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
     }
     PROF_T(t3b);
     if (alpha) {
-        team_sum2(dll, dpr, sh, tm);
+        team_sum2_async(dll, dpr, sh, tm);
         ll += dll;
         prior += dpr;
     } else {
-        ll += team_sum(dll, sh, tm);
+        ll += team_sum_async(dll, sh, tm);
     }
     PROF_T(t4);
     PROF_ADD(3, t3b, t4);
@@ -918,7 +1017,7 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
     extern __shared__ unsigned char step_smem[];
     __shared__ StepShared sh;
     const int chain = blockIdx.x / sp.team;             // one cluster of sp.team CTAs per chain (cluster dims (team,1,1))
-    Team tm = {(int)(blockIdx.x % sp.team), sp.team, 0u};
+    Team tm = {(int)(blockIdx.x % sp.team), sp.team, 0u, 0u};
     unsigned* nbr = reinterpret_cast<unsigned*>(step_smem);
     unsigned* freeb = nbr + sp.nwords;
     double* prim_key = reinterpret_cast<double*>(freeb + sp.nwords + (sp.nwords & 1));
@@ -930,6 +1029,7 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
     __shared__ double2 flog_tab[SB_FLOG_N];
     flog_init(flog_tab);
     __syncthreads();
+    mail_init(sh, tm);
     kv.flt = flog_tab;
     const Chain& k = kv;
     const unsigned gchain = (unsigned)(sp.chain_offset + chain);
@@ -937,6 +1037,7 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
     double ll = st.ll[chain], prior = st.prior[chain], geo = st.geo[chain];
     const uint64_t step0 = st.step[chain];
 
+    bool dirty = false;         // a Gibbs operator wrote chain tables since the last full team barrier
     for (long long it = 0; it < n_steps; ++it) {
         const uint64_t step = step0 + (uint64_t)it;
         PROF_T(ts0);
@@ -948,6 +1049,16 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
         bool accepted = true;
         bool synced = false;    // the operator ended in a team barrier that followed all of its global writes
         PROF_T(ts1);
+        // A Gibbs operator leaves its writes (own feature range only) unpublished; every other operator reads the
+        // chain's tables across feature ranges, so it starts behind a full team barrier if anything is pending.
+        const bool gibbs_table_op = op == SB_OP_GIBBS_WEIGHTS || op == SB_OP_GIBBS_P_GLOBAL ||
+                                    op == SB_OP_GIBBS_P_ZONES || op == SB_OP_GIBBS_P_FAMILIES;
+        if (gibbs_table_op) {
+            dirty = true;
+        } else if (dirty) {
+            team_sync(tm);
+            dirty = false;
+        }
         switch (op) {
             case SB_OP_SHRINK_ZONE: case SB_OP_GROW_ZONE: case SB_OP_SWAP_ZONE:
                 accepted = op_zone_move(d, sp, k, op, chain, key, step, ll, prior, geo, nbr, freeb, prim_key,
