@@ -65,6 +65,12 @@ __device__ __forceinline__ int rng_int(RngKey key, uint64_t step, uint32_t purpo
     return v < n ? v : n - 1;
 }
 
+// the same integer from a uniform that was drawn ahead of time
+__device__ __forceinline__ int ahead_int(double u, int n) {
+    const int v = (int)(u * (double)n);
+    return v < n ? v : n - 1;
+}
+
 // Gamma(alpha, 1), Marsaglia & Tsang (2000).  alpha < 1 uses Gamma(alpha+1) * U^(1/alpha).
 // One Philox block per attempt: word 0 -> Box-Muller radius, word 1 -> angle, words 2-3 -> the accept uniforms of the
 // two normals, which are both tried before a new block is drawn (so a whole warp rarely needs a second attempt:

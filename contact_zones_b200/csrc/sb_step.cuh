@@ -16,7 +16,12 @@
 #include <cooperative_groups.h>
 namespace cg = cooperative_groups;
 
-#define STEP_THREADS 512
+#ifndef STEP_THREADS
+#define STEP_THREADS 512     // threads per CTA of the step kernel
+#endif
+#ifndef STEP_MIN_CTAS
+#define STEP_MIN_CTAS 1       // CTAs the register budget must let share an SM
+#endif
 #define SB_W_STRIDE 24        // scratch doubles per feature in op_gibbs_weights: 3 new w | 10 old w~ | 10 counts
 
 // optional phase timing (build with -DSB_PROF): cycles of CTA 0 / thread 0 accumulated per marker
@@ -56,6 +61,7 @@ struct StepParams {
 // ---- shared scratch of the step kernel -----------------------------------------------------------
 #define STEP_WARPS (STEP_THREADS / 32)
 #define SB_MAX_TEAM 8
+#define SB_AHEAD 32
 struct StepShared {
     double red[33];
     int redi[33];
@@ -66,6 +72,10 @@ struct StepShared {
     // with st.async, which also counts the bytes on the mbarrier of the same parity
     double2 mail[2][SB_MAX_TEAM * STEP_WARPS];
     unsigned long long mail_bar[2];
+    // per-step scalar draws of the next SB_AHEAD steps (operator id and the uniforms behind "which zone / family /
+    // fixed component"), filled by four warps once per SB_AHEAD steps instead of by every thread in every step
+    int op_ahead[SB_AHEAD];
+    double u_ahead[3][SB_AHEAD];        // RP_ZONE, RP_FAMILY, RP_FIXED
 };
 
 // ---- site bitmaps in shared memory -----------------------------------------------------------
@@ -156,13 +166,14 @@ struct Team {
     int rank, size;
     unsigned turn;      // parity of the reduction buffer (advances identically in every CTA)
     unsigned mturn;     // uses of the mailboxes so far (buffer = mturn & 1, mbarrier phase parity = (mturn >> 1) & 1)
+    int shift;          // log2(size)
 };
 __device__ __forceinline__ void team_sync(const Team& t) {
     if (t.size > 1) cg::this_cluster().sync(); else __syncthreads();
 }
 // contiguous share [lo, hi) of n items for this CTA
 __device__ __forceinline__ void team_share(const Team& t, int n, int& lo, int& hi) {
-    const int per = (n + t.size - 1) / t.size;
+    const int per = (n + t.size - 1) >> t.shift;
     lo = min(n, t.rank * per);
     hi = min(n, lo + per);
 }
@@ -677,10 +688,9 @@ __device__ __forceinline__ double weights_phase_c(const Chain& k, int f_lo, int 
 
 // gibbs_sample_weights (zone_sampling.py:222-331).  Always accepted (incl. quirk Q2: with inheritance the
 // per-feature MH decision is overwritten by `sample_new.weights = w_new`, :325-327).
-__device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, uint64_t step, double& ll,
-                                 StepShared& sh, Team& tm) {
-    // fixed = choice(['inheritance', 'contact'])  (:249)
-    const bool fixed_inheritance = rng_uniform(key, step, RP_FIXED, 0) < 0.5;
+__device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, uint64_t step, bool fixed_inheritance,
+                                 double& ll, StepShared& sh, Team& tm) {
+    // fixed = choice(['inheritance', 'contact'])  (:249): fixed_inheritance = (uniform(step, RP_FIXED) < 0.5)
     // phase A (one thread per feature): the two Gammas of the feature's Beta / Dirichlet draw in lock-step, then the
     // new weight row, staged in the scratch ([0,3F))
     const int a = (d.C == 2) ? 1 : (fixed_inheritance ? 1 : 2);   // cfg of the "only this component" sites; also column x
@@ -1012,12 +1022,12 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
 }
 
 // ---- K8: the persistent kernel ---------------------------------------------------------------------
-__global__ void __launch_bounds__(STEP_THREADS)
+__global__ void __launch_bounds__(STEP_THREADS, STEP_MIN_CTAS)
 mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
     extern __shared__ unsigned char step_smem[];
     __shared__ StepShared sh;
     const int chain = blockIdx.x / sp.team;             // one cluster of sp.team CTAs per chain (cluster dims (team,1,1))
-    Team tm = {(int)(blockIdx.x % sp.team), sp.team, 0u, 0u};
+    Team tm = {(int)(blockIdx.x % sp.team), sp.team, 0u, 0u, 31 - __clz(sp.team)};
     unsigned* nbr = reinterpret_cast<unsigned*>(step_smem);
     unsigned* freeb = nbr + sp.nwords;
     double* prim_key = reinterpret_cast<double*>(freeb + sp.nwords + (sp.nwords & 1));
@@ -1041,11 +1051,23 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
     for (long long it = 0; it < n_steps; ++it) {
         const uint64_t step = step0 + (uint64_t)it;
         PROF_T(ts0);
-        // operator choice: np.random.choice(fn_operators, p=p_operators)  (mcmc_generative.py:294)
-        const double uo = rng_uniform(key, step, RP_OP, 0);
-        int oi = 0;
-        while (oi < sp.n_ops - 1 && uo >= sp.op_cdf[oi]) ++oi;
-        const int op = sp.op_ids[oi];
+        // operator choice: np.random.choice(fn_operators, p=p_operators)  (mcmc_generative.py:294).  The draws that
+        // depend on the step number only are made SB_AHEAD steps at a time: warp w, lane l -> draw w of step + l.
+        // (The previous step ended in a CTA barrier, so nobody still reads the old table.)
+        const int ia = (int)(it & (SB_AHEAD - 1));
+        if (ia == 0) {
+            const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+            if (w == 0) {
+                const double uo = rng_uniform(key, step + l, RP_OP, 0);
+                int oi = 0;
+                while (oi < sp.n_ops - 1 && uo >= sp.op_cdf[oi]) ++oi;
+                sh.op_ahead[l] = sp.op_ids[oi];
+            } else if (w < 4) {
+                sh.u_ahead[w - 1][l] = rng_uniform(key, step + l, w == 1 ? RP_ZONE : (w == 2 ? RP_FAMILY : RP_FIXED), 0);
+            }
+            __syncthreads();
+        }
+        const int op = sh.op_ahead[ia];
         bool accepted = true;
         bool synced = false;    // the operator ended in a team barrier that followed all of its global writes
         PROF_T(ts1);
@@ -1069,7 +1091,7 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
                 synced = true;
                 break;
             case SB_OP_GIBBS_WEIGHTS:
-                op_gibbs_weights(d, k, key, step, ll, sh, tm);
+                op_gibbs_weights(d, k, key, step, sh.u_ahead[2][ia] < 0.5, ll, sh, tm);
                 synced = true;
                 break;
             case SB_OP_GIBBS_P_GLOBAL:
@@ -1078,14 +1100,14 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
                 synced = true;
                 break;
             case SB_OP_GIBBS_P_ZONES: {
-                const size_t o = (size_t)rng_int(key, step, RP_ZONE, 0, d.Z) * d.F * d.S;
+                const size_t o = (size_t)ahead_int(sh.u_ahead[0][ia], d.Z) * d.F * d.S;
                 gibbs_table_row(d, sp, k, key, step, k.pz + o, k.cz + o, nullptr, false, nullptr, nullptr, nullptr,
                                 ll, prior, sh, tm);
                 synced = true;
                 break;
             }
             case SB_OP_GIBBS_P_FAMILIES: {
-                const int fam = rng_int(key, step, RP_FAMILY, 0, d.Fam);
+                const int fam = ahead_int(sh.u_ahead[1][ia], d.Fam);
                 const size_t o = (size_t)fam * d.F * d.S;
                 gibbs_table_row(d, sp, k, key, step, k.pf + o, k.cf + o, d.gibbs_f + o, true,
                                 d.pf_type == 1 ? d.alpha_f + o : nullptr, d.lnorm_f + (size_t)fam * d.F,
