@@ -1047,7 +1047,7 @@ int sb_move_log_q(sb_ctx* ctx, int chain, int kind, int zone, int site_new, int 
 }
 
 int sb_rng_sample(sb_ctx* ctx, int kind, double alpha, uint64_t seed, int n, double* out) {
-    if (!ctx || !out || n < 1 || kind < 0 || kind > 2 || (kind == 1 && !(alpha > 0.0))) return SB_E_ARG;
+    if (!ctx || !out || n < 1 || kind < 0 || kind > 3 || (kind == 1 && !(alpha > 0.0))) return SB_E_ARG;
     CK(cudaSetDevice(ctx->device));
     double* dout;
     CK(cudaMalloc((void**)&dout, (size_t)n * sizeof(double)));

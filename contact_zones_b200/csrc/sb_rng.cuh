@@ -74,10 +74,11 @@ __device__ __forceinline__ int ahead_int(double u, int n) {
 // Gamma(alpha, 1), Marsaglia & Tsang (2000).  alpha < 1 uses Gamma(alpha+1) * U^(1/alpha).
 // One Philox block per attempt: word 0 -> Box-Muller radius, word 1 -> angle, words 2-3 -> the accept uniforms of the
 // two normals, which are both tried before a new block is drawn (so a whole warp rarely needs a second attempt:
-// 1 - (1 - 0.05^2)^32 ~ 8 %).  The candidate normals are evaluated with fp32 transcendentals (logf / sqrtf /
-// sincospif: relative error ~1e-7 on x, i.e. a 1e-7 perturbation of the proposal density -- orders of magnitude below
-// the Monte-Carlo error of any run; the radius uniform has 32 bits, so |x| <= 6.8) and then treated as exact fp64
-// numbers: v, the accept test and the variate are fp64.  The log-form accept test is decided by a fast fp32 estimate
+// 1 - (1 - 0.05^2)^32 ~ 8 %).  The candidate normals are evaluated with the fp32 hardware approximations (MUFU
+// lg2 / sqrt / sin / cos, ~12 instructions instead of ~55 for logf / sqrtf / sincospif): absolute error ~5e-7 on x,
+// i.e. a ~1e-6 perturbation of the proposal density -- orders of magnitude below the Monte-Carlo error of any run
+// (tests/test_rng_parity.py: KS tests against the exact CDFs); the radius uniform has 32 bits, so |x| <= 6.8.  The
+// candidates are then treated as exact fp64 numbers: v, the accept test and the variate are fp64.  The log-form accept test is decided by a fast fp32 estimate
 // when its margin is clear and in fp64 otherwise.
 __device__ __forceinline__ bool mt_accept(double x, double u, double c, double d, double& out) {
     // written without early exits so that two candidates can be interleaved by the compiler
@@ -106,9 +107,12 @@ struct MtCand { double x0, x1, u0, u1; };
 __device__ __forceinline__ MtCand mt_candidates(RngKey key, uint64_t step, uint32_t purpose, uint32_t attempt, uint32_t index) {
     uint32_t o[4];
     philox4x32((uint32_t)step, (uint32_t)(step >> 32), (purpose << 24) | attempt, index, key.k0, key.k1, o);
-    const float r = sqrtf(-2.0f * logf(((float)o[0] + 0.5f) * 2.3283064365386963e-10f));
-    float sn, cs;
-    sincospif(((float)(o[1] >> 8) + 0.5f) * (2.0f / 16777216.0f), &sn, &cs);
+    // hardware approximations (MUFU lg2 / sqrt / sin / cos): absolute error ~5e-7 on the candidate, see above
+    float r, sn, cs;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r)
+        : "f"(-1.3862943611198906f * __log2f(((float)o[0] + 0.5f) * 2.3283064365386963e-10f)));     // sqrt(-2 ln u)
+    // angle uniform on [-pi, pi): the range where sin.approx / cos.approx are most accurate
+    __sincosf(((float)(o[1] >> 8) - 8388607.5f) * (6.283185307179586f / 16777216.0f), &sn, &cs);
     MtCand m;
     m.x0 = (double)(r * cs); m.x1 = (double)(r * sn);
     m.u0 = ((double)o[2] + 0.5) * (1.0 / 4294967296.0);
@@ -161,6 +165,7 @@ __device__ double rng_gamma(RngKey key, uint64_t step, uint32_t purpose, uint32_
 }
 
 // debug / parity surface of K6 (sb_rng_sample): n independent draws, kind 0 = uniform(0,1), 1 = Gamma(alpha, 1),
+// 3 = the N(0,1) candidates of the Gamma sampler,
 // 2 = flog((1 + u_i) * 2^(i % 121 - 60)) with u_i the kind-0 draw (accuracy check of the table-driven logarithm)
 __global__ void rng_sample_kernel(int kind, double alpha, uint32_t seed_lo, uint32_t seed_hi, int n, double* out) {
     __shared__ double2 tab[SB_FLOG_N];
@@ -170,6 +175,11 @@ __global__ void rng_sample_kernel(int kind, double alpha, uint32_t seed_lo, uint
     if (i >= n) return;
     const RngKey key = {seed_lo, seed_hi};
     if (kind == 1) { out[i] = rng_gamma(key, 0, RP_GAMMA, (uint32_t)i, alpha); return; }
+    if (kind == 3) {
+        const MtCand m = mt_candidates(key, 0, RP_GAMMA, 0, (uint32_t)(i >> 1));
+        out[i] = (i & 1) ? m.x1 : m.x0;
+        return;
+    }
     const double u = rng_uniform(key, 0, RP_GAMMA, (uint32_t)i);
     out[i] = kind == 0 ? u : flog(ldexp(1.0 + u, i % 121 - 60), tab);
 }

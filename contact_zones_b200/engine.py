@@ -219,9 +219,10 @@ class Engine:
         return lq.value, lqb.value
 
     def rng_sample(self, kind, n, alpha=1.0, seed=0):
-        """n draws of the device generator: kind 'uniform' or 'gamma' (K6 parity surface)."""
+        """n draws of the device generator: kind 'uniform', 'gamma', 'normal' (the Gamma sampler's candidates) or
+        'flog' (K6 parity surface)."""
         out = np.zeros(int(n))
-        self._check(self.lib.sb_rng_sample(self._ctx, {'uniform': 0, 'gamma': 1, 'flog': 2}[kind], float(alpha), int(seed), int(n),
+        self._check(self.lib.sb_rng_sample(self._ctx, {'uniform': 0, 'gamma': 1, 'flog': 2, 'normal': 3}[kind], float(alpha), int(seed), int(n),
                                            ptr(out)))
         return out
 

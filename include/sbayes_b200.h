@@ -172,7 +172,8 @@ int sb_kernel_launches(sb_ctx* ctx, int64_t* launches);                         
 /* ---- K6 parity surface: n independent draws of the device generator (Philox4x32-10 + Marsaglia-Tsang), which
  *      replaces np.random.dirichlet / scipy.stats.beta.rvs (zone_sampling.py:243,262-265,351,373,401,560).
  *      kind 0 = uniform(0,1), 1 = Gamma(alpha, 1), 2 = the step kernel's table-driven log of
- *      (1 + u_i) * 2^(i % 121 - 60), u_i the kind-0 draw (accuracy surface). */
+ *      (1 + u_i) * 2^(i % 121 - 60), u_i the kind-0 draw (accuracy surface), 3 = the standard-normal candidates of
+ *      the Gamma sampler (draws 2j, 2j+1 = the Box-Muller pair of block j). */
 int sb_rng_sample(sb_ctx* ctx, int kind, double alpha, uint64_t seed, int n, double* out);
 
 #ifdef __cplusplus

@@ -38,6 +38,24 @@ def test_gamma(eng, alpha):
     assert abs(g.var() - alpha) < 5 * alpha * np.sqrt((2 + 6 / alpha) / N)
 
 
+def test_normal_candidates(eng):
+    """The N(0,1) candidates of the Gamma sampler come from hardware-approximate lg2 / sqrt / sin / cos: the
+    perturbation (~5e-7 absolute) must be invisible at 2e6 draws, in the body, the tails and the pair structure."""
+    n = 2_000_000
+    x = eng.rng_sample('normal', n, seed=5)
+    assert stats.kstest(x, 'norm').pvalue > 1e-4
+    assert abs(x.mean()) < 5 / np.sqrt(n) and abs(x.var() - 1) < 5 * np.sqrt(2 / n)
+    assert abs(np.mean(x ** 4) - 3) < 5 * np.sqrt(96 / n)
+    for t in (2.0, 3.0, 4.0):
+        p = 2 * stats.norm.sf(t)
+        assert abs(np.mean(np.abs(x) > t) - p) < 5 * np.sqrt(p / n)
+    assert abs(np.corrcoef(x[0::2], x[1::2])[0, 1]) < 5 / np.sqrt(n / 2)      # the two normals of a pair
+    r2 = x[0::2] ** 2 + x[1::2] ** 2                                           # radius^2 ~ chi2(2) = Exp(1/2)
+    assert stats.kstest(r2, 'expon', args=(0, 2)).pvalue > 1e-4
+    ang = np.arctan2(x[1::2], x[0::2])
+    assert stats.kstest(ang, 'uniform', args=(-np.pi, 2 * np.pi)).pvalue > 1e-4
+
+
 def test_beta_and_dirichlet_from_gammas(eng):
     """Beta(a, b) = Ga / (Ga + Gb) (gibbs_sample_weights) and a Dirichlet row (gibbs_sample_p_*)."""
     a, b = 3.0, 11.0
