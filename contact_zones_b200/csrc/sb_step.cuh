@@ -60,7 +60,6 @@ struct StepParams {
 
 // ---- shared scratch of the step kernel -----------------------------------------------------------
 #define STEP_WARPS (STEP_THREADS / 32)
-#define SB_MAX_TEAM 8
 #define SB_AHEAD 32
 struct StepShared {
     double red[33];
@@ -68,10 +67,6 @@ struct StepShared {
     int pick;           // bits_select result
     double dshare[4];
     double wpart[2][2][STEP_WARPS];   // per-warp partial sums of the team reductions (double-buffered pair), read by peers
-    // mailboxes of the asynchronous team reduction: every warp of every CTA of the team deposits its (a, b) pair here
-    // with st.async, which also counts the bytes on the mbarrier of the same parity
-    double2 mail[2][SB_MAX_TEAM * STEP_WARPS];
-    unsigned long long mail_bar[2];
     // per-step scalar draws of the next SB_AHEAD steps (operator id and the uniforms behind "which zone / family /
     // fixed component"), filled by four warps once per SB_AHEAD steps instead of by every thread in every step
     int op_ahead[SB_AHEAD];
@@ -165,7 +160,6 @@ __device__ void build_nbr_bits(const DevData& d, const int8_t* zone_id, const in
 struct Team {
     int rank, size;
     unsigned turn;      // parity of the reduction buffer (advances identically in every CTA)
-    unsigned mturn;     // uses of the mailboxes so far (buffer = mturn & 1, mbarrier phase parity = (mturn >> 1) & 1)
     int shift;          // log2(size)
 };
 __device__ __forceinline__ void team_sync(const Team& t) {
@@ -221,82 +215,6 @@ __device__ __forceinline__ double team_sum(double v, StepShared& sh, Team& t) {
 __device__ __forceinline__ double cta_sum(double v, StepShared& sh, Team& t) {      // this CTA only
     double z = 0.0;
     sum2_scope(v, z, sh, t, 1);
-    return v;
-}
-
-// ---- asynchronous team reduction (Gibbs operators) -----------------------------------------------
-// The barrier-based reduction above costs a cluster barrier whose release half waits until the CTA's global stores
-// have reached L2 and whose acquire half invalidates L1 (CCTL.IVALL) -- ~1000 cycles of a ~11000-cycle Gibbs step,
-// plus L2 instead of L1 latency for the next step's loads.  The Gibbs operators do not need either: a CTA only reads
-// and writes ITS OWN feature range of the chain's tables there.  So their reductions exchange the per-warp partials
-// with st.async (remote shared-memory store that signals an mbarrier in the receiving CTA): no fence on global
-// memory, one DSMEM hop, and every CTA sums the same mailbox image in the same order.  What a Gibbs operator wrote
-// is published to the team lazily, by a full team barrier in front of the next operator that reads across feature
-// ranges (`dirty` in mcmc_step_kernel).
-//   Buffer reuse: use n+2 of a mailbox is written by a peer only after it completed use n+1, which needs the n+1
-// deposits of ALL warps of this CTA, each made after that warp finished reading use n.  Thread 0 re-arms the
-// mbarrier (expect_tx of the next use) as soon as its own wait returned; early deposits only make the pending
-// transaction count transiently negative.
-__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mail_arm(StepShared& sh, const Team& t, int buf) {
-    const uint32_t bytes = (uint32_t)(t.size * STEP_WARPS * sizeof(double2));
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_addr(&sh.mail_bar[buf])), "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void mail_init(StepShared& sh, const Team& t) {     // whole CTA, once per launch
-    if (t.size == 1) return;
-    if (threadIdx.x == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(smem_addr(&sh.mail_bar[0])) : "memory");
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(smem_addr(&sh.mail_bar[1])) : "memory");
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        mail_arm(sh, t, 0);
-        mail_arm(sh, t, 1);
-    }
-    cg::this_cluster().sync();          // nobody deposits before every mbarrier of the team exists
-}
-template <bool TWO>
-__device__ __forceinline__ void team_sum_async_impl(double& a, double& b, StepShared& sh, Team& t) {
-    if (t.size == 1) { sum2_scope(a, b, sh, t, 1); return; }
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    a = warp_sum(a);
-    if (TWO) b = warp_sum(b);
-    const int buf = (int)(t.mturn & 1u);
-    const uint32_t parity = (t.mturn >> 1) & 1u;
-    ++t.mturn;
-    const uint32_t bar = smem_addr(&sh.mail_bar[buf]);
-    if (lane < t.size) {                // lane r deposits this warp's pair in CTA r (its own CTA included)
-        uint32_t rslot, rbar;
-        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rslot)
-                     : "r"(smem_addr(&sh.mail[buf][t.rank * STEP_WARPS + w])), "r"(lane));
-        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rbar) : "r"(bar), "r"(lane));
-        asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f64 [%0], {%1, %2}, [%3];"
-                     :: "r"(rslot), "d"(a), "d"(b), "r"(rbar) : "memory");
-    }
-    PROF_T(tm0);
-    uint32_t done;
-    do {
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-                     "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-    } while (!done);
-    PROF_T(tm1);
-    PROF_ADD(12, tm0, tm1);
-    if (threadIdx.x == 0) mail_arm(sh, t, buf);
-    const int n = t.size * STEP_WARPS;
-    double sa = 0.0, sb = 0.0;
-    for (int e = lane; e < n; e += 32) {
-        const double2 v = sh.mail[buf][e];
-        sa += v.x;
-        sb += v.y;
-    }
-    a = warp_sum(sa);
-    if (TWO) b = warp_sum(sb);
-}
-__device__ __forceinline__ void team_sum2_async(double& a, double& b, StepShared& sh, Team& t) {
-    team_sum_async_impl<true>(a, b, sh, t);
-}
-__device__ __forceinline__ double team_sum_async(double v, StepShared& sh, Team& t) {
-    double z = 0.0;
-    team_sum_async_impl<false>(v, z, sh, t);
     return v;
 }
 
@@ -689,7 +607,7 @@ __device__ __forceinline__ double weights_phase_c(const Chain& k, int f_lo, int 
 // gibbs_sample_weights (zone_sampling.py:222-331).  Always accepted (incl. quirk Q2: with inheritance the
 // per-feature MH decision is overwritten by `sample_new.weights = w_new`, :325-327).
 __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, uint64_t step, bool fixed_inheritance,
-                                 double& ll, StepShared& sh, Team& tm) {
+                                 double& ll_acc, const Team& tm) {
     // fixed = choice(['inheritance', 'contact'])  (:249): fixed_inheritance = (uniform(step, RP_FIXED) < 0.5)
     // phase A (one thread per feature): the two Gammas of the feature's Beta / Dirichlet draw in lock-step, then the
     // new weight row, staged in the scratch ([0,3F))
@@ -746,9 +664,8 @@ __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, u
     // (1, 0, 0) for ever, so only 7 (C = 3) or 2 (C = 2) entries per feature are live.
     const double dll = d.C == 3 ? weights_phase_c<7>(k, f_lo, f_hi) : weights_phase_c<2>(k, f_lo, f_hi);
     PROF_T(tw3);
-    ll += team_sum_async(dll, sh, tm);
-    PROF_T(tw4);
-    PROF_ADD(7, tw0, tw1); PROF_ADD(8, tw1, tw2); PROF_ADD(9, tw2, tw3); PROF_ADD(10, tw3, tw4);
+    ll_acc += dll;              // thread-private: summed over the team when somebody needs the total
+    PROF_ADD(7, tw0, tw1); PROF_ADD(8, tw1, tw2); PROF_ADD(9, tw2, tw3);
 }
 
 // Shared body of gibbs_sample_p_global / p_zones / p_families (zone_sampling.py:334-406):
@@ -759,7 +676,7 @@ __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, u
 __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Chain& k, RngKey key, uint64_t step,
                                 double* p, const int* cnt, const double* pc, bool use_subset,
                                 const double* alpha, const double* lnorm, double* pcache,
-                                double& ll, double& prior, StepShared& sh, Team& tm) {
+                                double& ll_acc, double& prior_acc, const Team& tm) {
     const int S = d.S;
     int f_lo, f_hi;
     team_share(tm, d.F, f_lo, f_hi);                    // whole rows per CTA: the row totals stay CTA-local
@@ -851,16 +768,8 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
             pcache[f] = v;
         }
     }
-    PROF_T(t3b);
-    if (alpha) {
-        team_sum2_async(dll, dpr, sh, tm);
-        ll += dll;
-        prior += dpr;
-    } else {
-        ll += team_sum_async(dll, sh, tm);
-    }
-    PROF_T(t4);
-    PROF_ADD(3, t3b, t4);
+    ll_acc += dll;              // thread-private: summed over the team when somebody needs the total
+    prior_acc += dpr;
 }
 
 // ---- K7d: alter_* operators (source-free mode), zone_sampling.py:408-612 --------------------------
@@ -1027,7 +936,7 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
     extern __shared__ unsigned char step_smem[];
     __shared__ StepShared sh;
     const int chain = blockIdx.x / sp.team;             // one cluster of sp.team CTAs per chain (cluster dims (team,1,1))
-    Team tm = {(int)(blockIdx.x % sp.team), sp.team, 0u, 0u, 31 - __clz(sp.team)};
+    Team tm = {(int)(blockIdx.x % sp.team), sp.team, 0u, 31 - __clz(sp.team)};
     unsigned* nbr = reinterpret_cast<unsigned*>(step_smem);
     unsigned* freeb = nbr + sp.nwords;
     double* prim_key = reinterpret_cast<double*>(freeb + sp.nwords + (sp.nwords & 1));
@@ -1039,7 +948,6 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
     __shared__ double2 flog_tab[SB_FLOG_N];
     flog_init(flog_tab);
     __syncthreads();
-    mail_init(sh, tm);
     kv.flt = flog_tab;
     const Chain& k = kv;
     const unsigned gchain = (unsigned)(sp.chain_offset + chain);
@@ -1048,6 +956,10 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
     const uint64_t step0 = st.step[chain];
 
     bool dirty = false;         // a Gibbs operator wrote chain tables since the last full team barrier
+    // The Gibbs operators are always accepted, and nobody needs the absolute ll / prior inside a launch (the
+    // Metropolis steps work on deltas), so their likelihood / prior changes stay in thread-private accumulators and
+    // are summed over the team once, at the end of the launch: a Gibbs step has no reduction and no team traffic.
+    double ll_acc = 0.0, prior_acc = 0.0;
     for (long long it = 0; it < n_steps; ++it) {
         const uint64_t step = step0 + (uint64_t)it;
         PROF_T(ts0);
@@ -1085,24 +997,26 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
             case SB_OP_SHRINK_ZONE: case SB_OP_GROW_ZONE: case SB_OP_SWAP_ZONE:
                 accepted = op_zone_move(d, sp, k, op, chain, key, step, ll, prior, geo, nbr, freeb, prim_key,
                                         prim_tree, sh, tm, synced);
+                if (accepted && d.sample_source) ll_acc = 0.0;      // ll was recomputed from scratch by the source sweep
                 break;
             case SB_OP_GIBBS_SOURCES:
                 ll = resample_sources(d, k, key, step, sh, tm);
+                ll_acc = 0.0;
                 synced = true;
                 break;
             case SB_OP_GIBBS_WEIGHTS:
-                op_gibbs_weights(d, k, key, step, sh.u_ahead[2][ia] < 0.5, ll, sh, tm);
+                op_gibbs_weights(d, k, key, step, sh.u_ahead[2][ia] < 0.5, ll_acc, tm);
                 synced = true;
                 break;
             case SB_OP_GIBBS_P_GLOBAL:
                 gibbs_table_row(d, sp, k, key, step, k.pg, k.cg, d.gibbs_g, true,
-                                d.pg_type == 1 ? d.alpha_g : nullptr, d.lnorm_g, k.ppg, ll, prior, sh, tm);
+                                d.pg_type == 1 ? d.alpha_g : nullptr, d.lnorm_g, k.ppg, ll_acc, prior_acc, tm);
                 synced = true;
                 break;
             case SB_OP_GIBBS_P_ZONES: {
                 const size_t o = (size_t)ahead_int(sh.u_ahead[0][ia], d.Z) * d.F * d.S;
                 gibbs_table_row(d, sp, k, key, step, k.pz + o, k.cz + o, nullptr, false, nullptr, nullptr, nullptr,
-                                ll, prior, sh, tm);
+                                ll_acc, prior_acc, tm);
                 synced = true;
                 break;
             }
@@ -1111,7 +1025,7 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
                 const size_t o = (size_t)fam * d.F * d.S;
                 gibbs_table_row(d, sp, k, key, step, k.pf + o, k.cf + o, d.gibbs_f + o, true,
                                 d.pf_type == 1 ? d.alpha_f + o : nullptr, d.lnorm_f + (size_t)fam * d.F,
-                                k.ppf + (size_t)fam * d.F, ll, prior, sh, tm);
+                                k.ppf + (size_t)fam * d.F, ll_acc, prior_acc, tm);
                 synced = true;
                 break;
             }
@@ -1127,6 +1041,9 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
         PROF_T(ts3);
         PROF_ADD(4, ts0, ts1); PROF_ADD(5, ts1, ts2); PROF_ADD(6, ts2, ts3);
     }
+    team_sum2(ll_acc, prior_acc, sh, tm);
+    ll += ll_acc;
+    prior += prior_acc;
     if (threadIdx.x == 0 && tm.rank == 0) {
         st.ll[chain] = ll; st.prior[chain] = prior; st.geo[chain] = geo;
         st.step[chain] = step0 + (uint64_t)n_steps;
