@@ -833,7 +833,7 @@ static size_t step_smem_base(const StepParams& sp) {
 // the source sweep are used at different times and overlay each other; whatever does not fit stays in global memory.
 static size_t step_smem_bytes(const DevData& d, StepParams& sp) {
     const size_t base = step_smem_base(sp);
-    const size_t scratch = (size_t)d.F * (d.S > SB_W_STRIDE ? d.S : SB_W_STRIDE) * sizeof(double);
+    const size_t scratch = (size_t)d.F * d.S * sizeof(double);
     const size_t counts = ((size_t)16 * d.S * (1 + d.Z + d.Fam) + 192) * sizeof(int);
     const size_t room = 160 * 1024 > base ? 160 * 1024 - base : 0;
     sp.work_off = (int)base;
@@ -849,7 +849,7 @@ static int ensure_step_scratch(sb_ctx* ctx) {
     StepParams& sp = ctx->sp;
     const DevData& d = ctx->d;
     if (!sp.scratch) {
-        sp.s_scratch = (size_t)d.F * (d.S > SB_W_STRIDE ? d.S : SB_W_STRIDE);     // Gamma draws [F][S] or the weight staging
+        sp.s_scratch = (size_t)d.F * d.S;     // Gamma draws [F][S]
         DA(sp.scratch, (size_t)ctx->dims.n_chains * sp.s_scratch);
         sp.s_tmp = (size_t)d.N;
         DA(sp.tmp_members, (size_t)ctx->dims.n_chains * sp.s_tmp);

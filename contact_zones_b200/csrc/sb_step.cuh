@@ -22,7 +22,6 @@ namespace cg = cooperative_groups;
 #ifndef STEP_MIN_CTAS
 #define STEP_MIN_CTAS 1       // CTAs the register budget must let share an SM
 #endif
-#define SB_W_STRIDE 24        // scratch doubles per feature in op_gibbs_weights: 3 new w | 10 old w~ | 10 counts
 
 // optional phase timing (build with -DSB_PROF): cycles of CTA 0 / thread 0 accumulated per marker
 #ifdef SB_PROF
@@ -573,71 +572,52 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
     return true;
 }
 
-// ---- K7c: Gibbs operators on the count tables ----------------------------------------------------
-// Phase C of op_gibbs_weights for one entry of the normalised table: returns cnt * log(w~_new / w~_old) and stores
-// w~_new.  Branch-free, so that the two items a thread may own are interleaved by the compiler.
-template <int LIVE>
-__device__ __forceinline__ double weights_entry(const Chain& k, int i, bool valid) {
-    const int f = i / LIVE, e = i - f * LIVE;
-    const int idx = LIVE == 2 ? 3 + e : (e < 2 ? 3 + e : (e < 4 ? (e == 2 ? 6 : 8) : 5 + e));      // 3,4 | 6,8 | 9,10,11
-    const int cfg = idx / 3, c = idx - cfg * 3;
-    const double* v = k.scratch + (size_t)f * SB_W_STRIDE;
-    const double tot = (v[0] + ((cfg & 1) ? v[1] : 0.0)) + ((cfg & 2) ? v[2] : 0.0);      // wnorm_row's order
-    const double nw = v[c] / tot;
-    const double old = v[3 + idx - 2], n = v[13 + idx - 2];
-    const bool on = valid && n > 0.0 && nw != old;
-    const double lr = flog(on ? nw / old : 1.0, k.flt);
-    if (valid) k.wn[(size_t)f * 12 + idx] = nw;
-    return on ? n * lr : 0.0;
-}
-template <int LIVE>
-__device__ __forceinline__ double weights_phase_c(const Chain& k, int f_lo, int f_hi) {
-    const int end = LIVE * f_hi, bd = blockDim.x;
-    double dll = 0.0;
-    for (int i = LIVE * f_lo + threadIdx.x; i < end; i += 2 * bd) {
-        const int i2 = i + bd;
-        const bool two = i2 < end;
-        const double a = weights_entry<LIVE>(k, i, true);
-        const double b = weights_entry<LIVE>(k, two ? i2 : i, two);
-        dll += a + b;
+// With SAMPLE_SOURCE the likelihood (model.py:177-184) is a function of the integer count tables (K4) and the
+// parameter tables alone:
+//   ll = sum_f [ sum_{cfg,c} cnt_src[f][cfg][c] log w~[f][cfg][c] + sum_s ( cnt_g[f][s] log p_global[f][s]
+//              + sum_z cnt_z[z][f][s] log p_zones[z][f][s] + sum_k cnt_f[k][f][s] log p_families[k][f][s] ) ]
+// (cells with count 0 contribute nothing; a positive count on a zero probability gives -inf, as the cell-by-cell
+// form does).  The Gibbs operators therefore do not track their likelihood change; the running value is re-formed
+// from the tables when it is needed -- once per launch -- at O(F * (12 + S * (1 + Z + Fam))) logarithms.
+__device__ __forceinline__ double count_term(int c, double p) { return c > 0 ? (double)c * log(p) : 0.0; }
+__device__ double ll_from_counts(const DevData& d, const Chain& k, StepShared& sh, Team& tm) {
+    int f_lo, f_hi;
+    team_share(tm, d.F, f_lo, f_hi);
+    const int S = d.S, FS = d.F * S;
+    double acc = 0.0;
+    for (int i = 12 * f_lo + threadIdx.x; i < 12 * f_hi; i += blockDim.x) acc += count_term(k.cs[i], k.wn[i]);
+    for (int i = f_lo * S + threadIdx.x; i < f_hi * S; i += blockDim.x) {
+        double t = count_term(k.cg[i], k.pg[i]);
+        for (int z = 0; z < d.Z; ++z) t += count_term(k.cz[(size_t)z * FS + i], k.pz[(size_t)z * FS + i]);
+        if (d.C == 3)
+            for (int m = 0; m < d.Fam; ++m) t += count_term(k.cf[(size_t)m * FS + i], k.pf[(size_t)m * FS + i]);
+        acc += t;
     }
-    return dll;
+    return team_sum(acc, sh, tm);
 }
 
+// ---- K7c: Gibbs operators on the count tables ----------------------------------------------------
 // gibbs_sample_weights (zone_sampling.py:222-331).  Always accepted (incl. quirk Q2: with inheritance the
 // per-feature MH decision is overwritten by `sample_new.weights = w_new`, :325-327).
 __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, uint64_t step, bool fixed_inheritance,
-                                 double& ll_acc, const Team& tm) {
+                                 const Team& tm) {
     // fixed = choice(['inheritance', 'contact'])  (:249): fixed_inheritance = (uniform(step, RP_FIXED) < 0.5)
-    // phase A (one thread per feature): the two Gammas of the feature's Beta / Dirichlet draw in lock-step, then the
-    // new weight row, staged in the scratch ([0,3F))
+    // One thread per feature: the two Gammas of the feature's Beta / Dirichlet draw in lock-step, the new weight row
+    // and its normalised table (wnorm_row: the same arithmetic as every other producer of w~).  The likelihood change
+    // is not formed here: with SAMPLE_SOURCE the likelihood is a function of the count tables, see ll_from_counts.
     const int a = (d.C == 2) ? 1 : (fixed_inheritance ? 1 : 2);   // cfg of the "only this component" sites; also column x
     int f_lo, f_hi;
     team_share(tm, d.F, f_lo, f_hi);                    // each CTA of the team owns a contiguous range of features
     PROF_T(tw0);
-    // Everything a feature needs from global memory (its 12 source counts, 3 weights, 12 old normalised weights) is
-    // requested in one batch at the top; the live entries are staged in the scratch (stride SB_W_STRIDE doubles per
-    // feature: new weights | old w~ | counts), so phase C touches global memory only to store.
     for (int f = f_lo + threadIdx.x; f < f_hi; f += blockDim.x) {
         const int4* cs4 = reinterpret_cast<const int4*>(k.cs + (size_t)f * 12);
         const int4 ca = cs4[0], cb = cs4[1], cc = cs4[2];
-        const int cs[12] = {ca.x, ca.y, ca.z, ca.w, cb.x, cb.y, cb.z, cb.w, cc.x, cc.y, cc.z, cc.w};
         double* w = k.w + (size_t)f * 3;
         double v[3] = {w[0], w[1], d.C == 3 ? w[2] : 0.0};
-        const double2* wn2 = reinterpret_cast<const double2*>(k.wn + (size_t)f * 12);
-        double* stage = k.scratch + (size_t)f * SB_W_STRIDE;
-#pragma unroll
-        for (int q = 1; q < 6; ++q) {                       // entries 2..11 (entries 0..2 = cfg 0 are constant)
-            const double2 t = wn2[q];
-            stage[3 + 2 * q - 2] = t.x;                     // old w~[idx] at stage[3 + idx - 2]
-            stage[3 + 2 * q - 1] = t.y;
-        }
-#pragma unroll
-        for (int i = 2; i < 12; ++i) stage[13 + i - 2] = (double)cs[i];       // counts at stage[13 + idx - 2]
         int c0, c1;
-        if (d.C == 2) { c0 = cs[3 + 0]; c1 = cs[3 + 1]; }                  // counts over sites with a zone (:239-243)
-        else if (a == 1) { c0 = cs[4] + cs[10]; c1 = cs[3] + cs[9]; }      // c_x, c_univ over has_zone sites (:256-259)
-        else { c0 = cs[8] + cs[11]; c1 = cs[6] + cs[9]; }                  // ... over has_family sites     (:283-286)
+        if (d.C == 2) { c0 = ca.w; c1 = cb.x; }                            // counts over sites with a zone (:239-243)
+        else if (a == 1) { c0 = cb.x + cc.z; c1 = ca.w + cc.y; }           // c_x, c_univ over has_zone sites (:256-259)
+        else { c0 = cc.x + cc.w; c1 = cb.z + cc.y; }                       // ... over has_family sites     (:283-286)
         double g0, g1;
         rng_gamma2(key, step, RP_BETA_A, (uint32_t)f, 1.0 + (double)c0, true, RP_BETA_B, (uint32_t)f, 1.0 + (double)c1,
                    true, g0, g1);
@@ -653,19 +633,11 @@ __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, u
         for (int c = 0; c < 3; ++c) {
             v[c] /= s;
             w[c] = v[c];
-            stage[c] = v[c];
         }
+        wnorm_row(v, k.wn + (size_t)f * 12, d.C);
     }
     PROF_T(tw1);
-    __syncthreads();
-    PROF_T(tw2);
-    // phase C (one thread per non-constant entry of the normalised table): w~_new and the complete-data likelihood
-    // change  sum cnt_src * log(w~_new / w~_old).  Entries of impossible (cfg, component) pairs stay 0 and cfg 0 stays
-    // (1, 0, 0) for ever, so only 7 (C = 3) or 2 (C = 2) entries per feature are live.
-    const double dll = d.C == 3 ? weights_phase_c<7>(k, f_lo, f_hi) : weights_phase_c<2>(k, f_lo, f_hi);
-    PROF_T(tw3);
-    ll_acc += dll;              // thread-private: summed over the team when somebody needs the total
-    PROF_ADD(7, tw0, tw1); PROF_ADD(8, tw1, tw2); PROF_ADD(9, tw2, tw3);
+    PROF_ADD(7, tw0, tw1);
 }
 
 // Shared body of gibbs_sample_p_global / p_zones / p_families (zone_sampling.py:334-406):
@@ -676,21 +648,20 @@ __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, u
 __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Chain& k, RngKey key, uint64_t step,
                                 double* p, const int* cnt, const double* pc, bool use_subset,
                                 const double* alpha, const double* lnorm, double* pcache,
-                                double& ll_acc, double& prior_acc, const Team& tm) {
+                                double& prior_acc, const Team& tm) {
     const int S = d.S;
     int f_lo, f_hi;
     team_share(tm, d.F, f_lo, f_hi);                    // whole rows per CTA: the row totals stay CTA-local
     const int i_lo = f_lo * S, i_hi = f_hi * S;
     PROF_T(t0);
-    double dll = 0.0, dpr = 0.0;
+    double dpr = 0.0;
     const int bd = blockDim.x;
     constexpr int R = 4;                                 // items per thread held in registers
     if (tm.size > 1 && i_hi - i_lo <= R * bd) {
         // Fast path: a thread's (feature, state) items stay in registers across the phases, and everything it needs
-        // from global memory (counts, prior pseudo-counts, old probabilities) is requested up front in one batch --
-        // after a team barrier these loads come from L2, and one overlapped round trip replaces several serial ones.
+        // from global memory (counts, prior pseudo-counts) is requested up front in one batch.
         int fi[R], ci[R];
-        double al[R], po[R];
+        double al[R];
         bool app[R];
 #pragma unroll
         for (int r = 0; r < R; ++r) {
@@ -700,7 +671,6 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
             app[r] = in && (d.app_mask[fi[r]] >> (i - fi[r] * S) & 1u);
             ci[r] = app[r] ? cnt[i] : 0;
             al[r] = (app[r] && pc) ? pc[i] : 1.0;
-            po[r] = app[r] ? p[i] : 1.0;
         }
         // phase 0: feature subset (one draw per feature); marker -1 in the feature's first scratch slot = not selected
         for (int f = f_lo + threadIdx.x; f < f_hi; f += bd)
@@ -716,8 +686,8 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
         PROF_T(t1);
         __syncthreads();
         PROF_T(t2);
-        // phase 2: normalise, write, accumulate the likelihood delta; the S threads of a row each form the row total
-        // in the same order, so they agree bit for bit
+        // phase 2: normalise and write; the S threads of a row each form the row total in the same order, so they
+        // agree bit for bit.  (No likelihood delta: see ll_from_counts.)
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const int i = i_lo + (int)threadIdx.x + r * bd;
@@ -725,9 +695,7 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
             if (!app[r] || g[0] < 0.0) continue;
             double tot = 0.0;
             for (int t = 0; t < S; ++t) tot += g[t];
-            const double pn = g[i - fi[r] * S] / tot;
-            if (ci[r] > 0) dll += (double)ci[r] * flog(pn / po[r], k.flt);
-            p[i] = pn;
+            p[i] = g[i - fi[r] * S] / tot;
         }
         PROF_T(t3);
         PROF_ADD(0, t0, t1); PROF_ADD(1, t1, t2); PROF_ADD(2, t2, t3);
@@ -746,17 +714,14 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
         k.scratch[i] = g;
     }
     __syncthreads();
-    // phase 2: normalise, write, accumulate the likelihood delta -- one thread per (feature, state)
+    // phase 2: normalise and write -- one thread per (feature, state)
     for (int i = i_lo + threadIdx.x; i < i_hi; i += blockDim.x) {
         const int f = (int)__umulhi((unsigned)i, sp.s_magic), s = i - f * S;
         const double* g = k.scratch + (size_t)f * S;
         if (g[0] < 0.0 || !(d.app_mask[f] >> s & 1u)) continue;
         double tot = 0.0;
         for (int t = 0; t < S; ++t) tot += g[t];
-        const double pn = g[s] / tot;
-        const int c = cnt[i];
-        if (c > 0) dll += (double)c * flog(pn / p[i], k.flt);
-        p[i] = pn;
+        p[i] = g[s] / tot;
     }
     }
     if (alpha) {
@@ -768,8 +733,7 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
             pcache[f] = v;
         }
     }
-    ll_acc += dll;              // thread-private: summed over the team when somebody needs the total
-    prior_acc += dpr;
+    prior_acc += dpr;           // thread-private: summed over the team at the end of the launch
 }
 
 // ---- K7d: alter_* operators (source-free mode), zone_sampling.py:408-612 --------------------------
@@ -957,9 +921,12 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
 
     bool dirty = false;         // a Gibbs operator wrote chain tables since the last full team barrier
     // The Gibbs operators are always accepted, and nobody needs the absolute ll / prior inside a launch (the
-    // Metropolis steps work on deltas), so their likelihood / prior changes stay in thread-private accumulators and
-    // are summed over the team once, at the end of the launch: a Gibbs step has no reduction and no team traffic.
-    double ll_acc = 0.0, prior_acc = 0.0;
+    // Metropolis steps work on deltas).  So a Gibbs step has no reduction and no team traffic: its prior change stays
+    // in a thread-private accumulator that is summed over the team at the end of the launch, and its likelihood
+    // change is not formed at all -- the running ll is re-formed from the count tables (ll_from_counts) if a Gibbs
+    // operator ran after the last from-scratch value.
+    double prior_acc = 0.0;
+    bool ll_stale = false;
     for (long long it = 0; it < n_steps; ++it) {
         const uint64_t step = step0 + (uint64_t)it;
         PROF_T(ts0);
@@ -989,6 +956,7 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
                                     op == SB_OP_GIBBS_P_ZONES || op == SB_OP_GIBBS_P_FAMILIES;
         if (gibbs_table_op) {
             dirty = true;
+            ll_stale = true;
         } else if (dirty) {
             team_sync(tm);
             dirty = false;
@@ -997,26 +965,26 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
             case SB_OP_SHRINK_ZONE: case SB_OP_GROW_ZONE: case SB_OP_SWAP_ZONE:
                 accepted = op_zone_move(d, sp, k, op, chain, key, step, ll, prior, geo, nbr, freeb, prim_key,
                                         prim_tree, sh, tm, synced);
-                if (accepted && d.sample_source) ll_acc = 0.0;      // ll was recomputed from scratch by the source sweep
+                if (accepted && d.sample_source) ll_stale = false;  // ll was recomputed from scratch by the source sweep
                 break;
             case SB_OP_GIBBS_SOURCES:
                 ll = resample_sources(d, k, key, step, sh, tm);
-                ll_acc = 0.0;
+                ll_stale = false;
                 synced = true;
                 break;
             case SB_OP_GIBBS_WEIGHTS:
-                op_gibbs_weights(d, k, key, step, sh.u_ahead[2][ia] < 0.5, ll_acc, tm);
+                op_gibbs_weights(d, k, key, step, sh.u_ahead[2][ia] < 0.5, tm);
                 synced = true;
                 break;
             case SB_OP_GIBBS_P_GLOBAL:
                 gibbs_table_row(d, sp, k, key, step, k.pg, k.cg, d.gibbs_g, true,
-                                d.pg_type == 1 ? d.alpha_g : nullptr, d.lnorm_g, k.ppg, ll_acc, prior_acc, tm);
+                                d.pg_type == 1 ? d.alpha_g : nullptr, d.lnorm_g, k.ppg, prior_acc, tm);
                 synced = true;
                 break;
             case SB_OP_GIBBS_P_ZONES: {
                 const size_t o = (size_t)ahead_int(sh.u_ahead[0][ia], d.Z) * d.F * d.S;
                 gibbs_table_row(d, sp, k, key, step, k.pz + o, k.cz + o, nullptr, false, nullptr, nullptr, nullptr,
-                                ll_acc, prior_acc, tm);
+                                prior_acc, tm);
                 synced = true;
                 break;
             }
@@ -1025,7 +993,7 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
                 const size_t o = (size_t)fam * d.F * d.S;
                 gibbs_table_row(d, sp, k, key, step, k.pf + o, k.cf + o, d.gibbs_f + o, true,
                                 d.pf_type == 1 ? d.alpha_f + o : nullptr, d.lnorm_f + (size_t)fam * d.F,
-                                k.ppf + (size_t)fam * d.F, ll_acc, prior_acc, tm);
+                                k.ppf + (size_t)fam * d.F, prior_acc, tm);
                 synced = true;
                 break;
             }
@@ -1041,9 +1009,8 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
         PROF_T(ts3);
         PROF_ADD(4, ts0, ts1); PROF_ADD(5, ts1, ts2); PROF_ADD(6, ts2, ts3);
     }
-    team_sum2(ll_acc, prior_acc, sh, tm);
-    ll += ll_acc;
-    prior += prior_acc;
+    if (ll_stale) ll = ll_from_counts(d, k, sh, tm);       // reads this CTA's own feature range only
+    prior += team_sum(prior_acc, sh, tm);
     if (threadIdx.x == 0 && tm.rank == 0) {
         st.ll[chain] = ll; st.prior[chain] = prior; st.geo[chain] = geo;
         st.step[chain] = step0 + (uint64_t)n_steps;
