@@ -829,28 +829,21 @@ static size_t step_smem_base(const StepParams& sp) {
     const size_t words = 2 * (size_t)sp.nwords + (sp.nwords & 1);
     return (words * sizeof(unsigned) + (size_t)sp.prim_cap * 9 + 16 + 15) & ~(size_t)15;
 }
-// Shared work area of the step kernel (one CTA per SM, so up to ~200 KB): the Gibbs scratch and the count tables of
-// the source sweep are used at different times and overlay each other; whatever does not fit stays in global memory.
+// Shared work area of the step kernel (one CTA per SM, so up to ~200 KB): the count tables of one 16-feature block
+// of the source sweep; if they do not fit, the sweep falls back to global atomics.
 static size_t step_smem_bytes(const DevData& d, StepParams& sp) {
     const size_t base = step_smem_base(sp);
-    const size_t scratch = (size_t)d.F * d.S * sizeof(double);
     const size_t counts = ((size_t)16 * d.S * (1 + d.Z + d.Fam) + 192) * sizeof(int);
     const size_t room = 160 * 1024 > base ? 160 * 1024 - base : 0;
     sp.work_off = (int)base;
-    sp.work_scratch = scratch <= room;
     sp.work_counts = d.sample_source && counts <= room;
-    size_t work = 0;
-    if (sp.work_scratch) work = scratch;
-    if (sp.work_counts && counts > work) work = counts;
-    return base + work;
+    return base + (sp.work_counts ? counts : 0);
 }
 
 static int ensure_step_scratch(sb_ctx* ctx) {
     StepParams& sp = ctx->sp;
     const DevData& d = ctx->d;
-    if (!sp.scratch) {
-        sp.s_scratch = (size_t)d.F * d.S;     // Gamma draws [F][S]
-        DA(sp.scratch, (size_t)ctx->dims.n_chains * sp.s_scratch);
+    if (!sp.tmp_members) {
         sp.s_tmp = (size_t)d.N;
         DA(sp.tmp_members, (size_t)ctx->dims.n_chains * sp.s_tmp);
     }
@@ -900,7 +893,8 @@ int sb_set_operators(sb_ctx* ctx, const sb_operator_cfg* cfg, const double* p_gr
     sp.prec_z = cfg->precision_p_zones; sp.prec_f = cfg->precision_p_families;
     sp.min_size = cfg->min_size;
     sp.frac = cfg->gibbs_feature_fraction;
-    sp.s_magic = (unsigned)((((uint64_t)1 << 32) + (uint64_t)d.S - 1) / (uint64_t)d.S);
+    sp.s_shift = 0;
+    while ((1 << sp.s_shift) < d.S) ++sp.s_shift;         // S <= SB_MAX_S = 32
     if ((uint64_t)d.F * d.S >= ((uint64_t)1 << 27)) FAIL(SB_E_ARG, "F*S too large for the step kernel");
     sp.seed_lo = (uint32_t)cfg->seed; sp.seed_hi = (uint32_t)(cfg->seed >> 32);
     int r = ensure_step_scratch(ctx);

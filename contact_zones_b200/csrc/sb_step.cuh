@@ -46,13 +46,10 @@ struct StepParams {
     const int* max_size;      // [chains]
     int nwords;               // words of one site bitmap
     int prim_cap;             // member capacity of the Prim scratch
-    unsigned s_magic;         // ceil(2^32 / S): i / S == __umulhi(i, s_magic) for i < 2^27
+    int s_shift;              // log2 of the smallest power of two >= S (S <= SB_MAX_S = 32)
     int team;                 // CTAs per chain (thread-block cluster size): 1, 2, 4 or 8
     int work_off;             // byte offset of the shared work area in the dynamic smem (16 B aligned)
-    int work_scratch;         // != 0: the Gibbs scratch ([F][max(S,12)] doubles) lives in the work area
     int work_counts;          // != 0: resample_all_sources keeps per-feature-block count tables in the work area
-    double* scratch;          // [chains][F*S]   Gamma draws of the Gibbs operators
-    size_t s_scratch;
     int* tmp_members;         // [chains][N]     candidate member list for the geo prior
     size_t s_tmp;
 };
@@ -224,7 +221,7 @@ struct Chain {
     uint8_t* src;
     int* cg; int* cz; int* cf; int* cs;
     double* ppg; double* ppf;
-    double* scratch; int* tmp;
+    int* tmp;
     int* cnt_tab;       // shared-memory count tables of resample_all_sources_blocked, or null
     const double2* flt; // shared-memory table of flog()
 };
@@ -238,7 +235,7 @@ __device__ __forceinline__ Chain chain_view(const ChainArrays& st, const StepPar
     k.cg = st.cnt_glob + c * st.s_cnt_glob; k.cz = st.cnt_zone + c * st.s_cnt_zone;
     k.cf = st.cnt_fam + c * st.s_cnt_fam; k.cs = st.cnt_src + c * st.s_cnt_src;
     k.ppg = st.prior_pg + c * st.s_prior_pg; k.ppf = st.prior_pf + c * st.s_prior_pf;
-    k.scratch = sp.scratch + c * sp.s_scratch; k.tmp = sp.tmp_members + c * sp.s_tmp;
+    k.tmp = sp.tmp_members + c * sp.s_tmp;
     k.cnt_tab = nullptr;
     k.flt = nullptr;
     return k;
@@ -609,7 +606,12 @@ __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, u
     int f_lo, f_hi;
     team_share(tm, d.F, f_lo, f_hi);                    // each CTA of the team owns a contiguous range of features
     PROF_T(tw0);
-    for (int f = f_lo + threadIdx.x; f < f_hi; f += blockDim.x) {
+    // The features go to the LAST warps of the CTA: in the table operators the first warps own two items each and the
+    // last ones one, and with barrier-free Gibbs steps (see mcmc_step_kernel) it is the per-warp total that counts.
+    const int nf = f_hi - f_lo, bd = blockDim.x;
+    const int first = bd - min(bd, (nf + 31) & ~31);
+    const int t0 = (int)threadIdx.x >= first ? (int)threadIdx.x - first : (int)threadIdx.x + bd - first;
+    for (int f = f_lo + t0; f < f_hi; f += bd) {
         const int4* cs4 = reinterpret_cast<const int4*>(k.cs + (size_t)f * 12);
         const int4 ca = cs4[0], cb = cs4[1], cc = cs4[2];
         double* w = k.w + (size_t)f * 3;
@@ -652,89 +654,46 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
     const int S = d.S;
     int f_lo, f_hi;
     team_share(tm, d.F, f_lo, f_hi);                    // whole rows per CTA: the row totals stay CTA-local
-    const int i_lo = f_lo * S, i_hi = f_hi * S;
-    PROF_T(t0);
-    double dpr = 0.0;
-    const int bd = blockDim.x;
-    constexpr int R = 4;                                 // items per thread held in registers
-    if (tm.size > 1 && i_hi - i_lo <= R * bd) {
-        // Fast path: a thread's (feature, state) items stay in registers across the phases, and everything it needs
-        // from global memory (counts, prior pseudo-counts) is requested up front in one batch.
-        int fi[R], ci[R];
-        double al[R];
-        bool app[R];
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const int i = i_lo + (int)threadIdx.x + r * bd;
-            const bool in = i < i_hi;
-            fi[r] = in ? (int)__umulhi((unsigned)i, sp.s_magic) : f_lo;
-            app[r] = in && (d.app_mask[fi[r]] >> (i - fi[r] * S) & 1u);
-            ci[r] = app[r] ? cnt[i] : 0;
-            al[r] = (app[r] && pc) ? pc[i] : 1.0;
-        }
-        // phase 0: feature subset (one draw per feature); marker -1 in the feature's first scratch slot = not selected
-        for (int f = f_lo + threadIdx.x; f < f_hi; f += bd)
-            k.scratch[(size_t)f * S] = (use_subset && !(rng_uniform(key, step, RP_SUBSET, f) < sp.frac)) ? -1.0 : 0.0;
-        __syncthreads();
-        // phase 1: Gamma draws (a selected feature's first slot only ever holds values >= 0, so the test is stable)
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const int i = i_lo + (int)threadIdx.x + r * bd;
-            if (i >= i_hi || k.scratch[(size_t)fi[r] * S] < 0.0) continue;
-            k.scratch[i] = app[r] ? rng_gamma(key, step, RP_GAMMA, i, al[r] + (double)ci[r]) : 0.0;
+    {
+        // Warp-autonomous form (S <= SB_MAX_S = 32): a row (feature) occupies 2^s_shift consecutive lanes of one warp, one lane
+        // per state.  Every lane draws its Gamma, the row total is a shuffle tree inside the lane group, and the lane
+        // writes its own probability: no shared memory, no CTA barrier, and a (feature, state) item belongs to the
+        // same thread in every step.  The subset draw of a feature (:335, 385) is recomputed by the lanes of its row
+        // (same counter, same value; one instruction stream per warp either way).
+        const int Sp = 1 << sp.s_shift;
+        const int n_slots = (f_hi - f_lo) << sp.s_shift;
+        double dpr = 0.0;
+        PROF_T(t0);
+        for (int base = 0; base < n_slots; base += blockDim.x) {           // CTA-uniform trip count
+            const int slot = base + (int)threadIdx.x;
+            const int f = f_lo + (slot >> sp.s_shift), s = slot & (Sp - 1);
+            const bool row = slot < n_slots;
+            const int i = f * S + s;
+            const bool app = row && s < S && (d.app_mask[f] >> s & 1u);
+            bool fsel = row;
+            if (use_subset) fsel = fsel && rng_uniform(key, step, RP_SUBSET, f) < sp.frac;
+            const bool sel = fsel && app;
+            double g = 0.0;
+            if (sel) g = rng_gamma(key, step, RP_GAMMA, i, (pc ? pc[i] : 1.0) + (double)cnt[i]);
+            double tot = g;
+            for (int o = Sp >> 1; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+            if (sel) p[i] = g / tot;
+            if (alpha) {                                                    // prior change of the rows just written
+                __syncwarp();
+                if (fsel && s == 0) {
+                    const double v = dirichlet_row(p + (size_t)f * S, alpha + (size_t)f * S, lnorm[f], d.app_mask[f], S);
+                    dpr += v - pcache[f];
+                    pcache[f] = v;
+                }
+                __syncwarp();
+            }
         }
         PROF_T(t1);
-        __syncthreads();
-        PROF_T(t2);
-        // phase 2: normalise and write; the S threads of a row each form the row total in the same order, so they
-        // agree bit for bit.  (No likelihood delta: see ll_from_counts.)
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const int i = i_lo + (int)threadIdx.x + r * bd;
-            const double* g = k.scratch + (size_t)fi[r] * S;
-            if (!app[r] || g[0] < 0.0) continue;
-            double tot = 0.0;
-            for (int t = 0; t < S; ++t) tot += g[t];
-            p[i] = g[i - fi[r] * S] / tot;
-        }
-        PROF_T(t3);
-        PROF_ADD(0, t0, t1); PROF_ADD(1, t1, t2); PROF_ADD(2, t2, t3);
-    } else {
-    // phase 0: feature subset (one draw per feature); marker -1 in the feature's first scratch slot = not selected
-    for (int f = f_lo + threadIdx.x; f < f_hi; f += blockDim.x)
-        k.scratch[(size_t)f * S] = (use_subset && !(rng_uniform(key, step, RP_SUBSET, f) < sp.frac)) ? -1.0 : 0.0;
-    __syncthreads();
-    // phase 1: Gamma draws, one thread per (feature, state)
-    for (int i = i_lo + threadIdx.x; i < i_hi; i += blockDim.x) {
-        const int f = (int)__umulhi((unsigned)i, sp.s_magic), s = i - f * S;
-        if (k.scratch[(size_t)f * S] < 0.0) continue;      // a selected feature's slot only ever holds values >= 0
-        double g = 0.0;
-        if (d.app_mask[f] >> s & 1u)
-            g = rng_gamma(key, step, RP_GAMMA, i, (pc ? pc[i] : 1.0) + (double)cnt[i]);
-        k.scratch[i] = g;
+        PROF_ADD(0, t0, t1);
+        prior_acc += dpr;           // thread-private: summed over the team at the end of the launch
     }
-    __syncthreads();
-    // phase 2: normalise and write -- one thread per (feature, state)
-    for (int i = i_lo + threadIdx.x; i < i_hi; i += blockDim.x) {
-        const int f = (int)__umulhi((unsigned)i, sp.s_magic), s = i - f * S;
-        const double* g = k.scratch + (size_t)f * S;
-        if (g[0] < 0.0 || !(d.app_mask[f] >> s & 1u)) continue;
-        double tot = 0.0;
-        for (int t = 0; t < S; ++t) tot += g[t];
-        p[i] = g[s] / tot;
-    }
-    }
-    if (alpha) {
-        __syncthreads();
-        for (int f = f_lo + threadIdx.x; f < f_hi; f += blockDim.x) {
-            if (k.scratch[(size_t)f * S] < 0.0) continue;
-            const double v = dirichlet_row(p + (size_t)f * S, alpha + (size_t)f * S, lnorm[f], d.app_mask[f], S);
-            dpr += v - pcache[f];
-            pcache[f] = v;
-        }
-    }
-    prior_acc += dpr;           // thread-private: summed over the team at the end of the launch
 }
+
 
 // ---- K7d: alter_* operators (source-free mode), zone_sampling.py:408-612 --------------------------
 // log pdf of a 2-component Dirichlet
@@ -907,7 +866,6 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
     unsigned char* prim_tree = reinterpret_cast<unsigned char*>(prim_key + sp.prim_cap);
 
     Chain kv = chain_view(st, sp, chain);
-    if (sp.work_scratch) kv.scratch = reinterpret_cast<double*>(step_smem + sp.work_off);
     if (sp.work_counts) kv.cnt_tab = reinterpret_cast<int*>(step_smem + sp.work_off);
     __shared__ double2 flog_tab[SB_FLOG_N];
     flog_init(flog_tab);
@@ -932,9 +890,9 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
         PROF_T(ts0);
         // operator choice: np.random.choice(fn_operators, p=p_operators)  (mcmc_generative.py:294).  The draws that
         // depend on the step number only are made SB_AHEAD steps at a time: warp w, lane l -> draw w of step + l.
-        // (The previous step ended in a CTA barrier, so nobody still reads the old table.)
         const int ia = (int)(it & (SB_AHEAD - 1));
         if (ia == 0) {
+            __syncthreads();            // Gibbs steps end without a barrier: wait until nobody reads the old table
             const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
             if (w == 0) {
                 const double uo = rng_uniform(key, step + l, RP_OP, 0);
@@ -1004,11 +962,16 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
         PROF_T(ts2);
         if (threadIdx.x == 0 && tm.rank == 0)      // fire-and-forget reduction: nobody waits for the L2 round trip
             atomicAdd((accepted ? st.acc : st.rej) + (size_t)chain * SB_N_OPS + op, 1ull);
-        // step boundary: the next step's writes must not overtake this step's reads in a slower CTA of the team
-        if (synced) __syncthreads(); else team_sync(tm);
+        // Step boundary.  The Gibbs table operators are warp-autonomous -- a thread only ever reads and writes the
+        // items it owns, in every step -- so the warps run on without a barrier until the next operator of another
+        // kind (which starts behind the `dirty` team barrier above) or the next refill of the look-ahead table.
+        // After any other operator: the next step's writes must not overtake this step's reads in a slower thread
+        // or CTA of the team.
+        if (!gibbs_table_op) { if (synced) __syncthreads(); else team_sync(tm); }
         PROF_T(ts3);
         PROF_ADD(4, ts0, ts1); PROF_ADD(5, ts1, ts2); PROF_ADD(6, ts2, ts3);
     }
+    __syncthreads();            // the warps may arrive from barrier-free Gibbs steps
     if (ll_stale) ll = ll_from_counts(d, k, sh, tm);       // reads this CTA's own feature range only
     prior += team_sum(prior_acc, sh, tm);
     if (threadIdx.x == 0 && tm.rank == 0) {
