@@ -466,6 +466,7 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
                              RngKey key, uint64_t step, double& ll, double& prior, double& geo,
                              unsigned* nbr, unsigned* freeb, double* prim_key, unsigned char* prim_tree,
                              StepShared& sh, Team& tm, bool& synced) {
+    PROF_T(tzp);
     const double rho = sp.p_grow[chain];
     const int max_size = sp.max_size[chain];
     const int z = rng_int(key, step, RP_ZONE, 0, d.Z);
@@ -479,10 +480,16 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
     const int n_free = d.N - n_occ;
     int site_new = -1, site_removed = -1;
     double q, q_back;
+    PROF_T(tz0);
+    PROF_ADD(12, tzp, tz0);
 
     if (kind != SB_OP_SHRINK_ZONE) {
         build_nbr_bits(d, k.zone_id, mem, size, -1, nbr, sp.nwords);
+        PROF_T(tz1);
+        PROF_ADD(8, tz0, tz1);
         const int n_nbr = bits_count(nbr, sp.nwords, sh.redi);
+        PROF_T(tz2);
+        PROF_ADD(9, tz1, tz2);
         const bool connected = rng_uniform(key, step, RP_CONNECTED, 0) < rho;     // :731,823
         const int n_cand = connected ? n_nbr : n_free;
         if (n_cand == 0) return false;                                            // :740-741, 832-833
@@ -512,11 +519,15 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
         if (d.warmup) q_back = 1.0 / (double)(size + 1);                          // :1552 (quirk Q3)
     }
     __syncthreads();
+    PROF_T(tz3);
+    PROF_ADD(10, tz0, tz3);
 
     // likelihood ratio of the moved site(s)
     double dll = 0.0;
     if (site_new >= 0) dll += site_zone_delta(d, k, site_new, -1, z, sh, tm);
     if (site_removed >= 0) dll += site_zone_delta(d, k, site_removed, z, -1, sh, tm);
+    PROF_T(tz4);
+    PROF_ADD(11, tz3, tz4);
 
     // prior ratio: only the size and geo terms depend on the zones
     const int new_size = size + (site_new >= 0 ? 1 : 0) - (site_removed >= 0 ? 1 : 0);
@@ -542,6 +553,8 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
         const double mh = dll - flog(q / q_back, k.flt) + dprior;                 // mcmc_generative.py:345-349
         accept = flog(rng_uniform(key, step, RP_ACCEPT, 0), k.flt) < mh;          // :318
     }
+    PROF_T(tz5);
+    PROF_ADD(13, tz4, tz5);
     if (!accept) return false;
 
     // Proposal and decision above are computed redundantly (and identically) by every CTA of the team from the old
@@ -626,17 +639,30 @@ __device__ void op_gibbs_weights(const DevData& d, const Chain& k, RngKey key, u
         if (d.C == 2) {
             v[0] = g0; v[1] = g1;                           // Dir(1 + counts) = normalised Gammas
         } else {
-            const double ax = g0 / (g0 + g1);               // ~ Beta(1 + c_x, 1 + c_univ)      (:262-265, 289-292)
-            const double nv = ax * v[0] / (1.0 - ax);       // :270, 297
+            // a_x ~ Beta(1 + c_x, 1 + c_univ) = g0 / (g0 + g1)  (:262-265, 289-292);  w_x = a_x w_univ / (1 - a_x)
+            // (:270, 297), and a_x / (1 - a_x) = g0 / g1
+            const double nv = v[0] * (g0 / g1);
             if (a == 1) v[1] = nv; else v[2] = nv;
         }
-        const double s = (v[0] + v[1]) + v[2];              // normalize(w_new) :271, 298
+        const double rs = 1.0 / ((v[0] + v[1]) + v[2]);     // normalize(w_new) :271, 298
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-            v[c] /= s;
+            v[c] *= rs;
             w[c] = v[c];
         }
-        wnorm_row(v, k.wn + (size_t)f * 12, d.C);
+        // the entries of w~ that can change (wnorm_row's arithmetic: a_c / ((a_0 + a_1) + a_2)); the others are the
+        // constants 1 and 0 written at upload
+        double* wn = k.wn + (size_t)f * 12;
+        const double s1 = v[0] + v[1];
+        const double q3 = v[0] / s1, q4 = v[1] / s1;
+        wn[3] = q3; wn[4] = q4;
+        if (d.C == 3) {
+            const double s2 = v[0] + v[2], s3 = s1 + v[2];
+            wn[6] = v[0] / s2; wn[8] = v[2] / s2;
+            wn[9] = v[0] / s3; wn[10] = v[1] / s3; wn[11] = v[2] / s3;
+        } else {
+            wn[9] = q3; wn[10] = q4;                        // cfg 3 = cfg 1 without a family component
+        }
     }
     PROF_T(tw1);
     PROF_ADD(7, tw0, tw1);

@@ -18,8 +18,8 @@ for c in range(64):
     eng.set_state(c, s['zones'], s['weights'], s['p_global'], s['p_zones'], s['p_families'], np.argmax(s['source'], -1))
 eng.eval()
 buf = (C.c_ulonglong * 16)()
-names = ['gibbs:phase0+1', 'gibbs:sync', 'gibbs:phase2', 'gibbs:reduce', 'step:op-select', 'step:operator', 'step:tail-sync', 'w:phaseA', 'w:sync', 'w:phaseC', 'w:reduce', 'cluster.sync']
-for k in ('gibbs_sample_p_zones', 'gibbs_sample_weights', 'gibbs_sample_p_global', 'swap_zone'):
+names = ['gibbs:phase0+1', 'gibbs:sync', 'gibbs:phase2', 'gibbs:reduce', 'step:op-select', 'step:operator', 'step:tail-sync', 'w:all', 'z:nbr', 'z:count', 'z:proposal', 'z:delta', 'z:prelude', 'z:decide']
+for k in ('swap_zone', 'grow_zone', 'shrink_zone'):
     eng.set_operators({k: 1.0}, bench.PRECISION, min_size=3, max_size=50, p_grow_connected=0.85, seed=1)
     eng.run(20); eng.sync()
     eng.lib.sb_prof_read(buf, 1)
