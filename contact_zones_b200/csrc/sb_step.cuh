@@ -57,6 +57,12 @@ struct StepParams {
 // ---- shared scratch of the step kernel -----------------------------------------------------------
 #define STEP_WARPS (STEP_THREADS / 32)
 #define SB_AHEAD 32
+// uniforms that depend on the step number only, drawn SB_AHEAD steps at a time (index into StepShared::u_ahead)
+enum { UA_ZONE = 0, UA_FAMILY, UA_FIXED, UA_CONNECTED, UA_SITE_NEW, UA_SITE_REMOVED, UA_ACCEPT, SB_N_AHEAD };
+__host__ __device__ constexpr uint32_t ahead_purpose(int q) {
+    return q == UA_ZONE ? RP_ZONE : q == UA_FAMILY ? RP_FAMILY : q == UA_FIXED ? RP_FIXED : q == UA_CONNECTED ? RP_CONNECTED
+         : q == UA_SITE_NEW ? RP_SITE_NEW : q == UA_SITE_REMOVED ? RP_SITE_REMOVED : RP_ACCEPT;
+}
 struct StepShared {
     double red[33];
     int redi[33];
@@ -66,7 +72,7 @@ struct StepShared {
     // per-step scalar draws of the next SB_AHEAD steps (operator id and the uniforms behind "which zone / family /
     // fixed component"), filled by four warps once per SB_AHEAD steps instead of by every thread in every step
     int op_ahead[SB_AHEAD];
-    double u_ahead[3][SB_AHEAD];        // RP_ZONE, RP_FAMILY, RP_FIXED
+    double u_ahead[SB_N_AHEAD][SB_AHEAD];
 };
 
 // ---- site bitmaps in shared memory -----------------------------------------------------------
@@ -84,7 +90,9 @@ __device__ __forceinline__ int bits_count(const unsigned* bits, int nwords, int*
 
 // index of the k-th (0-based) set bit, ascending site order == order of `candidates.nonzero()[0]`
 // (zone_sampling.py:744,836).  Executed by warp 0; result broadcast through *out.  Caller syncs.
-__device__ void bits_select(const unsigned* bits, int nwords, int k, int* out) {
+// With `total` non-null the number of set bits n is stored there and the bit picked is floor(u * n) (capped at
+// n - 1; nothing is picked if n == 0); otherwise k is used as given.
+__device__ void bits_select(const unsigned* bits, int nwords, int k, int* out, int* total = nullptr, double u = 0.0) {
     if (threadIdx.x >= 32) return;
     const int lane = threadIdx.x;
     const int per = (nwords + 31) / 32;
@@ -96,6 +104,11 @@ __device__ void bits_select(const unsigned* bits, int nwords, int k, int* out) {
     for (int o = 1; o < 32; o <<= 1) {
         const int t = __shfl_up_sync(0xffffffffu, incl, o);
         if (lane >= o) incl += t;
+    }
+    if (total) {
+        const int n = __shfl_sync(0xffffffffu, incl, 31);
+        if (lane == 0) *total = n;
+        k = ahead_int(u, n);            // -1 if n == 0: no lane matches below
     }
     const int excl = incl - c;
     if (k >= excl && k < incl) {
@@ -161,6 +174,15 @@ struct Team {
 __device__ __forceinline__ void team_sync(const Team& t) {
     if (t.size > 1) cg::this_cluster().sync(); else __syncthreads();
 }
+// Execution barrier of the team without memory ordering beyond the CTA: enough between a step that only READ the
+// chain state and the next step's writes; unlike cluster.sync() it does not invalidate L1 (no CCTL.IVALL).
+__device__ __forceinline__ void team_sync_exec(const Team& t) {
+    __syncthreads();
+    if (t.size > 1) {
+        asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+        asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
+    }
+}
 // contiguous share [lo, hi) of n items for this CTA
 __device__ __forceinline__ void team_share(const Team& t, int n, int& lo, int& hi) {
     const int per = (n + t.size - 1) >> t.shift;
@@ -181,15 +203,10 @@ __device__ __forceinline__ void sum2_scope(double& a, double& b, StepShared& sh,
     double sa = 0.0, sb = 0.0;
     if (scope > 1) {
         cg::cluster_group cl = cg::this_cluster();
-#ifdef SB_RELAXED_BARRIER      // timing experiment only: no release/acquire, hence no L1 invalidation
-        asm volatile("barrier.cluster.arrive.relaxed.aligned;\n" ::: "memory");
-        asm volatile("barrier.cluster.wait.aligned;\n" ::: "memory");
-#else
         PROF_T(tb0);
         cl.sync();
         PROF_T(tb1);
         PROF_ADD(11, tb0, tb1);
-#endif
         for (int r = 0; r < scope; ++r) {
             const double* peer = cl.map_shared_rank(slot, r);
             sa += warp_sum(lane < STEP_WARPS ? peer[lane] : 0.0);
@@ -256,15 +273,19 @@ __device__ __forceinline__ double cell_mix(const DevData& d, const Chain& k, int
 // K5a: log marginal-likelihood change of ONE site whose zone assignment changes zid_old -> zid_new
 // (either may be -1).  Sum over features of log mix_new - log mix_old; NA cells contribute 0 in both the
 // source-free likelihood (model.py:247) and the source-marginalised Hastings ratio.
-__device__ double site_zone_delta(const DevData& d, const Chain& k, int site, int zid_old, int zid_new, StepShared& sh,
-                                  Team& tm) {
-    const int fam = d.inheritance ? d.fam_id[site] : -1;
+// Marginal-likelihood change of a zone move: site_new joins zone z and / or site_removed leaves it (-1 = none).
+// One pass over the features and ONE reduction for both sites.
+__device__ double zone_move_delta(const DevData& d, const Chain& k, int site_new, int site_removed, int z,
+                                  StepShared& sh, Team& tm) {
+    const int fam_n = (d.inheritance && site_new >= 0) ? d.fam_id[site_new] : -1;
+    const int fam_r = (d.inheritance && site_removed >= 0) ? d.fam_id[site_removed] : -1;
     double acc = 0.0;
     for (int f = threadIdx.x; f < d.F; f += blockDim.x) {
-        const int xs = d.x[(size_t)site * d.ldx + f];
-        if (xs == SB_NA) continue;
+        const int xn = site_new >= 0 ? d.x[(size_t)site_new * d.ldx + f] : SB_NA;
+        const int xr = site_removed >= 0 ? d.x[(size_t)site_removed * d.ldx + f] : SB_NA;
         const double* wrow = k.wn + (size_t)f * 12;
-        acc += flog(cell_mix(d, k, f, xs, zid_new, fam, wrow) / cell_mix(d, k, f, xs, zid_old, fam, wrow), k.flt);
+        if (xn != SB_NA) acc += flog(cell_mix(d, k, f, xn, z, fam_n, wrow) / cell_mix(d, k, f, xn, -1, fam_n, wrow), k.flt);
+        if (xr != SB_NA) acc += flog(cell_mix(d, k, f, xr, -1, fam_r, wrow) / cell_mix(d, k, f, xr, z, fam_r, wrow), k.flt);
     }
     return cta_sum(acc, sh, tm);        // every CTA of the team evaluates the whole delta (F terms) itself
 }
@@ -465,11 +486,13 @@ __device__ __forceinline__ double grow_q(bool in_nbr, int n_free, int n_nbr, dou
 __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain& k, int kind, int chain,
                              RngKey key, uint64_t step, double& ll, double& prior, double& geo,
                              unsigned* nbr, unsigned* freeb, double* prim_key, unsigned char* prim_tree,
-                             StepShared& sh, Team& tm, bool& synced) {
+                             StepShared& sh, Team& tm, const double* ua, bool& synced, bool& wrote_nothing) {
+    wrote_nothing = true;       // until the proposal is accepted: a rejected move only read the chain state
+    // ua: this step's column of the look-ahead table (ua[q * SB_AHEAD] = uniform q of the step)
     PROF_T(tzp);
     const double rho = sp.p_grow[chain];
     const int max_size = sp.max_size[chain];
-    const int z = rng_int(key, step, RP_ZONE, 0, d.Z);
+    const int z = ahead_int(ua[UA_ZONE * SB_AHEAD], d.Z);
     const int size = k.zsize[z];
     int* mem = k.members + (size_t)z * d.N;
     if (kind == SB_OP_GROW_ZONE && size >= max_size) return false;        // :818-820
@@ -487,34 +510,36 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
         build_nbr_bits(d, k.zone_id, mem, size, -1, nbr, sp.nwords);
         PROF_T(tz1);
         PROF_ADD(8, tz0, tz1);
-        const int n_nbr = bits_count(nbr, sp.nwords, sh.redi);
+        const bool connected = ua[UA_CONNECTED * SB_AHEAD] < rho;                 // :731,823
+        // warp 0 counts the neighbourhood and, for a connected step, picks the candidate in the same scan; the
+        // other warps meanwhile build the bitmap of free sites if the step is not connected
+        bits_select(nbr, sp.nwords, 0, connected ? &sh.pick : &sh.redi[1], &sh.redi[0], ua[UA_SITE_NEW * SB_AHEAD]);
+        if (!connected) build_free_bits(d, k.zone_id, freeb, sp.nwords);
+        __syncthreads();
+        const int n_nbr = sh.redi[0];
         PROF_T(tz2);
         PROF_ADD(9, tz1, tz2);
-        const bool connected = rng_uniform(key, step, RP_CONNECTED, 0) < rho;     // :731,823
         const int n_cand = connected ? n_nbr : n_free;
         if (n_cand == 0) return false;                                            // :740-741, 832-833
-        const int pick = rng_int(key, step, RP_SITE_NEW, 0, n_cand);
-        if (connected) {
-            bits_select(nbr, sp.nwords, pick, &sh.pick);
-        } else {
-            build_free_bits(d, k.zone_id, freeb, sp.nwords);
+        if (!connected) {
+            bits_select(freeb, sp.nwords, ahead_int(ua[UA_SITE_NEW * SB_AHEAD], n_cand), &sh.pick);
             __syncthreads();
-            bits_select(freeb, sp.nwords, pick, &sh.pick);
         }
-        __syncthreads();
         site_new = sh.pick;
         q = grow_q(bit_test(nbr, site_new), n_free, n_nbr, rho);
         if (kind == SB_OP_GROW_ZONE) {
             q_back = 1.0 / (double)(size + 1);                                    // :848
         } else {
-            site_removed = mem[rng_int(key, step, RP_SITE_REMOVED, 0, size)];     // :748-750
+            site_removed = mem[ahead_int(ua[UA_SITE_REMOVED * SB_AHEAD], size)];  // :748-750
             q_back = grow_q(false, n_free, n_nbr, rho);    // old zone's neighbourhood never holds a member (:753,768)
         }
     } else {
-        site_removed = mem[rng_int(key, step, RP_SITE_REMOVED, 0, size)];         // :899-901
+        site_removed = mem[ahead_int(ua[UA_SITE_REMOVED * SB_AHEAD], size)];      // :899-901
         q = 1.0 / (double)size;                                                   // :904
         build_nbr_bits(d, k.zone_id, mem, size, site_removed, nbr, sp.nwords);    // :906-908
-        const int n_nbr_back = bits_count(nbr, sp.nwords, sh.redi);
+        bits_select(nbr, sp.nwords, 0, &sh.redi[1], &sh.redi[0], 0.0);            // warp 0: the count only
+        __syncthreads();
+        const int n_nbr_back = sh.redi[0];
         q_back = grow_q(bit_test(nbr, site_removed), n_free + 1, n_nbr_back, rho);   // :911-917
         if (d.warmup) q_back = 1.0 / (double)(size + 1);                          // :1552 (quirk Q3)
     }
@@ -523,9 +548,7 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
     PROF_ADD(10, tz0, tz3);
 
     // likelihood ratio of the moved site(s)
-    double dll = 0.0;
-    if (site_new >= 0) dll += site_zone_delta(d, k, site_new, -1, z, sh, tm);
-    if (site_removed >= 0) dll += site_zone_delta(d, k, site_removed, z, -1, sh, tm);
+    const double dll = zone_move_delta(d, k, site_new, site_removed, z, sh, tm);
     PROF_T(tz4);
     PROF_ADD(11, tz3, tz4);
 
@@ -551,7 +574,7 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
         accept = true;      // warm-up forces as_gibbs=True in gibbs_sample_sources => log_q = -inf => accept (:1293-1296)
     } else {
         const double mh = dll - flog(q / q_back, k.flt) + dprior;                 // mcmc_generative.py:345-349
-        accept = flog(rng_uniform(key, step, RP_ACCEPT, 0), k.flt) < mh;          // :318
+        accept = flog(ua[UA_ACCEPT * SB_AHEAD], k.flt) < mh;                      // :318
     }
     PROF_T(tz5);
     PROF_ADD(13, tz4, tz5);
@@ -559,6 +582,7 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
 
     // Proposal and decision above are computed redundantly (and identically) by every CTA of the team from the old
     // state.  Barrier 1: nobody reads the old zone state any more; rank 0 writes; barrier 2: everybody sees the new one.
+    wrote_nothing = false;
     team_sync(tm);
     if (threadIdx.x == 0 && tm.rank == 0) {
         if (site_removed >= 0) {
@@ -925,14 +949,17 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
                 int oi = 0;
                 while (oi < sp.n_ops - 1 && uo >= sp.op_cdf[oi]) ++oi;
                 sh.op_ahead[l] = sp.op_ids[oi];
-            } else if (w < 4) {
-                sh.u_ahead[w - 1][l] = rng_uniform(key, step + l, w == 1 ? RP_ZONE : (w == 2 ? RP_FAMILY : RP_FIXED), 0);
+            } else {
+#pragma unroll
+                for (int q = 0; q < SB_N_AHEAD; ++q)
+                    if (q % (STEP_WARPS - 1) == w - 1) sh.u_ahead[q][l] = rng_uniform(key, step + l, ahead_purpose(q), 0);
             }
             __syncthreads();
         }
         const int op = sh.op_ahead[ia];
         bool accepted = true;
         bool synced = false;    // the operator ended in a team barrier that followed all of its global writes
+        bool read_only = false; // the operator wrote nothing (a rejected zone move)
         PROF_T(ts1);
         // A Gibbs operator leaves its writes (own feature range only) unpublished; every other operator reads the
         // chain's tables across feature ranges, so it starts behind a full team barrier if anything is pending.
@@ -948,7 +975,7 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
         switch (op) {
             case SB_OP_SHRINK_ZONE: case SB_OP_GROW_ZONE: case SB_OP_SWAP_ZONE:
                 accepted = op_zone_move(d, sp, k, op, chain, key, step, ll, prior, geo, nbr, freeb, prim_key,
-                                        prim_tree, sh, tm, synced);
+                                        prim_tree, sh, tm, &sh.u_ahead[0][ia], synced, read_only);
                 if (accepted && d.sample_source) ll_stale = false;  // ll was recomputed from scratch by the source sweep
                 break;
             case SB_OP_GIBBS_SOURCES:
@@ -957,7 +984,7 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
                 synced = true;
                 break;
             case SB_OP_GIBBS_WEIGHTS:
-                op_gibbs_weights(d, k, key, step, sh.u_ahead[2][ia] < 0.5, tm);
+                op_gibbs_weights(d, k, key, step, sh.u_ahead[UA_FIXED][ia] < 0.5, tm);
                 synced = true;
                 break;
             case SB_OP_GIBBS_P_GLOBAL:
@@ -966,14 +993,14 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
                 synced = true;
                 break;
             case SB_OP_GIBBS_P_ZONES: {
-                const size_t o = (size_t)ahead_int(sh.u_ahead[0][ia], d.Z) * d.F * d.S;
+                const size_t o = (size_t)ahead_int(sh.u_ahead[UA_ZONE][ia], d.Z) * d.F * d.S;
                 gibbs_table_row(d, sp, k, key, step, k.pz + o, k.cz + o, nullptr, false, nullptr, nullptr, nullptr,
                                 prior_acc, tm);
                 synced = true;
                 break;
             }
             case SB_OP_GIBBS_P_FAMILIES: {
-                const int fam = ahead_int(sh.u_ahead[1][ia], d.Fam);
+                const int fam = ahead_int(sh.u_ahead[UA_FAMILY][ia], d.Fam);
                 const size_t o = (size_t)fam * d.F * d.S;
                 gibbs_table_row(d, sp, k, key, step, k.pf + o, k.cf + o, d.gibbs_f + o, true,
                                 d.pf_type == 1 ? d.alpha_f + o : nullptr, d.lnorm_f + (size_t)fam * d.F,
@@ -993,7 +1020,13 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
         // kind (which starts behind the `dirty` team barrier above) or the next refill of the look-ahead table.
         // After any other operator: the next step's writes must not overtake this step's reads in a slower thread
         // or CTA of the team.
-        if (!gibbs_table_op) { if (synced) __syncthreads(); else team_sync(tm); }
+        // A step that wrote nothing needs the team barrier only for execution order (no release / acquire, so L1
+        // stays valid).
+        if (!gibbs_table_op) {
+            if (synced) __syncthreads();
+            else if (read_only) team_sync_exec(tm);
+            else team_sync(tm);
+        }
         PROF_T(ts3);
         PROF_ADD(4, ts0, ts1); PROF_ADD(5, ts1, ts2); PROF_ADD(6, ts2, ts3);
     }
