@@ -726,7 +726,9 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
             double g = 0.0;
             if (sel) g = rng_gamma(key, step, RP_GAMMA, i, (pc ? pc[i] : 1.0) + (double)cnt[i]);
             double tot = g;
-            for (int o = Sp >> 1; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)                                // levels above the row width are skipped (uniform)
+                if (o < Sp) tot += __shfl_xor_sync(0xffffffffu, tot, o);
             if (sel) p[i] = g / tot;
             if (alpha) {                                                    // prior change of the rows just written
                 __syncwarp();

@@ -19,6 +19,9 @@ for c in range(nc):
     eng.set_state(c, s['zones'], s['weights'], s['p_global'], s['p_zones'], s['p_families'], np.argmax(s['source'], -1))
 eng.eval()
 mixes = {'default': bench.default_ops()}
+mixes['gibbs_mix'] = {k: v for k, v in bench.default_ops().items() if k.startswith('gibbs')}
+mixes['gibbs_mix+swap'] = dict(mixes['gibbs_mix'], swap_zone=0.05)
+mixes['gibbs_mix+shrink'] = dict(mixes['gibbs_mix'], shrink_zone=0.05)
 for k in ('gibbs_sample_weights', 'gibbs_sample_p_zones', 'gibbs_sample_p_global', 'gibbs_sample_p_families',
           'grow_zone', 'shrink_zone', 'swap_zone', 'gibbs_sample_sources'):
     mixes[k] = {k: 1.0}
