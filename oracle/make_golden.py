@@ -36,14 +36,20 @@ CASES = {
     'D_small':       (300, 40, 8, 7, 4, 12, True, False, False, 'cost_based', 'uniform'),
     'E_small':       (500, 20, 4, 0, 4, 25, False, False, False, 'uniform', 'none'),
 }
+# the reference's BUNDLED data sets, read with the reference's own loaders (oracle/refdata.py):
+# name: (experiment, Z, zone_size, geo, size_prior) -- priors / scale_counts as in the experiment's config.json
+BUNDLED_CASES = {
+    'F_balkan_data':   ('balkan', 3, 4, 'uniform', 'uniform'),
+    'G_samerica_data': ('south_america', 5, 6, 'cost_based', 'quadratic'),
+}
 
 
-def prior_config(inheritance, counts_prior, geo, size):
-    cfg = {'geo': {'type': geo, 'scale': 100.}, 'area_size': {'type': size}, 'weights': {'type': 'uniform'},
-           'universal': {'type': 'counts', 'scale_counts': 10.} if counts_prior else {'type': 'uniform'},
+def prior_config(inheritance, counts_prior, geo, size, scale_u=10., scale_f=10., geo_scale=100.):
+    cfg = {'geo': {'type': geo, 'scale': geo_scale}, 'area_size': {'type': size}, 'weights': {'type': 'uniform'},
+           'universal': {'type': 'counts', 'scale_counts': scale_u} if counts_prior else {'type': 'uniform'},
            'contact': {'type': 'uniform'}}
     if inheritance:
-        cfg['inheritance'] = ({'type': 'counts', 'scale_counts': 10.} if counts_prior else {'type': 'uniform'})
+        cfg['inheritance'] = ({'type': 'counts', 'scale_counts': scale_f} if counts_prior else {'type': 'uniform'})
     return cfg
 
 
@@ -53,13 +59,25 @@ def rel_err(a, b):
 
 
 def run_case(name, spec, seed):
-    n, f, s, fam, z, zs, inh, ragged, cp, geo, size = spec
-    data = synthetic.make_data(n, f, s, n_families=fam, na_frac=0.03, seed=seed, ragged_states=ragged,
-                               counts_prior=cp)
+    scale_u = scale_f = 10.
+    geo_scale = 100.
+    if name in BUNDLED_CASES:
+        import refdata
+        exp, z, zs, geo, size = spec
+        data, info = refdata.load_bundled(exp)
+        n, f, s = data.features.shape
+        fam, inh, ragged, cp = data.families.shape[0], info['inheritance'], True, True
+        scale_u, scale_f = info['scale_universal'], info['scale_inheritance']
+        if geo == 'cost_based':        # scale of the order of a Delaunay edge, so that the MST term is O(1)
+            geo_scale = float(np.median(data.network['dist_mat'][data.network['adj_mat'].toarray() > 0]))
+    else:
+        n, f, s, fam, z, zs, inh, ragged, cp, geo, size = spec
+        data = synthetic.make_data(n, f, s, n_families=fam, na_frac=0.03, seed=seed, ragged_states=ragged,
+                                   counts_prior=cp)
     raw_univ = np.array(data.prior_universal['counts'], float) if cp else None
     raw_fam = np.array(data.prior_inheritance['counts'], float) if (cp and inh) else None
     st = synthetic.random_state(data, z, zs, inh, with_source=True, seed=seed + 100)
-    pcfg = prior_config(inh, cp, geo, size)
+    pcfg = prior_config(inh, cp, geo, size, scale_u, scale_f, geo_scale)
     model_cfg = {'N_AREAS': z, 'MIN_M': 3, 'MAX_M': 50, 'INHERITANCE': inh, 'SAMPLE_SOURCE': True, 'PRIOR': pcfg}
     model = ref.model.Model(data, model_cfg)   # NB scales data.prior_*['counts'] in place (quirk Q10)
     Sample = ref.zone_sampling.Sample
@@ -106,10 +124,10 @@ def run_case(name, spec, seed):
     ag = af = None
     gibbs_g = gibbs_f = None
     if cp:
-        gibbs_g, ag = orc.dirichlet_prior_tables(raw_univ, 10.)
+        gibbs_g, ag = orc.dirichlet_prior_tables(raw_univ, scale_u)
         assert np.array_equal(gibbs_g, model.prior.prior_p_global.counts)
         if inh:
-            gibbs_f, af = orc.dirichlet_prior_tables(raw_fam, 10.)
+            gibbs_f, af = orc.dirichlet_prior_tables(raw_fam, scale_f)
             assert np.array_equal(gibbs_f, model.prior.prior_p_families.counts)
     o_prior = orc.log_prior(st['zones'], st['p_global'], st['p_families'], data.states, inh, pcfg,
                             cost_mat=data.geo_prior['cost_matrix'], alpha_global=ag, alpha_families=af)
@@ -166,7 +184,9 @@ def run_case(name, spec, seed):
         cost=(data.geo_prior['cost_matrix'] if geo == 'cost_based' else np.zeros((0, 0))), inheritance=np.bool_(inh),
         zones=st['zones'], weights=st['weights'], p_global=st['p_global'], p_zones=st['p_zones'],
         source_idx=np.argmax(src, axis=-1).astype(np.uint8),
-        geo_type=np.str_(geo), size_type=np.str_(size), geo_scale=np.float64(100.), counts_prior=np.bool_(cp),
+        geo_type=np.str_(geo), size_type=np.str_(size), geo_scale=np.float64(geo_scale), counts_prior=np.bool_(cp),
+        scale_universal=np.float64(np.nan if scale_u is None else scale_u),
+        scale_inheritance=np.float64(np.nan if scale_f is None else scale_f),
         **{'ref_' + k: np.asarray(v) for k, v in out.items()})
     if inh:
         save['p_families'] = st['p_families']
@@ -181,6 +201,8 @@ def run_case(name, spec, seed):
 
 if __name__ == '__main__':
     os.chdir('/tmp')
-    for i, (name, spec) in enumerate(CASES.items()):
-        run_case(name, spec, seed=11 + i)
+    only = sys.argv[1:]
+    for i, (name, spec) in enumerate(list(CASES.items()) + list(BUNDLED_CASES.items())):
+        if not only or name in only:
+            run_case(name, spec, seed=11 + i)
     print('golden vectors written to tests/golden/')

@@ -45,15 +45,23 @@ CASES = {
                            n_steps=60000, n_samples=3000),
     'run_C_alter': dict(N=60, F=10, S=4, Fam=3, Z=1, inh=True, src=False, cp=False, geo='cost_based',
                         size='quadratic', n_steps=60000, n_samples=3000),
+    # the reference's BUNDLED data sets (BASELINE.json configs[1], configs[2]), read with the reference's own loaders
+    # (oracle/refdata.py); count priors and scale_counts as in the experiment's config.json
+    'run_D_balkan': dict(bundled='balkan', Z=2, inh=True, src=True, cp=True, geo='uniform', size='none',
+                         n_steps=60000, n_samples=3000),
+    'run_E_samerica': dict(bundled='south_america', Z=3, inh=True, src=True, cp=True, geo='uniform', size='uniform',
+                           n_steps=60000, n_samples=3000),
 }
+SCALES = {}         # case -> (scale_counts universal, scale_counts inheritance); default (10, 10)
 
 
 def prior_config(c):
+    su, sf = c.get('scales', (10., 10.))
     cfg = {'geo': {'type': c['geo'], 'scale': 100.}, 'area_size': {'type': c['size']}, 'weights': {'type': 'uniform'},
-           'universal': {'type': 'counts', 'scale_counts': 10.} if c['cp'] else {'type': 'uniform'},
+           'universal': {'type': 'counts', 'scale_counts': su} if c['cp'] else {'type': 'uniform'},
            'contact': {'type': 'uniform'}}
     if c['inh']:
-        cfg['inheritance'] = {'type': 'counts', 'scale_counts': 10.} if c['cp'] else {'type': 'uniform'}
+        cfg['inheritance'] = {'type': 'counts', 'scale_counts': sf} if c['cp'] else {'type': 'uniform'}
     return cfg
 
 
@@ -67,9 +75,18 @@ def summarise(zones, weights, p_global, ll, prior, burn, planted):
 
 
 def build(case, seed=7):
-    c = CASES[case]
-    data = synthetic.make_data(c['N'], c['F'], c['S'], n_families=c['Fam'], na_frac=0.03, seed=seed,
-                               counts_prior=c['cp'], planted_zones=max(1, c['Z']), planted_size=10, planted_conc=0.3)
+    c = dict(CASES[case])
+    if 'bundled' in c:
+        import refdata
+        data, info = refdata.load_bundled(c['bundled'])
+        c.update(N=data.features.shape[0], F=data.features.shape[1], S=data.features.shape[2],
+                 Fam=data.families.shape[0], scales=(info['scale_universal'], info['scale_inheritance']))
+        # "planted" = the sites of the initial zones: planted_occ then tracks how much of the start survives
+        data.planted_zones = synthetic.random_state(data, c['Z'], 5, c['inh'], False, seed=seed + 1)['zones']
+    else:
+        data = synthetic.make_data(c['N'], c['F'], c['S'], n_families=c['Fam'], na_frac=0.03, seed=seed,
+                                   counts_prior=c['cp'], planted_zones=max(1, c['Z']), planted_size=10,
+                                   planted_conc=0.3)
     raw_u = np.array(data.prior_universal['counts'], float) if c['cp'] else None
     raw_f = np.array(data.prior_inheritance['counts'], float) if (c['cp'] and c['inh']) else None
     st = synthetic.random_state(data, c['Z'], 5, c['inh'], with_source=c['src'], seed=seed + 1)
@@ -151,10 +168,10 @@ def main(cases):
                                        'SAMPLE_SOURCE': c['src'], 'PRIOR': prior_config(c)})
         gibbs_g = alpha_g = gibbs_f = alpha_f = None
         if c['cp']:
-            gibbs_g, alpha_g = orc.dirichlet_prior_tables(raw_u, 10.)
+            gibbs_g, alpha_g = orc.dirichlet_prior_tables(raw_u, c.get('scales', (10., 10.))[0])
             assert np.array_equal(gibbs_g, model.prior.prior_p_global.counts)
             if c['inh']:
-                gibbs_f, alpha_f = orc.dirichlet_prior_tables(raw_f, 10.)
+                gibbs_f, alpha_f = orc.dirichlet_prior_tables(raw_f, c.get('scales', (10., 10.))[1])
         o_out, o_rate = run_oracle(c, data, st, 5, gibbs_g, alpha_g, gibbs_f, alpha_f)
         keys = ['occ_freq', 'zone_size', 'planted_occ', 'w_mean', 'w_comp', 'pg_mean', 'll_mean', 'prior_mean', 'acc']
         ref_stack = {k: np.stack([np.asarray(r[k]) for r in runs]) for k in keys}

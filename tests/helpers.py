@@ -144,6 +144,8 @@ def case_model_config(c, sample_source=True, min_m=3, max_m=30):
     pc = {k: dict(v) for k, v in c['prior_cfg'].items()}
     for k in ('universal', 'inheritance'):
         if pc[k]['type'] == 'counts':
-            pc[k].update(scale_counts=10., file='golden', files={})
+            # fixtures of the bundled data sets carry their config's scale_counts (NaN = null: counts used as they are)
+            sc = float(c['g'].get('scale_' + k, 10.))
+            pc[k].update(scale_counts=None if np.isnan(sc) else sc, file='golden', files={})
     return {'N_AREAS': c['Z'], 'MIN_M': min_m, 'MAX_M': max_m, 'INHERITANCE': c['inheritance'],
             'SAMPLE_SOURCE': sample_source, 'PRIOR': pc}
