@@ -361,10 +361,12 @@ def run_gpu_arm(args, rank, world, local_rank):
         cpu.update(cpu_likelihood())
 
     torch.cuda.set_device(local_rank)
+    # stdout carries exactly one JSON line: NCCL prints its version banner (NCCL_DEBUG >= VERSION) and other library
+    # chatter on fd 1, so everything written to fd 1 from here on goes to stderr and the line is written to the saved fd
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
-        # NCCL prints its version banner on stdout at NCCL_DEBUG=VERSION; stdout carries exactly one JSON line
-        if os.environ.get('NCCL_DEBUG', '').upper() in ('', 'VERSION'):
-            os.environ['NCCL_DEBUG'] = 'WARN'
         dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
     # torch.cuda.Event only sees torch's current stream: make a real (non-legacy) stream current and hand the
     # same stream to the C ABI, so that events, flushes, NCCL and our kernels are ordered on one stream
@@ -499,7 +501,8 @@ def run_gpu_arm(args, rank, world, local_rank):
                        for k, i in (('shrink_zone', 0), ('grow_zone', 1), ('swap_zone', 2))},
         'roofline': roof, 'likelihood_sweep': sweep, 'sampler_variants': variants, 'cpu_baseline': cpu,
     }
-    print(json.dumps(line), flush=True)
+    sys.stdout.flush()
+    os.write(json_fd, (json.dumps(line) + '\n').encode())
 
 
 def main():

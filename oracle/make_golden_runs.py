@@ -48,7 +48,7 @@ CASES = {
     # the reference's BUNDLED data sets (BASELINE.json configs[1], configs[2]), read with the reference's own loaders
     # (oracle/refdata.py); count priors and scale_counts as in the experiment's config.json
     'run_D_balkan': dict(bundled='balkan', Z=2, inh=True, src=True, cp=True, geo='uniform', size='none',
-                         n_steps=60000, n_samples=3000),
+                         n_steps=60000, n_samples=3000, max_m=10),      # 28 sites: MAX_M = 30 would let two zones take them all
     'run_E_samerica': dict(bundled='south_america', Z=3, inh=True, src=True, cp=True, geo='uniform', size='uniform',
                            n_steps=60000, n_samples=3000),
 }
@@ -97,8 +97,8 @@ def build(case, seed=7):
 
 
 def run_reference(c, data, st, seed):
-    model_cfg = {'N_AREAS': c['Z'], 'MIN_M': 3, 'MAX_M': 30, 'INHERITANCE': c['inh'], 'SAMPLE_SOURCE': c['src'],
-                 'PRIOR': prior_config(c)}
+    model_cfg = {'N_AREAS': c['Z'], 'MIN_M': 3, 'MAX_M': c.get('max_m', 30), 'INHERITANCE': c['inh'],
+                 'SAMPLE_SOURCE': c['src'], 'PRIOR': prior_config(c)}
     model = ref.model.Model(data, model_cfg)
     ops = so.default_operators(c['inh'], c['src'], STEPS)
     init = ref.zone_sampling.Sample(zones=st['zones'].copy(), weights=st['weights'].copy(),
@@ -124,7 +124,7 @@ def run_reference(c, data, st, seed):
 def run_oracle(c, data, st, seed, gibbs_g, alpha_g, gibbs_f, alpha_f, n_steps=None):
     ops = so.default_operators(c['inh'], c['src'], STEPS)
     smp = so.OracleSampler(data.features, data.states, data.families, data.network['adj_mat'], c['inh'], c['src'],
-                           prior_config(c), ops, PRECISION, 3, 30, 0.85, st, seed=seed,
+                           prior_config(c), ops, PRECISION, 3, c.get('max_m', 30), 0.85, st, seed=seed,
                            cost_mat=data.geo_prior['cost_matrix'], gibbs_counts_global=gibbs_g, alpha_global=alpha_g,
                            gibbs_counts_fam=gibbs_f, alpha_fam=alpha_f)
     if c['src']:
@@ -164,7 +164,7 @@ def main(cases):
         with mp.get_context('fork').Pool(N_RUNS) as pool:
             res = pool.starmap(_ref_job, [(case, 100 + r) for r in range(N_RUNS)])
         runs, rate, names = [r[0] for r in res], [r[2] for r in res], res[0][1]
-        model = ref.model.Model(data, {'N_AREAS': c['Z'], 'MIN_M': 3, 'MAX_M': 30, 'INHERITANCE': c['inh'],
+        model = ref.model.Model(data, {'N_AREAS': c['Z'], 'MIN_M': 3, 'MAX_M': c.get('max_m', 30), 'INHERITANCE': c['inh'],
                                        'SAMPLE_SOURCE': c['src'], 'PRIOR': prior_config(c)})
         gibbs_g = alpha_g = gibbs_f = alpha_f = None
         if c['cp']:
@@ -190,6 +190,7 @@ def main(cases):
             geo_type=np.str_(c['geo']), size_type=np.str_(c['size']), geo_scale=np.float64(100.),
             zones=st['zones'], weights=st['weights'], p_global=st['p_global'], p_zones=st['p_zones'],
             n_steps=np.int64(c['n_steps']), n_samples=np.int64(c['n_samples']), op_names=np.array(names),
+            max_m=np.int64(c.get('max_m', 30)),
             op_weights=np.array([so.default_operators(c['inh'], c['src'], STEPS)[k] for k in names]),
             planted=data.planted_zones.any(0),
             ref_steps_per_s=np.array(rate), port_steps_per_s=np.float64(o_rate),

@@ -16,7 +16,8 @@ def test_port_matches_reference_summaries(name):
           'p_families': c['p_families'],
           'source': np.eye(c['C'], dtype=bool)[g['source_idx']] if c['sample_source'] else None}
     smp = so.OracleSampler(c['features'], g['states'], c['families'], c['adj'], c['inheritance'], c['sample_source'],
-                           c['prior_cfg'], c['operators'], PRECISION, 3, 30, 0.85, st, seed=11, cost_mat=c['cost'],
+                           c['prior_cfg'], c['operators'], PRECISION, 3, int(g.get('max_m', 30)), 0.85, st, seed=11,
+                           cost_mat=c['cost'],
                            gibbs_counts_global=g.get('gibbs_counts_global'), alpha_global=g.get('alpha_global'),
                            gibbs_counts_fam=g.get('gibbs_counts_fam'), alpha_fam=g.get('alpha_fam'))
     n_steps, every = int(g['n_steps']) * 2 // 3, int(g['n_steps']) // int(g['n_samples'])

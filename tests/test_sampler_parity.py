@@ -31,7 +31,7 @@ def test_posterior_summaries_match_reference(name, built_lib):
         eng.set_state(ch, g['zones'], g['weights'], g['p_global'], g['p_zones'], c['p_families'],
                       g['source_idx'] if c['sample_source'] else None)
     eng.eval()
-    eng.set_operators(c['operators'], PRECISION, min_size=3, max_size=30, p_grow_connected=0.85, seed=2024)
+    eng.set_operators(c['operators'], PRECISION, min_size=3, max_size=int(g.get('max_m', 30)), p_grow_connected=0.85, seed=2024)
     n_steps, n_samples = int(g['n_steps']), int(g['n_samples'])
     every = n_steps // n_samples
     zs = [[] for _ in range(N_CHAINS)]
