@@ -837,7 +837,20 @@ static size_t step_smem_bytes(const DevData& d, StepParams& sp) {
     const size_t room = 160 * 1024 > base ? 160 * 1024 - base : 0;
     sp.work_off = (int)base;
     sp.work_counts = d.sample_source && counts <= room;
-    return base + (sp.work_counts ? counts : 0);
+    // SBAYES_B200_SWEEP caps the variant of the source sweep (tests): 0 global atomics, 1 shared counters, 2 staged
+    int cap = 2;
+    if (const char* env = getenv("SBAYES_B200_SWEEP")) cap = atoi(env);
+    if (cap < 1) sp.work_counts = 0;
+    if (!sp.work_counts) return base;
+    // the sweep's parameter tables (w~ [16][12], p_* [1+Z+Fam][16][S+1], f64) behind the counters, if they fit too
+    const size_t par_off = (base + counts + 7) & ~(size_t)7;
+    const size_t params = ((size_t)192 + (size_t)16 * (d.S + 1) * (1 + d.Z + d.Fam)) * sizeof(double);
+    sp.par_off = (int)par_off;
+    if (cap >= 2 && par_off + params <= base + room) {
+        sp.work_counts = 2;
+        return par_off + params;
+    }
+    return base + counts;
 }
 
 static int ensure_step_scratch(sb_ctx* ctx) {

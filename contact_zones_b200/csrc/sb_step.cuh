@@ -49,7 +49,9 @@ struct StepParams {
     int s_shift;              // log2 of the smallest power of two >= S (S <= SB_MAX_S = 32)
     int team;                 // CTAs per chain (thread-block cluster size): 1, 2, 4 or 8
     int work_off;             // byte offset of the shared work area in the dynamic smem (16 B aligned)
-    int work_counts;          // != 0: resample_all_sources keeps per-feature-block count tables in the work area
+    int work_counts;          // != 0: resample_all_sources keeps per-feature-block count tables in the work area;
+                              // 2: the block's parameter tables are staged behind them as well (par_off)
+    int par_off;              // byte offset of the staged parameter tables (8 B aligned)
     int* tmp_members;         // [chains][N]     candidate member list for the geo prior
     size_t s_tmp;
 };
@@ -240,6 +242,7 @@ struct Chain {
     double* ppg; double* ppf;
     int* tmp;
     int* cnt_tab;       // shared-memory count tables of resample_all_sources_blocked, or null
+    double* par_tab;    // shared-memory parameter tables of resample_all_sources_staged, or null
     const double2* flt; // shared-memory table of flog()
 };
 __device__ __forceinline__ Chain chain_view(const ChainArrays& st, const StepParams& sp, int c) {
@@ -254,6 +257,7 @@ __device__ __forceinline__ Chain chain_view(const ChainArrays& st, const StepPar
     k.ppg = st.prior_pg + c * st.s_prior_pg; k.ppf = st.prior_pf + c * st.s_prior_pf;
     k.tmp = sp.tmp_members + c * sp.s_tmp;
     k.cnt_tab = nullptr;
+    k.par_tab = nullptr;
     k.flt = nullptr;
     return k;
 }
@@ -448,11 +452,131 @@ __device__ double resample_all_sources_blocked(const DevData& d, const Chain& k,
     return team_sum(lp_value(acc), sh, tm);
 }
 
+// The same sweep with the PARAMETER tables of the 16-feature block staged in shared memory as well: w~ [16][12],
+// p_global [16][S+1], p_zones [Z][16][S+1], p_families [Fam][16][S+1], the extra column holding 1 for NA cells
+// (model.py:247).  The cell body is then branch-free on-chip arithmetic -- three weight * probability products from
+// shared memory, one categorical draw, two shared-memory counter increments -- with no dependent global load in the
+// inner loop (the global gathers were the top stall of the sweep, profiles/r01_k8_op_sources_lines.txt).  The
+// complete-data likelihood is NOT accumulated here: it is a function of the count tables (ll_from_counts) and nobody
+// needs its absolute value inside a launch, so the caller just marks it stale.  Same counters, same Philox blocks and
+// the same arithmetic per cell as resample_all_sources_blocked: the two produce identical source states.
+__device__ void resample_all_sources_staged(const DevData& d, const Chain& k, RngKey key, uint64_t step, int* tab,
+                                            double* ptab, Team& tm) {
+    const int S = d.S, S1 = S + 1, F = d.F, C = d.C, N = d.N;
+    const size_t FS = (size_t)F * S;
+    const int bS = 16 * S, bP = 16 * S1;
+    int* tcg = tab;                     // [16][S]
+    int* tcs = tcg + bS;                // [16][12]
+    int* tcz = tcs + 192;               // [Z][16][S]
+    int* tcf = tcz + d.Z * bS;          // [Fam][16][S]
+    const int T = bS * (1 + d.Z + d.Fam) + 192;
+    double* W = ptab;                   // [16][12]
+    double* PG = W + 192;               // [16][S1]
+    double* PZ = PG + bP;               // [Z][16][S1]
+    double* PF = PZ + d.Z * bP;         // [Fam][16][S1]
+    const int nP = bP * (1 + d.Z + d.Fam);
+    const int nb = d.ldx >> 4;
+    int fb_lo, fb_hi;
+    team_share(tm, nb, fb_lo, fb_hi);                   // each CTA of the team sweeps its own feature blocks
+    for (int i = threadIdx.x; i < T; i += blockDim.x) tab[i] = 0;
+    for (int fb = fb_lo; fb < fb_hi; ++fb) {
+        const int f0 = fb << 4;
+        const int nf = min(16, F - f0);
+        // stage the block's parameters (the previous block's cells are done: barrier at the end of the loop body)
+        for (int i = threadIdx.x; i < 192; i += blockDim.x) W[i] = i < nf * 12 ? k.wn[(size_t)f0 * 12 + i] : 0.0;
+        for (int i = threadIdx.x; i < nP; i += blockDim.x) {
+            const int t = i / bP, r = i - t * bP, j = r / S1, sx = r - j * S1;
+            double v = 1.0;
+            if (j < nf && sx < S) {
+                const double* src = t == 0 ? k.pg : (t <= d.Z ? k.pz + (size_t)(t - 1) * FS : k.pf + (size_t)(t - 1 - d.Z) * FS);
+                v = src[(size_t)(f0 + j) * S + sx];
+            }
+            PG[i] = v;
+        }
+        __syncthreads();
+        for (int n = threadIdx.x; n < N; n += blockDim.x) {
+            const uint4 xv = *reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + f0);
+            const int zid = k.zone_id[n];
+            const int fam = d.inheritance ? d.fam_id[n] : -1;
+            const int cfg = (zid >= 0 ? 1 : 0) + (fam >= 0 ? 2 : 0);
+            const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+            uint32_t sw[4] = {0u, 0u, 0u, 0u};
+            const double* wr = W + cfg * 3;
+            const double* pzr = PZ + (zid >= 0 ? zid : 0) * bP;
+            const double* pfr = PF + (fam >= 0 ? fam : 0) * bP;
+            int* czr = tcz + (zid >= 0 ? zid : 0) * bS;
+            int* cfr = tcf + (fam >= 0 ? fam : 0) * bS;
+            int* tcc = tcs + cfg * 3;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if (q * 4 >= nf) break;                                     // CTA-uniform
+                uint32_t o[4];
+                philox4x32((uint32_t)step, (uint32_t)(step >> 32), ((uint32_t)RP_SOURCE << 24) | (uint32_t)q,
+                           (uint32_t)(n * nb + fb), key.k0, key.k1, o);
+#pragma unroll
+                for (int h = 0; h < 4; ++h) {
+                    const int j = q * 4 + h;
+                    if (j >= nf) break;                                     // CTA-uniform (padding columns)
+                    const int xs = (xw[q] >> (h * 8)) & 0xff;
+                    const int xi = min(xs, S);                              // NA -> the column of ones
+                    const double* w = wr + j * 12;
+                    // a weight is 0 where its component is absent (wnorm_row), so no branch on zid / fam is needed
+                    const double t0 = w[0] * PG[j * S1 + xi];
+                    const double t1 = w[1] * pzr[j * S1 + xi];
+                    const double t2 = C == 3 ? w[2] * pfr[j * S1 + xi] : 0.0;
+                    const double t01 = t0 + t1, tot = t01 + t2;
+                    // (o + 0.5) 2^-32 tot; the integer -> double conversion as one exact fp64 subtraction
+                    const double uo = __hiloint2double(0x43300000, (int)o[h]) - 4503599627370495.5;
+                    const double ut = (uo * (1.0 / 4294967296.0)) * tot;
+                    // sample_categorical (preprocessing.py:338-341): first component whose cumulative mass exceeds u
+                    int sc = 0;
+                    if (ut >= t0) sc = (ut < t01) ? 1 : ((C == 3 && ut < tot) ? 2 : 0);
+                    sw[q] |= (uint32_t)sc << (h * 8);
+                    atomicAdd(tcc + j * 12 + sc, 1);
+                    if (xs != SB_NA) {
+                        int* t = sc == 0 ? tcg : (sc == 1 ? czr : cfr);
+                        atomicAdd(t + j * S + xs, 1);
+                    }
+                }
+            }
+            *reinterpret_cast<uint4*>(k.src + (size_t)n * d.ldx + f0) = make_uint4(sw[0], sw[1], sw[2], sw[3]);
+        }
+        __syncthreads();
+        // flush + clear: the block's counters are contiguous runs of the global tables
+        for (int i = threadIdx.x; i < T; i += blockDim.x) {
+            const int v = tab[i];
+            tab[i] = 0;
+            if (i < bS) {
+                if (i < nf * S) k.cg[(size_t)f0 * S + i] = v;
+            } else if (i < bS + 192) {
+                const int r = i - bS;
+                if (r < nf * 12) k.cs[(size_t)f0 * 12 + r] = v;
+            } else {
+                const int r = i - bS - 192;
+                const int t = r / bS, e = r - t * bS;
+                if (e < nf * S) {
+                    if (t < d.Z) k.cz[(size_t)t * FS + (size_t)f0 * S + e] = v;
+                    else k.cf[(size_t)(t - d.Z) * FS + (size_t)f0 * S + e] = v;
+                }
+            }
+        }
+        __syncthreads();
+    }
+    team_sync(tm);      // the feature blocks of the sweep do not coincide with the feature ranges of the other operators
+}
+
 // (the global-atomics variant is only used by one-CTA teams: sb_set_operators picks team = 1 when the tables do not fit)
-__device__ __forceinline__ double resample_sources(const DevData& d, const Chain& k, RngKey key, uint64_t step,
-                                                   StepShared& sh, Team& tm) {
-    return k.cnt_tab ? resample_all_sources_blocked(d, k, key, step, sh, k.cnt_tab, tm)
-                     : resample_all_sources(d, k, key, step, sh.red);
+// ll / ll_stale: the running log-likelihood and its "must be re-formed from the count tables" flag (ll_from_counts)
+__device__ __forceinline__ void resample_sources(const DevData& d, const Chain& k, RngKey key, uint64_t step,
+                                                 StepShared& sh, Team& tm, double& ll, bool& ll_stale) {
+    if (k.par_tab) {
+        resample_all_sources_staged(d, k, key, step, k.cnt_tab, k.par_tab, tm);
+        ll_stale = true;
+        return;
+    }
+    ll = k.cnt_tab ? resample_all_sources_blocked(d, k, key, step, sh, k.cnt_tab, tm)
+                   : resample_all_sources(d, k, key, step, sh.red);
+    ll_stale = false;
 }
 
 // prior terms that depend on the zones: size prior (model.py:932-972) and geo prior (:1096-1139, last zone only)
@@ -486,7 +610,8 @@ __device__ __forceinline__ double grow_q(bool in_nbr, int n_free, int n_nbr, dou
 __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain& k, int kind, int chain,
                              RngKey key, uint64_t step, double& ll, double& prior, double& geo,
                              unsigned* nbr, unsigned* freeb, double* prim_key, unsigned char* prim_tree,
-                             StepShared& sh, Team& tm, const double* ua, bool& synced, bool& wrote_nothing) {
+                             StepShared& sh, Team& tm, const double* ua, bool& synced, bool& wrote_nothing,
+                             bool& ll_stale) {
     wrote_nothing = true;       // until the proposal is accepted: a rejected move only read the chain state
     // ua: this step's column of the look-ahead table (ua[q * SB_AHEAD] = uniform q of the step)
     PROF_T(tzp);
@@ -601,7 +726,7 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
     synced = true;
     prior += dprior;
     geo = geo_new;
-    if (d.sample_source) ll = resample_sources(d, k, key, step, sh, tm);          // :859-862 (on accept only)
+    if (d.sample_source) resample_sources(d, k, key, step, sh, tm, ll, ll_stale); // :859-862 (on accept only)
     else ll += dll;
     return true;
 }
@@ -919,6 +1044,7 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
 
     Chain kv = chain_view(st, sp, chain);
     if (sp.work_counts) kv.cnt_tab = reinterpret_cast<int*>(step_smem + sp.work_off);
+    if (sp.work_counts == 2) kv.par_tab = reinterpret_cast<double*>(step_smem + sp.par_off);
     __shared__ double2 flog_tab[SB_FLOG_N];
     flog_init(flog_tab);
     __syncthreads();
@@ -977,12 +1103,10 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
         switch (op) {
             case SB_OP_SHRINK_ZONE: case SB_OP_GROW_ZONE: case SB_OP_SWAP_ZONE:
                 accepted = op_zone_move(d, sp, k, op, chain, key, step, ll, prior, geo, nbr, freeb, prim_key,
-                                        prim_tree, sh, tm, &sh.u_ahead[0][ia], synced, read_only);
-                if (accepted && d.sample_source) ll_stale = false;  // ll was recomputed from scratch by the source sweep
+                                        prim_tree, sh, tm, &sh.u_ahead[0][ia], synced, read_only, ll_stale);
                 break;
             case SB_OP_GIBBS_SOURCES:
-                ll = resample_sources(d, k, key, step, sh, tm);
-                ll_stale = false;
+                resample_sources(d, k, key, step, sh, tm, ll, ll_stale);
                 synced = true;
                 break;
             case SB_OP_GIBBS_WEIGHTS:

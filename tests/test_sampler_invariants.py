@@ -67,10 +67,13 @@ def test_each_operator_keeps_running_values_exact(name, sample_source, built_lib
     eng.close()
 
 
-def _run_chains(c, n_chains, chain_offset, steps, ops, sample_source=True, team=None):
+def _run_chains(c, n_chains, chain_offset, steps, ops, sample_source=True, team=None, sweep=None):
     old = os.environ.get('SBAYES_B200_TEAM')
+    old_sweep = os.environ.get('SBAYES_B200_SWEEP')
     if team is not None:
         os.environ['SBAYES_B200_TEAM'] = str(team)
+    if sweep is not None:
+        os.environ['SBAYES_B200_SWEEP'] = str(sweep)
     try:
         eng = make_engine(c, n_chains=n_chains, sample_source=sample_source, chain_offset=chain_offset)
         for ch in range(n_chains):
@@ -83,11 +86,12 @@ def _run_chains(c, n_chains, chain_offset, steps, ops, sample_source=True, team=
         eng.close()
         return out, ll, pr
     finally:
-        if team is not None:
-            if old is None:
-                os.environ.pop('SBAYES_B200_TEAM', None)
-            else:
-                os.environ['SBAYES_B200_TEAM'] = old
+        for key, was, given in (('SBAYES_B200_TEAM', old, team), ('SBAYES_B200_SWEEP', old_sweep, sweep)):
+            if given is not None:
+                if was is None:
+                    os.environ.pop(key, None)
+                else:
+                    os.environ[key] = was
 
 
 MIX = {'shrink_zone': 0.1, 'grow_zone': 0.1, 'swap_zone': 0.05, 'gibbs_sample_weights': 0.3, 'gibbs_sample_p_global': 0.1,
@@ -121,3 +125,31 @@ def test_team_sizes_walk_the_same_trajectory(sample_source, built_lib):
                 assert np.array_equal(a['source'], b['source']), team
             assert np.allclose(a['p_zones'], b['p_zones'], rtol=1e-12, atol=0), team
             assert np.allclose(a['weights'], b['weights'], rtol=1e-12, atol=0), team
+
+
+def test_source_sweep_variants_produce_the_same_states(built_lib):
+    """The two shared-memory forms of the source sweep (counters only / counters + staged parameter tables) use the
+    same Philox blocks and the same arithmetic per cell: identical zones, sources and count tables, parameters equal
+    to rounding, for teams of 1 and 2 (SBAYES_B200_SWEEP caps the variant).  The global-atomics fallback (variant 0)
+    draws its uniforms differently; it must keep the running values consistent with a from-scratch evaluation."""
+    c = load_case('D_small')
+    ops = dict(MIX, gibbs_sample_sources=0.1)
+    ref, ll_ref, pr_ref = _run_chains(c, 2, 0, 300, ops, True, team=1, sweep=1)
+    for team, sweep in ((2, 1), (1, 2), (2, 2)):
+        got, ll, pr = _run_chains(c, 2, 0, 300, ops, True, team=team, sweep=sweep)
+        assert np.allclose(ll, ll_ref, rtol=1e-10) and np.allclose(pr, pr_ref, rtol=1e-10, atol=1e-10), (team, sweep)
+        for a, b in zip(ref, got):
+            assert np.array_equal(a['zones'], b['zones']) and np.array_equal(a['source'], b['source']), (team, sweep)
+            assert np.allclose(a['p_zones'], b['p_zones'], rtol=1e-12, atol=0), (team, sweep)
+    os.environ['SBAYES_B200_SWEEP'] = '0'
+    try:
+        eng = make_engine(c, n_chains=2, sample_source=True)
+        for ch in range(2):
+            set_golden_state(eng, c, ch)
+        eng.eval()
+        eng.set_operators(ops, PRECISION, min_size=3, max_size=25, p_grow_connected=0.85, seed=77)
+        eng.run(300)
+        check_consistency(eng, c, 2, True, 3, 25)
+        eng.close()
+    finally:
+        os.environ.pop('SBAYES_B200_SWEEP', None)
