@@ -833,7 +833,7 @@ static size_t step_smem_base(const StepParams& sp) {
 // of the source sweep; if they do not fit, the sweep falls back to global atomics.
 static size_t step_smem_bytes(const DevData& d, StepParams& sp) {
     const size_t base = step_smem_base(sp);
-    const size_t counts = ((size_t)16 * d.S * (1 + d.Z + d.Fam) + 192) * sizeof(int);
+    const size_t counts = ((size_t)16 * (d.S + 1) * (1 + d.Z + d.Fam) + 192) * sizeof(int);   // S+1: staged variant
     const size_t room = 160 * 1024 > base ? 160 * 1024 - base : 0;
     sp.work_off = (int)base;
     sp.work_counts = d.sample_source && counts <= room;

@@ -454,7 +454,7 @@ __device__ double resample_all_sources_blocked(const DevData& d, const Chain& k,
 
 // The same sweep with the PARAMETER tables of the 16-feature block staged in shared memory as well: w~ [16][12],
 // p_global [16][S+1], p_zones [Z][16][S+1], p_families [Fam][16][S+1], the extra column holding 1 for NA cells
-// (model.py:247).  The cell body is then branch-free on-chip arithmetic -- three weight * probability products from
+// (model.py:247); the counters get the same [table][16][S+1] shape, so a cell indexes both with one offset.  The cell body is then branch-free on-chip arithmetic -- three weight * probability products from
 // shared memory, one categorical draw, two shared-memory counter increments -- with no dependent global load in the
 // inner loop (the global gathers were the top stall of the sweep, profiles/r01_k8_op_sources_lines.txt).  The
 // complete-data likelihood is NOT accumulated here: it is a function of the count tables (ll_from_counts) and nobody
@@ -464,17 +464,13 @@ __device__ void resample_all_sources_staged(const DevData& d, const Chain& k, Rn
                                             double* ptab, Team& tm) {
     const int S = d.S, S1 = S + 1, F = d.F, C = d.C, N = d.N;
     const size_t FS = (size_t)F * S;
-    const int bS = 16 * S, bP = 16 * S1;
-    int* tcg = tab;                     // [16][S]
-    int* tcs = tcg + bS;                // [16][12]
-    int* tcz = tcs + 192;               // [Z][16][S]
-    int* tcf = tcz + d.Z * bS;          // [Fam][16][S]
-    const int T = bS * (1 + d.Z + d.Fam) + 192;
-    double* W = ptab;                   // [16][12]
-    double* PG = W + 192;               // [16][S1]
-    double* PZ = PG + bP;               // [Z][16][S1]
-    double* PF = PZ + d.Z * bP;         // [Fam][16][S1]
-    const int nP = bP * (1 + d.Z + d.Fam);
+    const int bP = 16 * S1;             // entries of one (table, feature block): 16 features x (S states + NA)
+    const int n_rows = 16 * (1 + d.Z + d.Fam);
+    // counters  tab  = cnt[1 + Z + Fam][16][S1] (global, zones, families; the NA column is discarded) | src[16][12]
+    // parameters ptab = p  [1 + Z + Fam][16][S1] (NA column = 1)                                         | w~ [16][12]
+    int* tcs = tab + n_rows * S1;
+    const double* W = ptab + n_rows * S1;
+    const int T = n_rows * S1 + 192;
     const int nb = d.ldx >> 4;
     int fb_lo, fb_hi;
     team_share(tm, nb, fb_lo, fb_hi);                   // each CTA of the team sweeps its own feature blocks
@@ -482,16 +478,17 @@ __device__ void resample_all_sources_staged(const DevData& d, const Chain& k, Rn
     for (int fb = fb_lo; fb < fb_hi; ++fb) {
         const int f0 = fb << 4;
         const int nf = min(16, F - f0);
-        // stage the block's parameters (the previous block's cells are done: barrier at the end of the loop body)
-        for (int i = threadIdx.x; i < 192; i += blockDim.x) W[i] = i < nf * 12 ? k.wn[(size_t)f0 * 12 + i] : 0.0;
-        for (int i = threadIdx.x; i < nP; i += blockDim.x) {
-            const int t = i / bP, r = i - t * bP, j = r / S1, sx = r - j * S1;
-            double v = 1.0;
-            if (j < nf && sx < S) {
-                const double* src = t == 0 ? k.pg : (t <= d.Z ? k.pz + (size_t)(t - 1) * FS : k.pf + (size_t)(t - 1 - d.Z) * FS);
-                v = src[(size_t)(f0 + j) * S + sx];
-            }
-            PG[i] = v;
+        // stage the block's parameters, one table row (table, feature) per thread (the previous block's cells are
+        // done: barrier at the end of the loop body)
+        for (int i = threadIdx.x; i < 192; i += blockDim.x)
+            ptab[n_rows * S1 + i] = i < nf * 12 ? k.wn[(size_t)f0 * 12 + i] : 0.0;
+        for (int r = threadIdx.x; r < n_rows; r += blockDim.x) {
+            const int t = r >> 4, j = r & 15;
+            const double* src = (t == 0 ? k.pg : (t <= d.Z ? k.pz + (size_t)(t - 1) * FS : k.pf + (size_t)(t - 1 - d.Z) * FS))
+                                + (size_t)(f0 + j) * S;
+            double* dst = ptab + r * S1;
+            for (int sx = 0; sx < S; ++sx) dst[sx] = j < nf ? src[sx] : 1.0;
+            dst[S] = 1.0;
         }
         __syncthreads();
         for (int n = threadIdx.x; n < N; n += blockDim.x) {
@@ -501,11 +498,10 @@ __device__ void resample_all_sources_staged(const DevData& d, const Chain& k, Rn
             const int cfg = (zid >= 0 ? 1 : 0) + (fam >= 0 ? 2 : 0);
             const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
             uint32_t sw[4] = {0u, 0u, 0u, 0u};
+            // table bases of this site (entries): component 0 / 1 / 2 -> global / its zone / its family
+            const int bz = (1 + (zid >= 0 ? zid : 0)) * bP;
+            const int bf = (1 + d.Z + (fam >= 0 ? fam : 0)) * bP;
             const double* wr = W + cfg * 3;
-            const double* pzr = PZ + (zid >= 0 ? zid : 0) * bP;
-            const double* pfr = PF + (fam >= 0 ? fam : 0) * bP;
-            int* czr = tcz + (zid >= 0 ? zid : 0) * bS;
-            int* cfr = tcf + (fam >= 0 ? fam : 0) * bS;
             int* tcc = tcs + cfg * 3;
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
@@ -518,47 +514,43 @@ __device__ void resample_all_sources_staged(const DevData& d, const Chain& k, Rn
                     const int j = q * 4 + h;
                     if (j >= nf) break;                                     // CTA-uniform (padding columns)
                     const int xs = (xw[q] >> (h * 8)) & 0xff;
-                    const int xi = min(xs, S);                              // NA -> the column of ones
+                    const int e = j * S1 + min(xs, S);                      // NA -> the extra column
                     const double* w = wr + j * 12;
                     // a weight is 0 where its component is absent (wnorm_row), so no branch on zid / fam is needed
-                    const double t0 = w[0] * PG[j * S1 + xi];
-                    const double t1 = w[1] * pzr[j * S1 + xi];
-                    const double t2 = C == 3 ? w[2] * pfr[j * S1 + xi] : 0.0;
+                    const double t0 = w[0] * ptab[e];
+                    const double t1 = w[1] * ptab[bz + e];
+                    const double t2 = C == 3 ? w[2] * ptab[bf + e] : 0.0;
                     const double t01 = t0 + t1, tot = t01 + t2;
                     // (o + 0.5) 2^-32 tot; the integer -> double conversion as one exact fp64 subtraction
                     const double uo = __hiloint2double(0x43300000, (int)o[h]) - 4503599627370495.5;
                     const double ut = (uo * (1.0 / 4294967296.0)) * tot;
-                    // sample_categorical (preprocessing.py:338-341): first component whose cumulative mass exceeds u
-                    int sc = 0;
-                    if (ut >= t0) sc = (ut < t01) ? 1 : ((C == 3 && ut < tot) ? 2 : 0);
+                    // sample_categorical (preprocessing.py:338-341): first component whose cumulative mass exceeds u.
+                    // u <= 1 - 2^-33, so ut < tot after rounding and the count of passed boundaries is the component
+                    // (with C == 2, t2 = 0 and t01 = tot is never passed)
+                    const int sc = (ut >= t0 ? 1 : 0) + (ut >= t01 ? 1 : 0);
                     sw[q] |= (uint32_t)sc << (h * 8);
                     atomicAdd(tcc + j * 12 + sc, 1);
-                    if (xs != SB_NA) {
-                        int* t = sc == 0 ? tcg : (sc == 1 ? czr : cfr);
-                        atomicAdd(t + j * S + xs, 1);
-                    }
+                    atomicAdd(tab + (sc == 0 ? 0 : (sc == 1 ? bz : bf)) + e, 1);
                 }
             }
             *reinterpret_cast<uint4*>(k.src + (size_t)n * d.ldx + f0) = make_uint4(sw[0], sw[1], sw[2], sw[3]);
         }
         __syncthreads();
-        // flush + clear: the block's counters are contiguous runs of the global tables
-        for (int i = threadIdx.x; i < T; i += blockDim.x) {
-            const int v = tab[i];
-            tab[i] = 0;
-            if (i < bS) {
-                if (i < nf * S) k.cg[(size_t)f0 * S + i] = v;
-            } else if (i < bS + 192) {
-                const int r = i - bS;
-                if (r < nf * 12) k.cs[(size_t)f0 * 12 + r] = v;
-            } else {
-                const int r = i - bS - 192;
-                const int t = r / bS, e = r - t * bS;
-                if (e < nf * S) {
-                    if (t < d.Z) k.cz[(size_t)t * FS + (size_t)f0 * S + e] = v;
-                    else k.cf[(size_t)(t - d.Z) * FS + (size_t)f0 * S + e] = v;
-                }
+        // flush + clear, one table row per thread: the rows of the block are contiguous runs of the global tables
+        for (int r = threadIdx.x; r < n_rows; r += blockDim.x) {
+            const int t = r >> 4, j = r & 15;
+            int* dst = (t == 0 ? k.cg : (t <= d.Z ? k.cz + (size_t)(t - 1) * FS : k.cf + (size_t)(t - 1 - d.Z) * FS))
+                       + (size_t)(f0 + j) * S;
+            int* row = tab + r * S1;
+            for (int sx = 0; sx < S; ++sx) {
+                if (j < nf) dst[sx] = row[sx];
+                row[sx] = 0;
             }
+            row[S] = 0;
+        }
+        for (int i = threadIdx.x; i < 192; i += blockDim.x) {
+            if (i < nf * 12) k.cs[(size_t)f0 * 12 + i] = tcs[i];
+            tcs[i] = 0;
         }
         __syncthreads();
     }
