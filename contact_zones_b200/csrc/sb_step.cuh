@@ -603,7 +603,7 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
                              RngKey key, uint64_t step, double& ll, double& prior, double& geo,
                              unsigned* nbr, unsigned* freeb, double* prim_key, unsigned char* prim_tree,
                              StepShared& sh, Team& tm, const double* ua, bool& synced, bool& wrote_nothing,
-                             bool& ll_stale) {
+                             bool& need_sweep) {
     wrote_nothing = true;       // until the proposal is accepted: a rejected move only read the chain state
     // ua: this step's column of the look-ahead table (ua[q * SB_AHEAD] = uniform q of the step)
     PROF_T(tzp);
@@ -718,7 +718,7 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
     synced = true;
     prior += dprior;
     geo = geo_new;
-    if (d.sample_source) resample_sources(d, k, key, step, sh, tm, ll, ll_stale); // :859-862 (on accept only)
+    if (d.sample_source) need_sweep = true;     // gibbs_sample_sources on accept (:859-862): run by the caller
     else ll += dll;
     return true;
 }
@@ -1080,6 +1080,7 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
         bool accepted = true;
         bool synced = false;    // the operator ended in a team barrier that followed all of its global writes
         bool read_only = false; // the operator wrote nothing (a rejected zone move)
+        bool need_sweep = false;
         PROF_T(ts1);
         // A Gibbs operator leaves its writes (own feature range only) unpublished; every other operator reads the
         // chain's tables across feature ranges, so it starts behind a full team barrier if anything is pending.
@@ -1095,40 +1096,44 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
         switch (op) {
             case SB_OP_SHRINK_ZONE: case SB_OP_GROW_ZONE: case SB_OP_SWAP_ZONE:
                 accepted = op_zone_move(d, sp, k, op, chain, key, step, ll, prior, geo, nbr, freeb, prim_key,
-                                        prim_tree, sh, tm, &sh.u_ahead[0][ia], synced, read_only, ll_stale);
+                                        prim_tree, sh, tm, &sh.u_ahead[0][ia], synced, read_only, need_sweep);
                 break;
             case SB_OP_GIBBS_SOURCES:
-                resample_sources(d, k, key, step, sh, tm, ll, ll_stale);
-                synced = true;
+                need_sweep = true;
                 break;
             case SB_OP_GIBBS_WEIGHTS:
                 op_gibbs_weights(d, k, key, step, sh.u_ahead[UA_FIXED][ia] < 0.5, tm);
                 synced = true;
                 break;
-            case SB_OP_GIBBS_P_GLOBAL:
-                gibbs_table_row(d, sp, k, key, step, k.pg, k.cg, d.gibbs_g, true,
-                                d.pg_type == 1 ? d.alpha_g : nullptr, d.lnorm_g, k.ppg, prior_acc, tm);
-                synced = true;
-                break;
-            case SB_OP_GIBBS_P_ZONES: {
-                const size_t o = (size_t)ahead_int(sh.u_ahead[UA_ZONE][ia], d.Z) * d.F * d.S;
-                gibbs_table_row(d, sp, k, key, step, k.pz + o, k.cz + o, nullptr, false, nullptr, nullptr, nullptr,
+            case SB_OP_GIBBS_P_GLOBAL: case SB_OP_GIBBS_P_ZONES: case SB_OP_GIBBS_P_FAMILIES: {
+                // one call site for the three table operators (one copy of the Gamma sampler in the instruction cache)
+                double* p = k.pg; const int* cnt = k.cg; const double* pc = d.gibbs_g;
+                const double* alpha = d.pg_type == 1 ? d.alpha_g : nullptr; const double* lnorm = d.lnorm_g;
+                double* pcache = k.ppg;
+                if (op == SB_OP_GIBBS_P_ZONES) {
+                    const size_t o = (size_t)ahead_int(sh.u_ahead[UA_ZONE][ia], d.Z) * d.F * d.S;
+                    p = k.pz + o; cnt = k.cz + o; pc = nullptr; alpha = nullptr; lnorm = nullptr; pcache = nullptr;
+                } else if (op == SB_OP_GIBBS_P_FAMILIES) {
+                    const int fam = ahead_int(sh.u_ahead[UA_FAMILY][ia], d.Fam);
+                    const size_t o = (size_t)fam * d.F * d.S;
+                    p = k.pf + o; cnt = k.cf + o; pc = d.gibbs_f + o;
+                    alpha = d.pf_type == 1 ? d.alpha_f + o : nullptr; lnorm = d.lnorm_f + (size_t)fam * d.F;
+                    pcache = k.ppf + (size_t)fam * d.F;
+                }
+                gibbs_table_row(d, sp, k, key, step, p, cnt, pc, op != SB_OP_GIBBS_P_ZONES, alpha, lnorm, pcache,
                                 prior_acc, tm);
-                synced = true;
-                break;
-            }
-            case SB_OP_GIBBS_P_FAMILIES: {
-                const int fam = ahead_int(sh.u_ahead[UA_FAMILY][ia], d.Fam);
-                const size_t o = (size_t)fam * d.F * d.S;
-                gibbs_table_row(d, sp, k, key, step, k.pf + o, k.cf + o, d.gibbs_f + o, true,
-                                d.pf_type == 1 ? d.alpha_f + o : nullptr, d.lnorm_f + (size_t)fam * d.F,
-                                k.ppf + (size_t)fam * d.F, prior_acc, tm);
                 synced = true;
                 break;
             }
             default:
                 accepted = op_alter(d, sp, k, op, key, step, ll, prior, sh, tm, synced);
                 break;
+        }
+        // the source sweep has ONE call site (gibbs_sample_sources and every accepted zone move): it is the largest
+        // block of code of the kernel
+        if (need_sweep) {
+            resample_sources(d, k, key, step, sh, tm, ll, ll_stale);
+            synced = true;
         }
         PROF_T(ts2);
         if (threadIdx.x == 0 && tm.rank == 0)      // fire-and-forget reduction: nobody waits for the L2 round trip
