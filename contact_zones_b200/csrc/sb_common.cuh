@@ -82,6 +82,9 @@ struct ChainArrays {
 // the 1e-9 relative parity bound (tests/test_gpu_parity.py).
 // ---------------------------------------------------------------------------------------------
 #define SB_LP_PERIOD 8
+// libm's log() expands to ~100 instructions at every call site; the cold paths share one out-of-line copy (the step
+// kernel is sensitive to the size of its hot loop)
+__device__ __noinline__ double sb_log(double x) { return log(x); }
 struct LogProd {
     double m;      // mantissa product, in [2^-960, 2)
     double side;   // exact logs of tiny factors (may be -inf)
@@ -97,7 +100,7 @@ __device__ __forceinline__ void lp_renorm(LogProd& a) {
 }
 __device__ __forceinline__ void lp_mul(LogProd& a, double v) {
     if (__double2hiint(v) < 0x38700000) {   // v < 2^-120, zero, subnormal (or negative/NaN): exact path
-        a.side += log(v);
+        a.side += sb_log(v);
     } else {
         a.m *= v;
         if (++a.k == SB_LP_PERIOD) lp_renorm(a);
@@ -169,7 +172,7 @@ __device__ __forceinline__ void flog_init(double2* tab) {      // call by the wh
 }
 __device__ __forceinline__ double flog(double x, const double2* __restrict__ tab) {
     const int hi = __double2hiint(x);
-    if ((unsigned)(hi - 0x00100000) >= 0x7fe00000u) return log(x);
+    if ((unsigned)(hi - 0x00100000) >= 0x7fe00000u) return sb_log(x);     // non-positive / subnormal / inf / NaN inputs
     const int e = (hi >> 20) - 1023;
     const double m = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(x));
     const double2 t = tab[(hi >> 13) & (SB_FLOG_N - 1)];
@@ -185,4 +188,4 @@ __device__ __forceinline__ double flog(double x, const double2* __restrict__ tab
 }
 
 // xlogy semantics of scipy (dirichlet._logpdf): 0 * log(0) = 0
-__device__ __forceinline__ double xlogy_d(double a, double p) { return a == 0.0 ? 0.0 : a * log(p); }
+__device__ __forceinline__ double xlogy_d(double a, double p) { return a == 0.0 ? 0.0 : a * sb_log(p); }

@@ -127,7 +127,7 @@ __global__ void lh_reduce_kernel(const double* __restrict__ partial, int n_tiles
 // K2 + K3: priors.  One CTA per chain.
 // ---------------------------------------------------------------------------------------------
 // log C(n,k) as the reference computes it (util.py:1202-1217): -betaln(1+n-k, 1+k) - log(n+1)
-__device__ __forceinline__ double log_binom_d(double n, double k) {
+__device__ __noinline__ double log_binom_d(double n, double k) {
     const double a = 1.0 + n - k, b = 1.0 + k;
     return -(lgamma(a) + lgamma(b) - lgamma(a + b)) - log(n + 1.0);
 }

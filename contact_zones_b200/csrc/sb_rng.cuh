@@ -80,6 +80,11 @@ __device__ __forceinline__ int ahead_int(double u, int n) {
 // (tests/test_rng_parity.py: KS tests against the exact CDFs); the radius uniform has 32 bits, so |x| <= 6.8.  The
 // candidates are then treated as exact fp64 numbers: v, the accept test and the variate are fp64.  The log-form accept test is decided by a fast fp32 estimate
 // when its margin is clear and in fp64 otherwise.
+// the fp64 form of the log test: rare (the fp32 estimate decides unless its margin is unclear), so it is kept out of
+// line -- the step kernel is sensitive to the size of its hot loop (instruction cache)
+__device__ __noinline__ bool mt_accept_exact(double u, double x2, double d, double v) {
+    return log(u) < 0.5 * x2 + d * (1.0 - v + log(v));
+}
 __device__ __forceinline__ bool mt_accept(double x, double u, double c, double d, double& out) {
     // written without early exits so that two candidates can be interleaved by the compiler
     const double v1 = 1.0 + c * x;
@@ -95,7 +100,7 @@ __device__ __forceinline__ bool mt_accept(double x, double u, double c, double d
     const float margin = 4e-6f * (fabsf(lu) + hx + df * (fabsf(omv) + fabsf(lv))) + 2e-6f * df + 4e-6f;
     const bool clear = fabsf(lu - rhs) > margin;
     bool acc = squeeze || (clear && lu < rhs);
-    if (pos && !squeeze && !clear) acc = log(u) < 0.5 * x2 + d * (1.0 - v + log(v));
+    if (pos && !squeeze && !clear) acc = mt_accept_exact(u, x2, d, v);
     return pos && acc;
 }
 

@@ -195,12 +195,13 @@ __device__ __forceinline__ void team_share(const Team& t, int n, int& lo, int& h
 // thread: warp tree, then the per-warp partials of all CTAs in fixed (rank, warp) order.  ONE barrier -- for the team
 // scope a cluster barrier, so everything the CTAs wrote before the call is visible to all of them after it.  The
 // partials are double-buffered: a buffer is rewritten two reductions later, after the barrier in between.
-__device__ __forceinline__ void sum2_scope(double& a, double& b, StepShared& sh, Team& t, int scope) {
+// Out of line: the reductions sit on the Metropolis paths only (no Gibbs step reduces), and ~30 inlined copies of the
+// shuffle trees were a quarter of the kernel's code.
+__device__ __noinline__ double2 sum2_impl(double a, double b, double* wpart, unsigned turn, int scope) {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     a = warp_sum(a);
     b = warp_sum(b);
-    double* slot = &sh.wpart[t.turn & 1u][0][0];
-    ++t.turn;
+    double* slot = wpart + (turn & 1u) * (2 * STEP_WARPS);
     if (lane == 0) { slot[w] = a; slot[STEP_WARPS + w] = b; }
     double sa = 0.0, sb = 0.0;
     if (scope > 1) {
@@ -219,7 +220,12 @@ __device__ __forceinline__ void sum2_scope(double& a, double& b, StepShared& sh,
         sa = warp_sum(lane < STEP_WARPS ? slot[lane] : 0.0);
         sb = warp_sum(lane < STEP_WARPS ? slot[STEP_WARPS + lane] : 0.0);
     }
-    a = sa; b = sb;
+    return make_double2(sa, sb);
+}
+__device__ __forceinline__ void sum2_scope(double& a, double& b, StepShared& sh, Team& t, int scope) {
+    const double2 r = sum2_impl(a, b, &sh.wpart[0][0][0], t.turn, scope);
+    ++t.turn;
+    a = r.x; b = r.y;
 }
 __device__ __forceinline__ void team_sum2(double& a, double& b, StepShared& sh, Team& t) { sum2_scope(a, b, sh, t, t.size); }
 __device__ __forceinline__ double team_sum(double v, StepShared& sh, Team& t) {
@@ -730,7 +736,7 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
 // (cells with count 0 contribute nothing; a positive count on a zero probability gives -inf, as the cell-by-cell
 // form does).  The Gibbs operators therefore do not track their likelihood change; the running value is re-formed
 // from the tables when it is needed -- once per launch -- at O(F * (12 + S * (1 + Z + Fam))) logarithms.
-__device__ __forceinline__ double count_term(int c, double p) { return c > 0 ? (double)c * log(p) : 0.0; }
+__device__ __forceinline__ double count_term(int c, double p) { return c > 0 ? (double)c * sb_log(p) : 0.0; }
 __device__ double ll_from_counts(const DevData& d, const Chain& k, StepShared& sh, Team& tm) {
     int f_lo, f_hi;
     team_share(tm, d.F, f_lo, f_hi);
@@ -866,7 +872,7 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
 
 // ---- K7d: alter_* operators (source-free mode), zone_sampling.py:408-612 --------------------------
 // log pdf of a 2-component Dirichlet
-__device__ __forceinline__ double dir2_logpdf(double x0, double x1, double a0, double a1) {
+__device__ __noinline__ double dir2_logpdf(double x0, double x1, double a0, double a1) {
     return lgamma(a0 + a1) - lgamma(a0) - lgamma(a1) + xlogy_d(a0 - 1.0, x0) + xlogy_d(a1 - 1.0, x1);
 }
 
