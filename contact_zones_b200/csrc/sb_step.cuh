@@ -58,9 +58,12 @@ struct StepParams {
 
 // ---- shared scratch of the step kernel -----------------------------------------------------------
 #define STEP_WARPS (STEP_THREADS / 32)
-#define SB_AHEAD 32
+#ifndef SB_AHEAD
+#define SB_AHEAD 128             // steps per refill of the look-ahead table (multiple of 32)
+#endif
 // uniforms that depend on the step number only, drawn SB_AHEAD steps at a time (index into StepShared::u_ahead)
 enum { UA_ZONE = 0, UA_FAMILY, UA_FIXED, UA_CONNECTED, UA_SITE_NEW, UA_SITE_REMOVED, UA_ACCEPT, SB_N_AHEAD };
+static_assert(SB_N_AHEAD + 1 == 8 && STEP_WARPS >= 8 && SB_AHEAD % 32 == 0, "look-ahead refill: 8 tasks per slab, one warp each");
 __host__ __device__ constexpr uint32_t ahead_purpose(int q) {
     return q == UA_ZONE ? RP_ZONE : q == UA_FAMILY ? RP_FAMILY : q == UA_FIXED ? RP_FIXED : q == UA_CONNECTED ? RP_CONNECTED
          : q == UA_SITE_NEW ? RP_SITE_NEW : q == UA_SITE_REMOVED ? RP_SITE_REMOVED : RP_ACCEPT;
@@ -1069,16 +1072,22 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
         const int ia = (int)(it & (SB_AHEAD - 1));
         if (ia == 0) {
             __syncthreads();            // Gibbs steps end without a barrier: wait until nobody reads the old table
+            // eight tasks per slab of 32 steps (the operator id and the SB_N_AHEAD = 7 uniforms), one warp each:
+            // warp w takes task w % 8 of slabs w / 8, w / 8 + STEP_WARPS / 8, ...; lane l -> step + 32 * slab + l
             const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-            if (w == 0) {
-                const double uo = rng_uniform(key, step + l, RP_OP, 0);
-                int oi = 0;
-                while (oi < sp.n_ops - 1 && uo >= sp.op_cdf[oi]) ++oi;
-                sh.op_ahead[l] = sp.op_ids[oi];
-            } else {
+            const int task = w & 7;
+            for (int slab = w >> 3; slab < SB_AHEAD / 32; slab += STEP_WARPS / 8) {
+                const int a = slab * 32 + l;
+                if (task == 0) {
+                    const double uo = rng_uniform(key, step + a, RP_OP, 0);
+                    int oi = 0;
+                    while (oi < sp.n_ops - 1 && uo >= sp.op_cdf[oi]) ++oi;
+                    sh.op_ahead[a] = sp.op_ids[oi];
+                } else {
 #pragma unroll
-                for (int q = 0; q < SB_N_AHEAD; ++q)
-                    if (q % (STEP_WARPS - 1) == w - 1) sh.u_ahead[q][l] = rng_uniform(key, step + l, ahead_purpose(q), 0);
+                    for (int q = 0; q < SB_N_AHEAD; ++q)
+                        if (q == task - 1) sh.u_ahead[q][a] = rng_uniform(key, step + a, ahead_purpose(q), 0);
+                }
             }
             __syncthreads();
         }
