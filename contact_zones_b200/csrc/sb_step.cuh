@@ -874,25 +874,37 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
 
 
 // ---- K7d: alter_* operators (source-free mode), zone_sampling.py:408-612 --------------------------
-// log pdf of a 2-component Dirichlet
-__device__ __noinline__ double dir2_logpdf(double x0, double x1, double a0, double a1) {
-    return lgamma(a0 + a1) - lgamma(a0) - lgamma(a1) + xlogy_d(a0 - 1.0, x0) + xlogy_d(a1 - 1.0, x1);
-}
-
-// dirichlet_proposal on a renormalised pair (zone_sampling.py:538-569): v' ~ Dir(1 + kappa v);
-// returns new pair (scaled back by the pair's mass) and log_q - log_q_back.
-__device__ __forceinline__ void pair_proposal(RngKey key, uint64_t step, double c0, double c1, double kappa,
-                                              double& n0, double& n1, double& log_q_ratio) {
-    const double mass = c0 + c1;
-    const double t0 = c0 / mass, t1 = c1 / mass;
-    const double a0 = 1.0 + kappa * t0, a1 = 1.0 + kappa * t1;
-    const double g0 = rng_gamma(key, step, RP_PROPOSAL, 0, a0);
-    const double g1 = rng_gamma(key, step, RP_PROPOSAL, 1, a1);
-    const double v0 = g0 / (g0 + g1), v1 = g1 / (g0 + g1);
-    const double log_q = dir2_logpdf(v0, v1, a0, a1);
-    const double log_q_back = dir2_logpdf(t0, t1, 1.0 + kappa * v0, 1.0 + kappa * v1);
-    n0 = v0 * mass; n1 = v1 * mass;
-    log_q_ratio = log_q - log_q_back;
+// dirichlet_proposal on a renormalised pair (zone_sampling.py:538-569): v' ~ Dir(1 + kappa v); returns the new pair
+// (scaled back by the pair's mass) and log_q - log_q_back, the difference of two 2-component Dirichlet log-densities
+//   [lgamma(a0+a1) - lgamma(a0) - lgamma(a1) + (a0-1) ln v0 + (a1-1) ln v1]        a = 1 + kappa t  (forward)
+// - [lgamma(b0+b1) - lgamma(b0) - lgamma(b1) + (b0-1) ln t0 + (b1-1) ln t1]        b = 1 + kappa v  (back).
+// Evaluated ONCE per CTA, by warp 0, and broadcast through shared memory: lanes 0 / 1 draw the two Gammas in lock-step,
+// then lane l takes one of the six lgamma terms and one of the four x log y terms.  (Every thread used to evaluate all of
+// it -- ~3000 instructions per warp and step, which is what an alter_* step cost whatever the number of sites.)
+// Ends in a CTA barrier; sh.dshare[0..2] is rewritten only after the caller's reduction barrier.
+__device__ void pair_proposal(RngKey key, uint64_t step, double c0, double c1, double kappa, double& n0, double& n1,
+                              double& log_q_ratio, StepShared& sh) {
+    if (threadIdx.x < 32) {
+        const int lane = threadIdx.x, l = lane & 7;
+        const double mass = c0 + c1;
+        const double t0 = c0 / mass, t1 = c1 / mass;
+        const double a0 = 1.0 + kappa * t0, a1 = 1.0 + kappa * t1;
+        const double g = rng_gamma(key, step, RP_PROPOSAL, (uint32_t)(lane & 1), (lane & 1) ? a1 : a0);
+        const double g0 = __shfl_sync(0xffffffffu, g, 0), g1 = __shfl_sync(0xffffffffu, g, 1);
+        const double v0 = g0 / (g0 + g1), v1 = g1 / (g0 + g1);
+        const double b0 = 1.0 + kappa * v0, b1 = 1.0 + kappa * v1;
+        const double X = l == 0 ? a0 : l == 1 ? a1 : l == 2 ? b0 : l == 3 ? b1 : l == 4 ? a0 + a1 : b0 + b1;
+        const double sgn = (l == 0 || l == 1 || l == 5) ? -1.0 : 1.0;
+        double term = l < 6 ? sgn * lgamma(X) : 0.0;
+        const double coef = l == 0 ? a0 - 1.0 : l == 1 ? a1 - 1.0 : l == 2 ? -(b0 - 1.0) : -(b1 - 1.0);
+        const double Y = l == 0 ? v0 : l == 1 ? v1 : l == 2 ? t0 : t1;
+        if (l < 4) term += xlogy_d(coef, Y);
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) term += __shfl_xor_sync(0xffffffffu, term, o);
+        if (lane == 0) { sh.dshare[0] = v0 * mass; sh.dshare[1] = v1 * mass; sh.dshare[2] = term; }
+    }
+    __syncthreads();
+    n0 = sh.dshare[0]; n1 = sh.dshare[1]; log_q_ratio = sh.dshare[2];
 }
 
 // ordered pair of distinct indices out of n (== random.sample(list, 2))
@@ -955,7 +967,7 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
         int a = 0, b = 1;
         if (d.C == 3) pick_pair(key, step, 3, a, b);                  // _random.sample([0,1,2], 2)  :423
         double* w = k.w + (size_t)f * 3;
-        pair_proposal(key, step, w[a], w[b], sp.prec_w, n0, n1, lqr);
+        pair_proposal(key, step, w[a], w[b], sp.prec_w, n0, n1, lqr, sh);
         __shared__ double wrow_new[12];
         if (threadIdx.x == 0) {
             double v[3] = {w[0], w[1], w[2]};
@@ -1005,15 +1017,21 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
             pcache = k.ppf + (size_t)tab * d.F + f;
         }
     }
-    pair_proposal(key, step, row[s0], row[s1], kappa, n0, n1, lqr);
+    pair_proposal(key, step, row[s0], row[s1], kappa, n0, n1, lqr, sh);
     double new_prior_term = 0.0;
     if (alpha) {
-        // Dirichlet prior of the changed row with the two entries replaced (read before the reduction's barrier)
-        double t = *lnorm;
-        for (int s = 0; s < d.S; ++s)
-            if (mask >> s & 1u) t += xlogy_d(alpha[s] - 1.0, s == s0 ? n0 : (s == s1 ? n1 : row[s]));
-        new_prior_term = t;
-        dprior = t - *pcache;
+        // Dirichlet prior of the changed row with the two entries replaced (read before the reduction's barrier):
+        // warp 0, one state per lane
+        if (threadIdx.x < 32) {
+            double t = 0.0;
+            for (int s = threadIdx.x; s < d.S; s += 32)
+                if (mask >> s & 1u) t += xlogy_d(alpha[s] - 1.0, s == s0 ? n0 : (s == s1 ? n1 : row[s]));
+            t = warp_sum(t);
+            if (threadIdx.x == 0) sh.dshare[3] = *lnorm + t;
+        }
+        __syncthreads();
+        new_prior_term = sh.dshare[3];
+        dprior = new_prior_term - *pcache;
     }
     dll = column_delta(d, k, f, sites, n_sites, nullptr, which, tab, s0, s1, n0, n1, sh, tm);
     const bool accept = flog(rng_uniform(key, step, RP_ACCEPT, 0), k.flt) < dll - lqr + dprior;
