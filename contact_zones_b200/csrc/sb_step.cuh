@@ -62,12 +62,15 @@ struct StepParams {
 #define SB_AHEAD 128             // steps per refill of the look-ahead table (multiple of 32)
 #endif
 // uniforms that depend on the step number only, drawn SB_AHEAD steps at a time (index into StepShared::u_ahead)
-enum { UA_ZONE = 0, UA_FAMILY, UA_FIXED, UA_CONNECTED, UA_SITE_NEW, UA_SITE_REMOVED, UA_ACCEPT, SB_N_AHEAD };
-static_assert(SB_N_AHEAD + 1 == 8 && STEP_WARPS >= 8 && SB_AHEAD % 32 == 0, "look-ahead refill: 8 tasks per slab, one warp each");
+enum { UA_ZONE = 0, UA_FAMILY, UA_FIXED, UA_CONNECTED, UA_SITE_NEW, UA_SITE_REMOVED, UA_ACCEPT, UA_FEATURE, UA_PAIR_A,
+       UA_PAIR_B, SB_N_AHEAD };
+static_assert(SB_AHEAD % 32 == 0, "look-ahead refill works on slabs of 32 steps");
 __host__ __device__ constexpr uint32_t ahead_purpose(int q) {
     return q == UA_ZONE ? RP_ZONE : q == UA_FAMILY ? RP_FAMILY : q == UA_FIXED ? RP_FIXED : q == UA_CONNECTED ? RP_CONNECTED
-         : q == UA_SITE_NEW ? RP_SITE_NEW : q == UA_SITE_REMOVED ? RP_SITE_REMOVED : RP_ACCEPT;
+         : q == UA_SITE_NEW ? RP_SITE_NEW : q == UA_SITE_REMOVED ? RP_SITE_REMOVED : q == UA_ACCEPT ? RP_ACCEPT
+         : q == UA_FEATURE ? RP_FEATURE : RP_PAIR;
 }
+__host__ __device__ constexpr uint32_t ahead_index(int q) { return q == UA_PAIR_B ? 1u : 0u; }   // counter index of the draw
 struct StepShared {
     double red[33];
     int redi[33];
@@ -908,9 +911,9 @@ __device__ void pair_proposal(RngKey key, uint64_t step, double c0, double c1, d
 }
 
 // ordered pair of distinct indices out of n (== random.sample(list, 2))
-__device__ __forceinline__ void pick_pair(RngKey key, uint64_t step, int n, int& a, int& b) {
-    a = rng_int(key, step, RP_PAIR, 0, n);
-    b = rng_int(key, step, RP_PAIR, 1, n - 1);
+__device__ __forceinline__ void pick_pair(const double* ua, int n, int& a, int& b) {
+    a = ahead_int(ua[UA_PAIR_A * SB_AHEAD], n);
+    b = ahead_int(ua[UA_PAIR_B * SB_AHEAD], n - 1);
     if (b >= a) ++b;
 }
 // index of the j-th applicable state of a feature
@@ -960,12 +963,13 @@ __device__ double column_delta(const DevData& d, const Chain& k, int f, const in
 
 // alter_weights / alter_p_global / alter_p_zones / alter_p_families (zone_sampling.py:408-612). Returns accepted.
 __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k, int op, RngKey key, uint64_t step,
-                         double& ll, double& prior, StepShared& sh, Team& tm, bool& synced) {
-    const int f = rng_int(key, step, RP_FEATURE, 0, d.F);            // np.random.choice(range(n_features))
+                         double& ll, double& prior, StepShared& sh, Team& tm, const double* ua, bool& synced) {
+    // ua: this step's column of the look-ahead table (ua[q * SB_AHEAD] = uniform q of the step)
+    const int f = ahead_int(ua[UA_FEATURE * SB_AHEAD], d.F);          // np.random.choice(range(n_features))
     double lqr, n0, n1, dll, dprior = 0.0;
     if (op == SB_OP_ALTER_WEIGHTS) {
         int a = 0, b = 1;
-        if (d.C == 3) pick_pair(key, step, 3, a, b);                  // _random.sample([0,1,2], 2)  :423
+        if (d.C == 3) pick_pair(ua, 3, a, b);                         // _random.sample([0,1,2], 2)  :423
         double* w = k.w + (size_t)f * 3;
         pair_proposal(key, step, w[a], w[b], sp.prec_w, n0, n1, lqr, sh);
         __shared__ double wrow_new[12];
@@ -976,7 +980,7 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
         }
         __syncthreads();
         dll = column_delta(d, k, f, nullptr, d.N, wrow_new, -1, 0, 0, 0, 0.0, 0.0, sh, tm);
-        const bool accept = flog(rng_uniform(key, step, RP_ACCEPT, 0), k.flt) < dll - lqr;
+        const bool accept = flog(ua[UA_ACCEPT * SB_AHEAD], k.flt) < dll - lqr;
         synced = !accept;       // a rejected proposal wrote nothing after the reduction's barrier
         if (accept) {
             __syncthreads();
@@ -993,7 +997,7 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
     const int napp = d.n_app[f];
     if (napp < 2) return false;       // the reference's random.sample(list, 2) raises here; we reject the step
     int ia, ib;
-    pick_pair(key, step, napp, ia, ib);                               // _random.sample(list(f_states), 2)
+    pick_pair(ua, napp, ia, ib);                                      // _random.sample(list(f_states), 2)
     const int s0 = nth_state(mask, ia), s1 = nth_state(mask, ib);
     double* row;
     int which, tab = 0;
@@ -1005,11 +1009,11 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
         which = 0; row = k.pg + (size_t)f * d.S; kappa = sp.prec_g;
         if (d.pg_type == 1) { alpha = d.alpha_g + (size_t)f * d.S; lnorm = d.lnorm_g + f; pcache = k.ppg + f; }
     } else if (op == SB_OP_ALTER_P_ZONES) {
-        which = 1; tab = rng_int(key, step, RP_ZONE, 0, d.Z); kappa = sp.prec_z;
+        which = 1; tab = ahead_int(ua[UA_ZONE * SB_AHEAD], d.Z); kappa = sp.prec_z;
         row = k.pz + ((size_t)tab * d.F + f) * d.S;
         sites = k.members + (size_t)tab * d.N; n_sites = k.zsize[tab];
     } else {
-        which = 2; tab = rng_int(key, step, RP_FAMILY, 0, d.Fam); kappa = sp.prec_f;
+        which = 2; tab = ahead_int(ua[UA_FAMILY * SB_AHEAD], d.Fam); kappa = sp.prec_f;
         row = k.pf + ((size_t)tab * d.F + f) * d.S;
         sites = d.fam_sites + d.fam_ptr[tab]; n_sites = d.fam_ptr[tab + 1] - d.fam_ptr[tab];
         if (d.pf_type == 1) {
@@ -1034,7 +1038,7 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
         dprior = new_prior_term - *pcache;
     }
     dll = column_delta(d, k, f, sites, n_sites, nullptr, which, tab, s0, s1, n0, n1, sh, tm);
-    const bool accept = flog(rng_uniform(key, step, RP_ACCEPT, 0), k.flt) < dll - lqr + dprior;
+    const bool accept = flog(ua[UA_ACCEPT * SB_AHEAD], k.flt) < dll - lqr + dprior;
     synced = !accept;
     if (accept) {
         __syncthreads();
@@ -1090,11 +1094,11 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
         const int ia = (int)(it & (SB_AHEAD - 1));
         if (ia == 0) {
             __syncthreads();            // Gibbs steps end without a barrier: wait until nobody reads the old table
-            // eight tasks per slab of 32 steps (the operator id and the SB_N_AHEAD = 7 uniforms), one warp each:
-            // warp w takes task w % 8 of slabs w / 8, w / 8 + STEP_WARPS / 8, ...; lane l -> step + 32 * slab + l
+            // SB_N_AHEAD + 1 tasks per slab of 32 steps (the operator id and the SB_N_AHEAD uniforms), one warp each,
+            // dealt round-robin to the warps; lane l -> step + 32 * slab + l
             const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-            const int task = w & 7;
-            for (int slab = w >> 3; slab < SB_AHEAD / 32; slab += STEP_WARPS / 8) {
+            for (int item = w; item < (SB_N_AHEAD + 1) * (SB_AHEAD / 32); item += STEP_WARPS) {
+                const int slab = item / (SB_N_AHEAD + 1), task = item - slab * (SB_N_AHEAD + 1);
                 const int a = slab * 32 + l;
                 if (task == 0) {
                     const double uo = rng_uniform(key, step + a, RP_OP, 0);
@@ -1104,7 +1108,7 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
                 } else {
 #pragma unroll
                     for (int q = 0; q < SB_N_AHEAD; ++q)
-                        if (q == task - 1) sh.u_ahead[q][a] = rng_uniform(key, step + a, ahead_purpose(q), 0);
+                        if (q == task - 1) sh.u_ahead[q][a] = rng_uniform(key, step + a, ahead_purpose(q), ahead_index(q));
                 }
             }
             __syncthreads();
@@ -1159,7 +1163,7 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
                 break;
             }
             default:
-                accepted = op_alter(d, sp, k, op, key, step, ll, prior, sh, tm, synced);
+                accepted = op_alter(d, sp, k, op, key, step, ll, prior, sh, tm, &sh.u_ahead[0][ia], synced);
                 break;
         }
         // the source sweep has ONE call site (gibbs_sample_sources and every accepted zone move): it is the largest
