@@ -51,8 +51,12 @@ CASES = {
                          n_steps=60000, n_samples=3000, max_m=10),      # 28 sites: MAX_M = 30 would let two zones take them all
     'run_E_samerica': dict(bundled='south_america', Z=3, inh=True, src=True, cp=True, geo='uniform', size='uniform',
                            n_steps=60000, n_samples=3000),
+    # experiments/simulation/sim_exp1 (BASELINE.json configs[0]): its 951 bundled sites, features drawn by the
+    # reference's own simulator (seeded; strength 1 = I_CONTACT 3 / E_CONTACT 0.5, area 4 of run_sim_exp1.py),
+    # model as in its config.json (1 area, MAX_M 200, no families, uniform priors); starts at the simulated area
+    'run_F_simexp1': dict(simulated='sim_exp1', Z=1, inh=False, src=True, cp=False, geo='uniform', size='none',
+                          n_steps=40000, n_samples=2000, max_m=200),
 }
-SCALES = {}         # case -> (scale_counts universal, scale_counts inheritance); default (10, 10)
 
 
 def prior_config(c):
@@ -83,6 +87,10 @@ def build(case, seed=7):
                  Fam=data.families.shape[0], scales=(info['scale_universal'], info['scale_inheritance']))
         # "planted" = the sites of the initial zones: planted_occ then tracks how much of the start survives
         data.planted_zones = synthetic.random_state(data, c['Z'], 5, c['inh'], False, seed=seed + 1)['zones']
+    elif 'simulated' in c:
+        import refdata
+        data, info = refdata.load_simulated(c['simulated'], seed=seed)
+        c.update(N=data.features.shape[0], F=data.features.shape[1], S=data.features.shape[2], Fam=0)
     else:
         data = synthetic.make_data(c['N'], c['F'], c['S'], n_families=c['Fam'], na_frac=0.03, seed=seed,
                                    counts_prior=c['cp'], planted_zones=max(1, c['Z']), planted_size=10,

@@ -53,3 +53,33 @@ def load_bundled(name):
     info = {'inheritance': bool(cfg['model']['INHERITANCE']), 'scale_universal': pu.get('scale_counts'),
             'scale_inheritance': pi.get('scale_counts'), 'mcmc': cfg['mcmc'], 'model': cfg['model']}
     return data, info
+
+
+def load_simulated(name='sim_exp1', seed=0, i_contact=3, e_contact=0.5, area=4):
+    """experiments/simulation/<name>: the bundled sites with features drawn by the reference's OWN simulator
+    (sbayes/simulation.py:Simulation.run_simulation, seeded), as `run_sim_exp1.py` does for one (strength, area) setup."""
+    import pathlib
+    import random
+    refshim.install()
+    from sbayes.simulation import Simulation
+    base = os.path.join(EXPERIMENTS, 'simulation', name)
+    cfg = json.load(open(os.path.join(base, 'config.json')))
+    sim_cfg = json.load(open(os.path.join(refshim.REFERENCE_ROOT, 'sbayes', 'config', 'default_config_simulation.json')))
+    sim_cfg.update(cfg['simulation'])
+    sim_cfg.update(SITES=os.path.join(base, cfg['simulation']['SITES']), I_CONTACT=i_contact, E_CONTACT=e_contact,
+                   AREA=area)
+    exp = types.SimpleNamespace(path_results=pathlib.Path('/tmp'), config={'simulation': sim_cfg})
+    random.seed(seed)
+    np.random.seed(seed)
+    sim = Simulation(experiment=exp)
+    with contextlib.redirect_stdout(io.StringIO()):
+        sim.run_simulation()
+    n = sim.features.shape[0]
+    data = types.SimpleNamespace(
+        features=np.asarray(sim.features, bool), families=np.zeros((0, n), bool), states=np.asarray(sim.states, bool),
+        network=sim.network, prior_universal={}, prior_inheritance={}, geo_prior=sim.geo_prior,
+        state_names=sim.state_names, feature_names=sim.feature_names, family_names=None, site_names=sim.site_names,
+        is_simulated=True, crs=None, planted_zones=np.asarray(sim.areas, bool))
+    info = {'inheritance': False, 'scale_universal': None, 'scale_inheritance': None, 'mcmc': cfg['mcmc'],
+            'model': cfg['model']}
+    return data, info
