@@ -174,7 +174,7 @@ int sb_create(sb_ctx** out, int device, const sb_dims* dims) {
     int spt = 64;
     ctx->sites_per_tile = spt;
     ctx->n_tiles = (N + spt - 1) / spt;
-    DA(ctx->partial, nc * ctx->n_tiles);
+    DA(ctx->partial, nc * (size_t)std::max(ctx->n_tiles, d.ldx >> 4));     // per site tile or per 16-feature block
     ctx->geo_cap = N < 4096 ? N : 4096;
     ctx->h_zone_size.assign(nc * (size_t)(Z > 0 ? Z : 1), 0);
     CK(cudaStreamSynchronize(ctx->stream));
@@ -412,6 +412,17 @@ static int recount_chains(sb_ctx* ctx, int chain, int n) {
     const DevData& d = ctx->d;
     ChainArrays& st = ctx->st;
     const size_t nn = (size_t)n;
+    const size_t cb_smem = count_block_smem(d.S, d.Z, d.Fam);
+    if (d.sample_source && cb_smem <= 200 * 1024) {
+        // blocked recount: shared-memory counters per (16-feature block, chain), every table entry written once
+        if (cb_smem > 48 * 1024)
+            CK(cudaFuncSetAttribute(count_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem));
+        dim3 grid((unsigned)(d.ldx >> 4), (unsigned)n);
+        count_block_kernel<<<grid, 256, cb_smem, ctx->stream>>>(d, st, chain);
+        ++ctx->launches;
+        CK(cudaGetLastError());
+        return SB_OK;
+    }
     CK(cudaMemsetAsync(st.cnt_glob + chain * st.s_cnt_glob, 0, nn * st.s_cnt_glob * sizeof(int), ctx->stream));
     CK(cudaMemsetAsync(st.cnt_zone + chain * st.s_cnt_zone, 0, nn * st.s_cnt_zone * sizeof(int), ctx->stream));
     CK(cudaMemsetAsync(st.cnt_fam + chain * st.s_cnt_fam, 0, nn * st.s_cnt_fam * sizeof(int), ctx->stream));
@@ -689,6 +700,18 @@ static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source
     }
     dim3 gw((d.F + 127) / 128, n);
     wnorm_kernel<<<gw, 128, 0, ctx->stream>>>(d, ctx->st, chain_begin);
+    const size_t lb_smem = lh_source_block_smem(d.S, d.Z, d.Fam);
+    if (use_source && lb_smem <= 200 * 1024) {
+        // blocked form: parameter tables of a 16-feature block staged in shared memory
+        const int nb = d.ldx >> 4;
+        if (lb_smem > 48 * 1024)
+            CK(cudaFuncSetAttribute(lh_source_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lb_smem));
+        lh_source_block_kernel<<<dim3(nb, n), LH_THREADS, lb_smem, ctx->stream>>>(d, ctx->st, chain_begin, ctx->partial, nb);
+        lh_reduce_kernel<<<n, 32, 0, ctx->stream>>>(ctx->partial, nb, ctx->st.ll, chain_begin);
+        ctx->launches += 3;
+        CK(cudaGetLastError());
+        return SB_OK;
+    }
     dim3 grid(ctx->n_tiles, n);
     if (use_source)
         lh_full_kernel<1><<<grid, LH_THREADS, 0, ctx->stream>>>(d, ctx->st, chain_begin, ctx->sites_per_tile,

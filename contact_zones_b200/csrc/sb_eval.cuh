@@ -113,6 +113,70 @@ lh_full_kernel(DevData d, ChainArrays st, int chain_begin, int sites_per_tile, d
     if (threadIdx.x == 0) partial[(size_t)blockIdx.y * n_tiles + tile] = v;
 }
 
+// K1 with source (SRC = 1), blocked form: one CTA = one (16-feature block, chain); the block's parameter tables
+// (w~ [16][12], p_* [1 + Z + Fam][16][S + 1], the extra column = 1 for NA cells) are staged in shared memory, so the
+// cell body is two shared-memory look-ups and one fp64 multiply into the running product.  Same result as
+// lh_full_kernel<1> (which remains the fallback when the tables do not fit); partial[chain][block] is reduced in
+// fixed order by lh_reduce_kernel.
+__host__ __device__ __forceinline__ size_t lh_source_block_smem(int S, int Z, int Fam) {
+    return ((size_t)16 * (S + 1) * (1 + Z + Fam) + 192) * sizeof(double);
+}
+__global__ void __launch_bounds__(LH_THREADS)
+lh_source_block_kernel(DevData d, ChainArrays st, int chain_begin, double* __restrict__ partial, int n_blocks) {
+    extern __shared__ double lb_tab[];
+    __shared__ double red[33];
+    const int chain = chain_begin + blockIdx.y;
+    const int f0 = blockIdx.x << 4;
+    const int S = d.S, S1 = S + 1, F = d.F, N = d.N;
+    const int nf = min(16, F - f0);
+    const int bP = 16 * S1, n_rows = 16 * (1 + d.Z + d.Fam);
+    const size_t FS = (size_t)F * S;
+    double* W = lb_tab + n_rows * S1;
+    const int8_t* __restrict__ zone_id = st.zone_id + chain * st.s_zone_id;
+    const uint8_t* __restrict__ src = st.source + chain * st.s_source;
+    const double* __restrict__ wn = st.wnorm + chain * st.s_wnorm;
+    for (int i = threadIdx.x; i < 192; i += blockDim.x) W[i] = i < nf * 12 ? wn[(size_t)f0 * 12 + i] : 1.0;
+    for (int r = threadIdx.x; r < n_rows; r += blockDim.x) {
+        const int t = r >> 4, j = r & 15;
+        const double* srow = (t == 0 ? st.p_global + chain * st.s_p_global
+                                     : (t <= d.Z ? st.p_zones + chain * st.s_p_zones + (size_t)(t - 1) * FS
+                                                 : st.p_fam + chain * st.s_p_fam + (size_t)(t - 1 - d.Z) * FS))
+                             + (size_t)(f0 + j) * S;
+        double* dst = lb_tab + r * S1;
+        for (int sx = 0; sx < S; ++sx) dst[sx] = j < nf ? srow[sx] : 1.0;
+        dst[S] = 1.0;
+    }
+    __syncthreads();
+    LogProd acc;
+    lp_init(acc);
+    bool zero_weight = false;
+    for (int n = threadIdx.x; n < N; n += blockDim.x) {
+        const uint4 xv = __ldg(reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + f0));
+        const uint4 sv = *reinterpret_cast<const uint4*>(src + (size_t)n * d.ldx + f0);
+        const int zid = zone_id[n];
+        const int fam = d.inheritance ? d.fam_id[n] : -1;
+        const int cfg = (zid >= 0 ? 1 : 0) + (fam >= 0 ? 2 : 0);
+        const int bz = (1 + max(zid, 0)) * bP, bf = (1 + d.Z + max(fam, 0)) * bP;
+        const double* wr = W + cfg * 3;
+        const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+        const uint32_t sw[4] = {sv.x, sv.y, sv.z, sv.w};
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            if (j >= nf) break;                                             // CTA-uniform (padding columns)
+            const int xs = (xw[j >> 2] >> ((j & 3) * 8)) & 0xff;
+            const int sc = (sw[j >> 2] >> ((j & 3) * 8)) & 0xff;
+            const double ws = wr[j * 12 + sc];
+            if (ws == 0.0) { zero_weight = true; continue; }                // model.py:177-184: log 0
+            const int e = j * S1 + min(xs, S);                              // NA -> the column of ones
+            lp_mul(acc, ws * lb_tab[(sc == 0 ? 0 : (sc == 1 ? bz : bf)) + e]);
+        }
+    }
+    double v = lp_value(acc);
+    if (zero_weight) v = -INFINITY;
+    v = block_sum(v, red);
+    if (threadIdx.x == 0) partial[(size_t)blockIdx.y * n_blocks + blockIdx.x] = v;
+}
+
 __global__ void lh_reduce_kernel(const double* __restrict__ partial, int n_tiles, double* __restrict__ ll,
                                  int chain_begin) {
     // one warp per chain, fixed order
@@ -303,6 +367,64 @@ count_kernel(DevData d, ChainArrays st, int chain_begin, int sites_per_tile) {
             else if (fam >= 0) atomicAdd(cf + ((size_t)fam * F + f) * S + xs, 1);
         }
     }
+}
+
+// K4 (full recount), blocked form: one CTA = one (16-feature block, chain).  The block's counters -- [1 + Z + Fam]
+// tables of [16][S] and the source table [16][12] -- live in shared memory, are filled with shared-memory atomics
+// while the CTA streams its 16-byte column strip of x and source over all sites, and are flushed with plain stores:
+// no global atomics and no zeroing pass (every entry of the block's rows is written).  Same semantics as
+// count_kernel, which remains the fallback when the tables of a block do not fit in shared memory.
+__host__ __device__ __forceinline__ size_t count_block_smem(int S, int Z, int Fam) {
+    return ((size_t)16 * S * (1 + Z + Fam) + 192) * sizeof(int);
+}
+__global__ void __launch_bounds__(256)
+count_block_kernel(DevData d, ChainArrays st, int chain_begin) {
+    extern __shared__ int cb_tab[];
+    const int chain = chain_begin + blockIdx.y;
+    const int f0 = blockIdx.x << 4;
+    const int S = d.S, F = d.F, N = d.N;
+    const int nf = min(16, F - f0);
+    const int bS = 16 * S, n_rows = 16 * (1 + d.Z + d.Fam);
+    int* tcs = cb_tab + n_rows * S;
+    const int T = n_rows * S + 192;
+    const int8_t* __restrict__ zone_id = st.zone_id + chain * st.s_zone_id;
+    const uint8_t* __restrict__ src = st.source + chain * st.s_source;
+    for (int i = threadIdx.x; i < T; i += blockDim.x) cb_tab[i] = 0;
+    __syncthreads();
+    for (int n = threadIdx.x; n < N; n += blockDim.x) {
+        const uint4 xv = __ldg(reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + f0));
+        const uint4 sv = *reinterpret_cast<const uint4*>(src + (size_t)n * d.ldx + f0);
+        const int zid = zone_id[n];
+        const int fam = d.inheritance ? d.fam_id[n] : -1;
+        const int cfg = (zid >= 0 ? 1 : 0) + (fam >= 0 ? 2 : 0);
+        const int bz = (1 + max(zid, 0)) * bS, bf = (1 + d.Z + max(fam, 0)) * bS;
+        const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+        const uint32_t sw[4] = {sv.x, sv.y, sv.z, sv.w};
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            if (j >= nf) break;                                             // CTA-uniform (padding columns)
+            const int xs = (xw[j >> 2] >> ((j & 3) * 8)) & 0xff;
+            const int s = (sw[j >> 2] >> ((j & 3) * 8)) & 0xff;
+            atomicAdd(tcs + j * 12 + cfg * 3 + s, 1);
+            if (xs == SB_NA) continue;
+            if (s == 0) atomicAdd(cb_tab + j * S + xs, 1);
+            else if (s == 1) { if (zid >= 0) atomicAdd(cb_tab + bz + j * S + xs, 1); }
+            else if (fam >= 0) atomicAdd(cb_tab + bf + j * S + xs, 1);
+        }
+    }
+    __syncthreads();
+    const size_t FS = (size_t)F * S;
+    for (int r = threadIdx.x; r < n_rows; r += blockDim.x) {
+        const int t = r >> 4, j = r & 15;
+        if (j >= nf) continue;
+        int* dst = (t == 0 ? st.cnt_glob + chain * st.s_cnt_glob
+                           : (t <= d.Z ? st.cnt_zone + chain * st.s_cnt_zone + (size_t)(t - 1) * FS
+                                       : st.cnt_fam + chain * st.s_cnt_fam + (size_t)(t - 1 - d.Z) * FS))
+                   + (size_t)(f0 + j) * S;
+        for (int sx = 0; sx < S; ++sx) dst[sx] = cb_tab[r * S + sx];
+    }
+    int* cs = st.cnt_src + chain * st.s_cnt_src + (size_t)f0 * 12;
+    for (int i = threadIdx.x; i < nf * 12; i += blockDim.x) cs[i] = tcs[i];
 }
 
 // ---------------------------------------------------------------------------------------------
