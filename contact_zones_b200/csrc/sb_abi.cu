@@ -33,6 +33,9 @@ struct sb_ctx {
     bool has_data = false, has_priors = false, has_ops = false;
     std::vector<void*> allocs;
     double* partial = nullptr;       // [n_chains][n_tiles]
+    cudaEvent_t direct_done = nullptr;   // last direct (unstaged) upload from page-locked caller memory
+    uint8_t* src_scratch = nullptr;      // device scratch of the unstaged source upload ([chains][N][F], unpadded)
+    size_t src_scratch_bytes = 0;
     int n_tiles = 0, sites_per_tile = 0;
     LhTab lt{};                      // static layout of the table-driven K1 (sb_lhtab.cuh)
     double* lt_partial = nullptr;    // [n_chains][lt.n_tiles * lt.n_chunks]
@@ -199,6 +202,8 @@ int sb_destroy(sb_ctx* ctx) {
         if (sg.done) { cudaEventSynchronize(sg.done); cudaEventDestroy(sg.done); }
         if (sg.buf) cudaFreeHost(sg.buf);
     }
+    if (ctx->direct_done) cudaEventDestroy(ctx->direct_done);
+    if (ctx->src_scratch) cudaFree(ctx->src_scratch);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
     return SB_OK;
@@ -459,6 +464,30 @@ static int staging_acquire(sb_ctx* ctx, size_t bytes, Staging** out) {
     return SB_OK;
 }
 
+// rows of F bytes -> rows of ld bytes (ld = F rounded up to 16), padding zero; one thread per 16-byte unit
+__global__ void pad_rows_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, size_t n_rows, int F, int ld) {
+    const int upr = ld >> 4;
+    const size_t u = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (u >= n_rows * upr) return;
+    const size_t r = u / upr;
+    const int b0 = (int)(u - r * upr) << 4;
+    const uint8_t* s = src + r * (size_t)F + b0;
+    uint32_t w[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+    for (int i = 0; i < 16; ++i)
+        if (b0 + i < F) w[i >> 2] |= (uint32_t)s[i] << ((i & 3) * 8);
+    *reinterpret_cast<uint4*>(dst + r * (size_t)ld + b0) = make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+// Page-locked (cudaMallocHost / cudaHostRegister / torch pin_memory) caller memory can be read by the copy engine
+// directly; pageable memory has to go through the pinned staging buffer.
+static bool host_pinned(const void* p) {
+    if (!p) return false;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+}
+
 // n consecutive chains from arrays stacked along a leading chain axis.  Staging layout = device layout (array-major,
 // per-chain strides st.s_*), so every device array is filled by ONE copy whatever n is.
 static int set_states_impl(sb_ctx* ctx, int chain, int n, const uint8_t* zones, const double* weights,
@@ -486,6 +515,39 @@ static int set_states_impl(sb_ctx* ctx, int chain, int n, const uint8_t* zones, 
     if (r != SB_OK) return r;
     unsigned char* b = sg->buf;
 
+    // Large arrays in page-locked caller memory skip the staging copy: their device layout equals the caller's
+    // (the source rows via a device scratch and a row-padding kernel), so the copy engine
+    // reads them in place while the host threads below pack the zones and validate the source.  The call then waits
+    // for these copies before it returns -- the host pointers are borrowed for the duration of the call only.
+    cudaStream_t sm = ctx->stream;
+    const size_t nn = (size_t)n;
+    const bool dir_pg = host_pinned(p_global), dir_pz = Z > 0 && host_pinned(p_zones);
+    const bool dir_pf = d.inheritance && host_pinned(p_families), dir_src = d.sample_source && host_pinned(source);
+    if (dir_pg) CK(cudaMemcpyAsync(st.p_global + chain * st.s_p_global, p_global, nn * FS * sizeof(double), cudaMemcpyHostToDevice, sm));
+    if (dir_pz) CK(cudaMemcpyAsync(st.p_zones + chain * st.s_p_zones, p_zones, nn * Z * FS * sizeof(double), cudaMemcpyHostToDevice, sm));
+    if (dir_pf) CK(cudaMemcpyAsync(st.p_fam + chain * st.s_p_fam, p_families, nn * Fam * FS * sizeof(double), cudaMemcpyHostToDevice, sm));
+    if (dir_src) {
+        // one contiguous copy into a device scratch, then a kernel pads the rows from F to ldx bytes (a pitched copy
+        // of 200-byte rows runs at a row per ~0.1 us on the copy engine: 13 ms for 64 chains at shape D)
+        const size_t need = nn * N * F;
+        if (ctx->src_scratch_bytes < need) {
+            if (ctx->src_scratch) { CK(cudaStreamSynchronize(sm)); CK(cudaFree(ctx->src_scratch)); ctx->src_scratch = nullptr; }
+            CK(cudaMalloc((void**)&ctx->src_scratch, need));
+            ctx->src_scratch_bytes = need;
+        }
+        CK(cudaMemcpyAsync(ctx->src_scratch, source, need, cudaMemcpyHostToDevice, sm));
+        const size_t units = nn * N * (size_t)(d.ldx >> 4);
+        pad_rows_kernel<<<(unsigned)((units + 255) / 256), 256, 0, sm>>>(ctx->src_scratch, st.source + chain * st.s_source,
+                                                                          nn * N, F, d.ldx);
+        ++ctx->launches;
+        CK(cudaGetLastError());
+    }
+    const bool any_direct = dir_pg || dir_pz || dir_pf || dir_src;
+    if (any_direct) {
+        if (!ctx->direct_done) CK(cudaEventCreateWithFlags(&ctx->direct_done, cudaEventDisableTiming));
+        CK(cudaEventRecord(ctx->direct_done, sm));
+    }
+
     // packing is host memory bandwidth: spread the chains over a few threads when there are many
     std::vector<int> h_sizes((size_t)n * st.s_zone_size, 0);
     auto pack = [&](int c) -> int {
@@ -512,10 +574,10 @@ static int set_states_impl(sb_ctx* ctx, int chain, int n, const uint8_t* zones, 
         const double* wc = weights + (size_t)c * F * C;
         for (int f = 0; f < F; ++f)
             for (int k = 0; k < 3; ++k) w3[(size_t)f * 3 + k] = k < C ? wc[(size_t)f * C + k] : 0.0;
-        memcpy(b + o_pg + (size_t)c * FS * sizeof(double), p_global + (size_t)c * FS, FS * sizeof(double));
-        if (Z > 0)
+        if (!dir_pg) memcpy(b + o_pg + (size_t)c * FS * sizeof(double), p_global + (size_t)c * FS, FS * sizeof(double));
+        if (Z > 0 && !dir_pz)
             memcpy(b + o_pz + (size_t)c * Z * FS * sizeof(double), p_zones + (size_t)c * Z * FS, (size_t)Z * FS * sizeof(double));
-        if (d.inheritance)
+        if (d.inheritance && !dir_pf)
             memcpy(b + o_pf + (size_t)c * Fam * FS * sizeof(double), p_families + (size_t)c * Fam * FS,
                    (size_t)Fam * FS * sizeof(double));
         if (d.sample_source) {
@@ -523,9 +585,11 @@ static int set_states_impl(sb_ctx* ctx, int chain, int n, const uint8_t* zones, 
             unsigned bad = 0;
             for (int i = 0; i < N; ++i) {
                 const uint8_t* srow = source + ((size_t)c * N + i) * F;
-                unsigned char* drow = hs + (size_t)i * d.ldx;
-                memcpy(drow, srow, (size_t)F);
-                memset(drow + F, 0, (size_t)(d.ldx - F));
+                if (!dir_src) {
+                    unsigned char* drow = hs + (size_t)i * d.ldx;
+                    memcpy(drow, srow, (size_t)F);
+                    memset(drow + F, 0, (size_t)(d.ldx - F));
+                }
                 unsigned char mx = 0;
                 for (int f = 0; f < F; ++f) mx = srow[f] > mx ? srow[f] : mx;      // vectorises (pmaxub)
                 bad |= (unsigned)(mx >= C);
@@ -552,12 +616,11 @@ static int set_states_impl(sb_ctx* ctx, int chain, int n, const uint8_t* zones, 
         for (auto& th : pool) th.join();
         for (int e : rc) if (e != SB_OK) status = e;
     }
+    if (status != SB_OK && any_direct) CK(cudaEventSynchronize(ctx->direct_done));       // borrowed pointers: drain first
     if (status == SB_E_OVERLAP) FAIL(SB_E_OVERLAP, "sb_set_state: zones overlap (a site belongs to two zones)");
     if (status != SB_OK) FAIL(SB_E_ARG, "sb_set_state: source component out of range");
     for (size_t i = 0; i < h_sizes.size(); ++i) ctx->h_zone_size[(size_t)chain * st.s_zone_size + i] = h_sizes[i];
 
-    cudaStream_t sm = ctx->stream;
-    const size_t nn = (size_t)n;
     CK(cudaMemcpyAsync(st.zone_id + chain * st.s_zone_id, b + o_zid, nn * st.s_zone_id, cudaMemcpyHostToDevice, sm));
     if (Z > 0) {
         CK(cudaMemcpyAsync(st.zone_members + chain * st.s_zone_members, b + o_mem, nn * st.s_zone_members * sizeof(int),
@@ -566,12 +629,13 @@ static int set_states_impl(sb_ctx* ctx, int chain, int n, const uint8_t* zones, 
                            cudaMemcpyHostToDevice, sm));
     }
     CK(cudaMemcpyAsync(st.weights + chain * st.s_weights, b + o_w, nn * st.s_weights * sizeof(double), cudaMemcpyHostToDevice, sm));
-    CK(cudaMemcpyAsync(st.p_global + chain * st.s_p_global, b + o_pg, nn * FS * sizeof(double), cudaMemcpyHostToDevice, sm));
-    if (Z > 0)
+    if (!dir_pg)
+        CK(cudaMemcpyAsync(st.p_global + chain * st.s_p_global, b + o_pg, nn * FS * sizeof(double), cudaMemcpyHostToDevice, sm));
+    if (Z > 0 && !dir_pz)
         CK(cudaMemcpyAsync(st.p_zones + chain * st.s_p_zones, b + o_pz, nn * Z * FS * sizeof(double), cudaMemcpyHostToDevice, sm));
-    if (d.inheritance)
+    if (d.inheritance && !dir_pf)
         CK(cudaMemcpyAsync(st.p_fam + chain * st.s_p_fam, b + o_pf, nn * Fam * FS * sizeof(double), cudaMemcpyHostToDevice, sm));
-    if (d.sample_source)
+    if (d.sample_source && !dir_src)
         CK(cudaMemcpyAsync(st.source + chain * st.s_source, b + o_src, nn * st.s_source, cudaMemcpyHostToDevice, sm));
     CK(cudaEventRecord(sg->done, sm));
     sg->pending = true;
@@ -579,7 +643,9 @@ static int set_states_impl(sb_ctx* ctx, int chain, int n, const uint8_t* zones, 
     wnorm_kernel<<<grid, 128, 0, ctx->stream>>>(d, st, chain);
     ++ctx->launches;
     CK(cudaGetLastError());
-    return recount_chains(ctx, chain, n);
+    r = recount_chains(ctx, chain, n);
+    if (any_direct) CK(cudaEventSynchronize(ctx->direct_done));     // the copy engine is done with the caller's memory
+    return r;
 }
 
 int sb_set_state(sb_ctx* ctx, int chain, const uint8_t* zones, const double* weights, const double* p_global,

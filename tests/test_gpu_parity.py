@@ -212,4 +212,27 @@ def test_bulk_upload_equals_single_uploads(built_lib):
         for k in sa:
             assert np.array_equal(sa[k], sb[k]), k
         assert np.array_equal(sa['zones'], zones[i]) and np.array_equal(np.argmax(sa['source'], -1), src[i])
-    a.close(); b.close()
+    # page-locked caller memory takes the unstaged path (direct copies, pitched for the source rows: F = 36 is not a
+    # multiple of 16); an out-of-range source value must still be refused and leave the call clean
+    import torch
+    pin = [torch.from_numpy(np.ascontiguousarray(v)).pin_memory().numpy()
+           for v in (np.stack(zones).astype(np.uint8), w, pg, pz, pf, np.stack(src))]
+    p = make_engine(c, n_chains=n)
+    p.set_states(0, *pin)
+    for x, y in zip(p.eval(), ra):
+        assert np.array_equal(x, y)
+    for i in (0, n - 1):
+        cp, ca = p.counts(i), a.counts(i)
+        for k in cp:
+            assert np.array_equal(cp[k], ca[k]), k
+        sp_, sa = p.get_state(i), a.get_state(i)
+        for k in sp_:
+            assert np.array_equal(sp_[k], sa[k]), k
+    pin[5][2, 3, 4] = 7
+    with pytest.raises(Exception):
+        p.set_states(0, *pin)
+    pin[5][2, 3, 4] = src[2][3, 4]
+    p.set_states(0, *pin)
+    for x, y in zip(p.eval(), ra):
+        assert np.array_equal(x, y)
+    a.close(); b.close(); p.close()
