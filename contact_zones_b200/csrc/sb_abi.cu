@@ -675,28 +675,48 @@ int sb_get_state(sb_ctx* ctx, int chain, uint8_t* zones, double* weights, double
     const DevData& d = ctx->d;
     ChainArrays& st = ctx->st;
     const int N = d.N, F = d.F, S = d.S, Z = d.Z, C = d.C, Fam = d.Fam;
-    if (zones && Z > 0) {
-        std::vector<int8_t> zid(st.s_zone_id);
-        D2H(zid.data(), st.zone_id + chain * st.s_zone_id, zid.size());
+    if (source && !d.sample_source) FAIL(SB_E_STATE, "context has no source state");
+    // every requested array is copied into the pinned staging buffer asynchronously; ONE stream synchronisation, then
+    // the host-side unpacking (zone ids -> indicator rows, [F][3] -> [F][C] weights, padded -> dense source rows)
+    const size_t FS = (size_t)F * S;
+    const bool want_z = zones && Z > 0, want_pz = p_zones && Z > 0, want_pf = p_families && d.inheritance;
+    const size_t o_zid = 0;
+    const size_t o_w = align16(o_zid + (want_z ? st.s_zone_id : 0));
+    const size_t o_pg = align16(o_w + (weights ? (size_t)F * 3 * sizeof(double) : 0));
+    const size_t o_pz = o_pg + (p_global ? FS * sizeof(double) : 0);
+    const size_t o_pf = o_pz + (want_pz ? (size_t)Z * FS * sizeof(double) : 0);
+    const size_t o_src = align16(o_pf + (want_pf ? (size_t)Fam * FS * sizeof(double) : 0));
+    const size_t total = o_src + (source ? (size_t)N * d.ldx : 0);
+    Staging* sg;
+    r = staging_acquire(ctx, total > 0 ? total : 16, &sg);
+    if (r != SB_OK) return r;
+    unsigned char* b = sg->buf;
+    cudaStream_t sm = ctx->stream;
+#define GET(off, arr, bytes) CK(cudaMemcpyAsync(b + (off), (arr), (bytes), cudaMemcpyDeviceToHost, sm))
+    if (want_z) GET(o_zid, st.zone_id + chain * st.s_zone_id, st.s_zone_id);
+    if (weights) GET(o_w, st.weights + chain * st.s_weights, (size_t)F * 3 * sizeof(double));
+    if (p_global) GET(o_pg, st.p_global + chain * st.s_p_global, FS * sizeof(double));
+    if (want_pz) GET(o_pz, st.p_zones + chain * st.s_p_zones, (size_t)Z * FS * sizeof(double));
+    if (want_pf) GET(o_pf, st.p_fam + chain * st.s_p_fam, (size_t)Fam * FS * sizeof(double));
+    if (source) GET(o_src, st.source + chain * st.s_source, (size_t)N * d.ldx);
+#undef GET
+    CK(cudaStreamSynchronize(sm));
+    if (want_z) {
+        const int8_t* zid = reinterpret_cast<const int8_t*>(b + o_zid);
         memset(zones, 0, (size_t)Z * N);
         for (int n = 0; n < N; ++n)
             if (zid[n] >= 0) zones[(size_t)zid[n] * N + n] = 1;
     }
     if (weights) {
-        std::vector<double> w3((size_t)F * 3);
-        D2H(w3.data(), st.weights + chain * st.s_weights, w3.size());
+        const double* w3 = reinterpret_cast<const double*>(b + o_w);
         for (int f = 0; f < F; ++f)
             for (int c = 0; c < C; ++c) weights[(size_t)f * C + c] = w3[(size_t)f * 3 + c];
     }
-    if (p_global) D2H(p_global, st.p_global + chain * st.s_p_global, (size_t)F * S);
-    if (p_zones && Z > 0) D2H(p_zones, st.p_zones + chain * st.s_p_zones, (size_t)Z * F * S);
-    if (p_families && d.inheritance) D2H(p_families, st.p_fam + chain * st.s_p_fam, (size_t)Fam * F * S);
-    if (source) {
-        if (!d.sample_source) FAIL(SB_E_STATE, "context has no source state");
-        std::vector<uint8_t> hs((size_t)N * d.ldx);
-        D2H(hs.data(), st.source + chain * st.s_source, hs.size());
-        for (int n = 0; n < N; ++n) memcpy(source + (size_t)n * F, hs.data() + (size_t)n * d.ldx, F);
-    }
+    if (p_global) memcpy(p_global, b + o_pg, FS * sizeof(double));
+    if (want_pz) memcpy(p_zones, b + o_pz, (size_t)Z * FS * sizeof(double));
+    if (want_pf) memcpy(p_families, b + o_pf, (size_t)Fam * FS * sizeof(double));
+    if (source)
+        for (int n = 0; n < N; ++n) memcpy(source + (size_t)n * F, b + o_src + (size_t)n * d.ldx, F);
     return SB_OK;
 }
 
