@@ -257,7 +257,7 @@ def measured_peak():
         return 6650.0, 'fallback'
 
 
-def likelihood_leg(torch, device, n_launch=60, sizes=(500, 2000, 20000)):
+def likelihood_leg(torch, device, n_launch=60, sizes=(500, 1000, 2000, 5000, 10000, 20000)):
     """K1 on configs[4] (256 chains x N x 100 x 4, Z=4 zones of 25, C=2, no source): GB/s per SURVEY.md 8(d)."""
     from contact_zones_b200 import synthetic
     from contact_zones_b200.engine import Engine
