@@ -413,12 +413,19 @@ static int check_chain(sb_ctx* ctx, int chain) {
     return SB_OK;
 }
 
+// SBAYES_B200_SWEEP=0 (tests) also selects the tile-per-site fallbacks of the evaluation kernels: no shared-memory
+// tables anywhere
+static bool blocked_kernels_allowed() {
+    const char* env = getenv("SBAYES_B200_SWEEP");
+    return !(env && atoi(env) < 1);
+}
+
 static int recount_chains(sb_ctx* ctx, int chain, int n) {
     const DevData& d = ctx->d;
     ChainArrays& st = ctx->st;
     const size_t nn = (size_t)n;
     const size_t cb_smem = count_block_smem(d.S, d.Z, d.Fam);
-    if (d.sample_source && cb_smem <= 200 * 1024) {
+    if (d.sample_source && cb_smem <= 200 * 1024 && blocked_kernels_allowed()) {
         // blocked recount: shared-memory counters per (16-feature block, chain), every table entry written once
         if (cb_smem > 48 * 1024)
             CK(cudaFuncSetAttribute(count_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem));
@@ -787,7 +794,7 @@ static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source
     dim3 gw((d.F + 127) / 128, n);
     wnorm_kernel<<<gw, 128, 0, ctx->stream>>>(d, ctx->st, chain_begin);
     const size_t lb_smem = lh_source_block_smem(d.S, d.Z, d.Fam);
-    if (use_source && lb_smem <= 200 * 1024) {
+    if (lb_smem <= 200 * 1024 && blocked_kernels_allowed()) {
         // blocked form: parameter tables of a 16-feature block staged in shared memory
         const int nb = d.ldx >> 4;
         if (lb_smem > 48 * 1024)
@@ -798,13 +805,10 @@ static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source
         CK(cudaGetLastError());
         return SB_OK;
     }
+    // fallback (tables of a feature block exceed shared memory): one CTA per (site tile, chain), global gathers
     dim3 grid(ctx->n_tiles, n);
-    if (use_source)
-        lh_full_kernel<1><<<grid, LH_THREADS, 0, ctx->stream>>>(d, ctx->st, chain_begin, ctx->sites_per_tile,
-                                                               ctx->partial, ctx->n_tiles);
-    else
-        lh_full_kernel<0><<<grid, LH_THREADS, 0, ctx->stream>>>(d, ctx->st, chain_begin, ctx->sites_per_tile,
-                                                               ctx->partial, ctx->n_tiles);
+    lh_full_kernel<1><<<grid, LH_THREADS, 0, ctx->stream>>>(d, ctx->st, chain_begin, ctx->sites_per_tile, ctx->partial,
+                                                           ctx->n_tiles);
     lh_reduce_kernel<<<n, 32, 0, ctx->stream>>>(ctx->partial, ctx->n_tiles, ctx->st.ll, chain_begin);
     ctx->launches += 3;
     CK(cudaGetLastError());

@@ -1,7 +1,7 @@
 // sb_step.cuh -- K5/K7/K8: the persistent per-chain MCMC step kernel.
 //
-// One CTA owns one chain for the whole launch and runs `n_steps` Metropolis-Hastings / Gibbs steps
-// (MCMCGenerative.step, mcmc_generative.py:282-329) without any host round-trip.  All proposals are DELTAS
+// A team of CTAs (one thread-block cluster, see `Team`) owns one chain for the whole launch and runs `n_steps`
+// Metropolis-Hastings / Gibbs steps (MCMCGenerative.step, mcmc_generative.py:282-329) without any host round-trip.  All proposals are DELTAS
 // on the resident chain state (no Sample.copy(), zone_sampling.py:95-115):
 //   zone moves      O(F*C) marginal-likelihood ratio of the moved site(s)       (K5)
 //   alter_*         O(N) / O(|zone|) / O(|family|) column delta on feature f    (K5)

@@ -236,3 +236,28 @@ def test_bulk_upload_equals_single_uploads(built_lib):
     for x, y in zip(p.eval(), ra):
         assert np.array_equal(x, y)
     a.close(); b.close(); p.close()
+
+
+@pytest.mark.parametrize('name', ['C_samerica_like', 'G_samerica_data'])
+def test_fallback_evaluation_kernels(name, built_lib, monkeypatch):
+    """SBAYES_B200_SWEEP=0 selects the tile-per-site fallbacks (count_kernel, lh_full_kernel<1>: used when the tables of
+    a 16-feature block do not fit in shared memory): same likelihood within 1e-9, same count tables bit for bit."""
+    c = load_case(name)
+    g = c['g']
+    monkeypatch.setenv('SBAYES_B200_SWEEP', '0')
+    eng = make_engine(c)
+    set_golden_state(eng, c)
+    ll, _, _ = eng.eval()
+    assert rel_err(ll[0], float(g['ref_ll_src'])) < 1e-9
+    slow = eng.counts(0, recount=True)
+    eng.close()
+    monkeypatch.delenv('SBAYES_B200_SWEEP')
+    eng = make_engine(c)
+    set_golden_state(eng, c)
+    ll2, _, _ = eng.eval()
+    fast = eng.counts(0, recount=True)
+    eng.close()
+    assert rel_err(ll2[0], ll[0]) < 1e-12
+    for k in fast:
+        if fast[k] is not None:
+            assert np.array_equal(fast[k], slow[k]), k
