@@ -33,6 +33,7 @@ struct sb_ctx {
     bool has_data = false, has_priors = false, has_ops = false;
     std::vector<void*> allocs;
     double* partial = nullptr;       // [n_chains][n_tiles]
+    int adj_nnz = 0;                 // entries of the adjacency CSR
     cudaEvent_t direct_done = nullptr;   // last direct (unstaged) upload from page-locked caller memory
     uint8_t* src_scratch = nullptr;      // device scratch of the unstaged source upload ([chains][N][F], unpadded)
     size_t src_scratch_bytes = 0;
@@ -279,6 +280,7 @@ int sb_upload_data(sb_ctx* ctx, const uint8_t* x, const uint8_t* applicable, con
     int *dptr = nullptr, *didx = nullptr;
     if (adj_indptr && adj_indices) {
         const int nnz = adj_indptr[N];
+        ctx->adj_nnz = nnz;
         for (int i = 0; i < nnz; ++i)
             if (adj_indices[i] < 0 || adj_indices[i] >= N) FAIL(SB_E_ARG, "adjacency index out of range");
         DA(dptr, N + 1); DA(didx, nnz);
@@ -944,7 +946,7 @@ static size_t step_smem_base(const StepParams& sp) {
 }
 // Shared work area of the step kernel (one CTA per SM, so up to ~200 KB): the count tables of one 16-feature block
 // of the source sweep; if they do not fit, the sweep falls back to global atomics.
-static size_t step_smem_bytes(const DevData& d, StepParams& sp) {
+static size_t step_smem_bytes(const DevData& d, StepParams& sp, int zone_cap, int adj_nnz) {
     const size_t base = step_smem_base(sp);
     const size_t counts = ((size_t)16 * (d.S + 1) * (1 + d.Z + d.Fam) + 192) * sizeof(int);   // S+1: staged variant
     const size_t room = 160 * 1024 > base ? 160 * 1024 - base : 0;
@@ -954,16 +956,39 @@ static size_t step_smem_bytes(const DevData& d, StepParams& sp) {
     int cap = 2;
     if (const char* env = getenv("SBAYES_B200_SWEEP")) cap = atoi(env);
     if (cap < 1) sp.work_counts = 0;
-    if (!sp.work_counts) return base;
-    // the sweep's parameter tables (w~ [16][12], p_* [1+Z+Fam][16][S+1], f64) behind the counters, if they fit too
-    const size_t par_off = (base + counts + 7) & ~(size_t)7;
-    const size_t params = ((size_t)192 + (size_t)16 * (d.S + 1) * (1 + d.Z + d.Fam)) * sizeof(double);
-    sp.par_off = (int)par_off;
-    if (cap >= 2 && par_off + params <= base + room) {
-        sp.work_counts = 2;
-        return par_off + params;
+    size_t end = base;
+    if (sp.work_counts) {
+        end = base + counts;
+        // the sweep's parameter tables (w~ [16][12], p_* [1+Z+Fam][16][S+1], f64) behind the counters, if they fit too
+        const size_t par_off = (base + counts + 7) & ~(size_t)7;
+        const size_t params = ((size_t)192 + (size_t)16 * (d.S + 1) * (1 + d.Z + d.Fam)) * sizeof(double);
+        sp.par_off = (int)par_off;
+        if (cap >= 2 && par_off + params <= base + room) {
+            sp.work_counts = 2;
+            end = par_off + params;
+        }
     }
-    return base + counts;
+    // Proposal phase of the zone moves on chip: this chain's zone sizes, member lists and zone ids, then the adjacency
+    // CSR ("adjacency rows staged in smem"), each only if it still fits next to the sweep's tables.
+    // SBAYES_B200_ZONE_CACHE=0 disables both (tests).
+    const size_t limit = 200 * 1024;
+    bool allow = true;
+    if (const char* env = getenv("SBAYES_B200_ZONE_CACHE")) allow = atoi(env) != 0;
+    sp.zc_off = -1; sp.adj_off = -1; sp.zc_cap = zone_cap;
+    if (allow && d.Z > 0) {
+        const size_t zc_off = (end + 15) & ~(size_t)15;
+        const size_t zc = (((size_t)d.Z * (1 + zone_cap)) * sizeof(int) + (size_t)d.N + 15) & ~(size_t)15;
+        if (zc_off + zc <= limit) {
+            sp.zc_off = (int)zc_off;
+            end = zc_off + zc;
+            const size_t adj = ((size_t)d.N + 1 + adj_nnz) * sizeof(int);
+            if (d.adj_ptr && end + adj <= limit) {
+                sp.adj_off = (int)end;
+                end += (adj + 15) & ~(size_t)15;
+            }
+        }
+    }
+    return end;
 }
 
 static int ensure_step_scratch(sb_ctx* ctx) {
@@ -1039,7 +1064,7 @@ int sb_set_operators(sb_ctx* ctx, const sb_operator_cfg* cfg, const double* p_gr
     H2D(ctx->d_maxsize, max_size, nc);
     sp.p_grow = ctx->d_pgrow; sp.max_size = ctx->d_maxsize;
     sp.prim_cap = d.geo_type == SB_GEO_COST_BASED ? cap : 0;
-    ctx->step_smem = step_smem_bytes(d, sp);
+    ctx->step_smem = step_smem_bytes(d, sp, cap, ctx->adj_nnz);
     if (ctx->step_smem > 200 * 1024) FAIL(SB_E_ARG, "step kernel scratch exceeds shared memory (N or MAX_M too large)");
     if (ctx->step_smem > 48 * 1024) {
         CK(cudaFuncSetAttribute(mcmc_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->step_smem));
@@ -1097,7 +1122,13 @@ int sb_run(sb_ctx* ctx, int64_t n_steps) {
         attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr;
         cfg.numAttrs = 1;
-        CK(cudaLaunchKernelEx(&cfg, mcmc_step_kernel, ctx->d, ctx->st, ctx->sp, (long long)n_steps));
+        // a state uploaded after sb_set_operators may hold a zone that outgrows the member capacity of the shared
+        // zone cache: such a launch reads the global lists instead
+        StepParams sp = ctx->sp;
+        if (sp.zc_off >= 0 && sp.zc_cap < ctx->d.N)
+            for (int v : ctx->h_zone_size)
+                if (v + 1 > sp.zc_cap) { sp.zc_off = -1; break; }
+        CK(cudaLaunchKernelEx(&cfg, mcmc_step_kernel, ctx->d, ctx->st, sp, (long long)n_steps));
     }
     ++ctx->launches;
     ctx->steps_done += n_steps;

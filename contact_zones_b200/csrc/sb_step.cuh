@@ -52,6 +52,10 @@ struct StepParams {
     int work_counts;          // != 0: resample_all_sources keeps per-feature-block count tables in the work area;
                               // 2: the block's parameter tables are staged behind them as well (par_off)
     int par_off;              // byte offset of the staged parameter tables (8 B aligned)
+    // zone cache of the proposal phase (each CTA of a team keeps its own, identical copy in shared memory):
+    int zc_off;               // byte offset of { int zsize[Z]; int members[Z][zc_cap]; int8 zone_id[N] }, or -1
+    int zc_cap;               // member capacity per zone of the cache (> every max_size)
+    int adj_off;              // byte offset of the adjacency CSR { int ptr[N+1]; int idx[nnz] } in shared memory, or -1
     int* tmp_members;         // [chains][N]     candidate member list for the geo prior
     size_t s_tmp;
 };
@@ -150,8 +154,8 @@ __device__ void build_free_bits(const DevData& d, const int8_t* zone_id, unsigne
 // neighbours of zone z: (adj_mat @ zone) & ~occupied (util.py:139-155).  `skip` (-1 = none) is a member that is
 // treated as already removed (its adjacency does not count and it is itself free) -- the back step of shrink_zone
 // (zone_sampling.py:906-908).
-__device__ void build_nbr_bits(const DevData& d, const int8_t* zone_id, const int* members, int size, int skip,
-                               unsigned* bits, int nwords) {
+__device__ void build_nbr_bits(const int* __restrict__ adj_ptr, const int* __restrict__ adj_idx, const int8_t* zone_id,
+                               const int* members, int size, int skip, unsigned* bits, int nwords) {
     bits_clear(bits, nwords);
     __syncthreads();
     // one warp per member, lanes over its adjacency row
@@ -159,9 +163,9 @@ __device__ void build_nbr_bits(const DevData& d, const int8_t* zone_id, const in
     for (int i = w; i < size; i += nw) {
         const int m = members[i];
         if (m == skip) continue;
-        const int b = d.adj_ptr[m], e = d.adj_ptr[m + 1];
+        const int b = adj_ptr[m], e = adj_ptr[m + 1];
         for (int j = b + lane; j < e; j += 32) {
-            const int n = d.adj_idx[j];
+            const int n = adj_idx[j];
             if (zone_id[n] < 0 || n == skip) atomicOr(&bits[n >> 5], 1u << (n & 31));
         }
     }
@@ -253,6 +257,10 @@ struct Chain {
     int* cg; int* cz; int* cf; int* cs;
     double* ppg; double* ppf;
     int* tmp;
+    // what the PROPOSAL phase of a zone move reads: the shared-memory zone cache if there is one, else the global
+    // arrays (zq_ld = row stride of the member lists); the adjacency CSR from shared memory if it was staged
+    const int8_t* zq; const int* memq; const int* szq; int zq_ld;
+    const int* adj_ptr; const int* adj_idx;
     int* cnt_tab;       // shared-memory count tables of resample_all_sources_blocked, or null
     double* par_tab;    // shared-memory parameter tables of resample_all_sources_staged, or null
     const double2* flt; // shared-memory table of flog()
@@ -270,6 +278,8 @@ __device__ __forceinline__ Chain chain_view(const ChainArrays& st, const StepPar
     k.tmp = sp.tmp_members + c * sp.s_tmp;
     k.cnt_tab = nullptr;
     k.par_tab = nullptr;
+    k.zq = k.zone_id; k.memq = k.members; k.szq = k.zsize; k.zq_ld = 0;   // zq_ld / adjacency set by the kernel
+    k.adj_ptr = nullptr; k.adj_idx = nullptr;
     k.flt = nullptr;
     return k;
 }
@@ -622,13 +632,14 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
     const double rho = sp.p_grow[chain];
     const int max_size = sp.max_size[chain];
     const int z = ahead_int(ua[UA_ZONE * SB_AHEAD], d.Z);
-    const int size = k.zsize[z];
-    int* mem = k.members + (size_t)z * d.N;
+    const int size = k.szq[z];
+    int* mem = k.members + (size_t)z * d.N;                 // global list (written on accept)
+    const int* memq = k.memq + (size_t)z * k.zq_ld;         // the list the proposal reads (shared-memory cache if any)
     if (kind == SB_OP_GROW_ZONE && size >= max_size) return false;        // :818-820
     if (kind == SB_OP_SHRINK_ZONE && size <= sp.min_size) return false;   // :894-896
 
     int n_occ = 0;
-    for (int i = 0; i < d.Z; ++i) n_occ += k.zsize[i];
+    for (int i = 0; i < d.Z; ++i) n_occ += k.szq[i];
     const int n_free = d.N - n_occ;
     int site_new = -1, site_removed = -1;
     double q, q_back;
@@ -636,14 +647,14 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
     PROF_ADD(12, tzp, tz0);
 
     if (kind != SB_OP_SHRINK_ZONE) {
-        build_nbr_bits(d, k.zone_id, mem, size, -1, nbr, sp.nwords);
+        build_nbr_bits(k.adj_ptr, k.adj_idx, k.zq, memq, size, -1, nbr, sp.nwords);
         PROF_T(tz1);
         PROF_ADD(8, tz0, tz1);
         const bool connected = ua[UA_CONNECTED * SB_AHEAD] < rho;                 // :731,823
         // warp 0 counts the neighbourhood and, for a connected step, picks the candidate in the same scan; the
         // other warps meanwhile build the bitmap of free sites if the step is not connected
         bits_select(nbr, sp.nwords, 0, connected ? &sh.pick : &sh.redi[1], &sh.redi[0], ua[UA_SITE_NEW * SB_AHEAD]);
-        if (!connected) build_free_bits(d, k.zone_id, freeb, sp.nwords);
+        if (!connected) build_free_bits(d, k.zq, freeb, sp.nwords);
         __syncthreads();
         const int n_nbr = sh.redi[0];
         PROF_T(tz2);
@@ -659,13 +670,13 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
         if (kind == SB_OP_GROW_ZONE) {
             q_back = 1.0 / (double)(size + 1);                                    // :848
         } else {
-            site_removed = mem[ahead_int(ua[UA_SITE_REMOVED * SB_AHEAD], size)];  // :748-750
+            site_removed = memq[ahead_int(ua[UA_SITE_REMOVED * SB_AHEAD], size)];  // :748-750
             q_back = grow_q(false, n_free, n_nbr, rho);    // old zone's neighbourhood never holds a member (:753,768)
         }
     } else {
-        site_removed = mem[ahead_int(ua[UA_SITE_REMOVED * SB_AHEAD], size)];      // :899-901
+        site_removed = memq[ahead_int(ua[UA_SITE_REMOVED * SB_AHEAD], size)];      // :899-901
         q = 1.0 / (double)size;                                                   // :904
-        build_nbr_bits(d, k.zone_id, mem, size, site_removed, nbr, sp.nwords);    // :906-908
+        build_nbr_bits(k.adj_ptr, k.adj_idx, k.zq, memq, size, site_removed, nbr, sp.nwords);    // :906-908
         bits_select(nbr, sp.nwords, 0, &sh.redi[1], &sh.redi[0], 0.0);            // warp 0: the count only
         __syncthreads();
         const int n_nbr_back = sh.redi[0];
@@ -684,13 +695,13 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
     // prior ratio: only the size and geo terms depend on the zones
     const int new_size = size + (site_new >= 0 ? 1 : 0) - (site_removed >= 0 ? 1 : 0);
     double dprior = 0.0;
-    if (d.size_type != 0) dprior += size_prior_of(d, k.zsize, z, new_size) - size_prior_of(d, k.zsize, -1, 0);
+    if (d.size_type != 0) dprior += size_prior_of(d, k.szq, z, new_size) - size_prior_of(d, k.szq, -1, 0);
     double geo_new = geo;
     if (d.geo_type == 1 && z == d.Z - 1) {
         int m = 0;
         if (threadIdx.x == 0) {
             for (int i = 0; i < size; ++i)
-                if (mem[i] != site_removed) k.tmp[m++] = mem[i];
+                if (memq[i] != site_removed) k.tmp[m++] = memq[i];
             if (site_new >= 0) k.tmp[m++] = site_new;
         }
         __syncthreads();
@@ -713,18 +724,26 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
     // state.  Barrier 1: nobody reads the old zone state any more; rank 0 writes; barrier 2: everybody sees the new one.
     wrote_nothing = false;
     team_sync(tm);
-    if (threadIdx.x == 0 && tm.rank == 0) {
-        if (site_removed >= 0) {
-            int i = 0;
-            while (mem[i] != site_removed) ++i;
-            mem[i] = mem[size - 1];
-            k.zone_id[site_removed] = -1;
+    // the same update on the global state (rank 0) and on this CTA's shared-memory cache (every CTA, so the copies of
+    // a team stay identical without any traffic between them)
+    const bool cached = k.zq != k.zone_id;
+    if (threadIdx.x == 0 && (tm.rank == 0 || cached)) {
+        for (int pass = (tm.rank == 0 ? 0 : 1); pass < (cached ? 2 : 1); ++pass) {
+            int* m_ = pass == 0 ? mem : const_cast<int*>(memq);
+            int8_t* zid_ = pass == 0 ? k.zone_id : const_cast<int8_t*>(k.zq);
+            int* zs_ = pass == 0 ? k.zsize : const_cast<int*>(k.szq);
+            if (site_removed >= 0) {
+                int i = 0;
+                while (m_[i] != site_removed) ++i;
+                m_[i] = m_[size - 1];
+                zid_[site_removed] = -1;
+            }
+            if (site_new >= 0) {
+                m_[new_size - 1] = site_new;
+                zid_[site_new] = (int8_t)z;
+            }
+            zs_[z] = new_size;
         }
-        if (site_new >= 0) {
-            mem[new_size - 1] = site_new;
-            k.zone_id[site_new] = (int8_t)z;
-        }
-        k.zsize[z] = new_size;
     }
     team_sync(tm);
     synced = true;
@@ -1070,6 +1089,29 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
     if (sp.work_counts == 2) kv.par_tab = reinterpret_cast<double*>(step_smem + sp.par_off);
     __shared__ double2 flog_tab[SB_FLOG_N];
     flog_init(flog_tab);
+    kv.zq_ld = d.N;
+    kv.adj_ptr = d.adj_ptr; kv.adj_idx = d.adj_idx;
+    if (sp.zc_off >= 0) {
+        // zone cache: sizes, member lists (first zc_cap entries of every row) and zone ids of this chain
+        int* zs = reinterpret_cast<int*>(step_smem + sp.zc_off);
+        int* zm = zs + d.Z;
+        int8_t* zi = reinterpret_cast<int8_t*>(zm + (size_t)d.Z * sp.zc_cap);
+        for (int i = threadIdx.x; i < d.Z; i += blockDim.x) zs[i] = kv.zsize[i];
+        for (int i = threadIdx.x; i < d.Z * sp.zc_cap; i += blockDim.x) {
+            const int z = i / sp.zc_cap, j = i - z * sp.zc_cap;
+            zm[i] = j < d.N ? kv.members[(size_t)z * d.N + j] : 0;
+        }
+        for (int i = threadIdx.x; i < d.N; i += blockDim.x) zi[i] = kv.zone_id[i];
+        kv.szq = zs; kv.memq = zm; kv.zq = zi; kv.zq_ld = sp.zc_cap;
+    }
+    if (sp.adj_off >= 0) {
+        int* ap = reinterpret_cast<int*>(step_smem + sp.adj_off);
+        int* ai = ap + d.N + 1;
+        for (int i = threadIdx.x; i <= d.N; i += blockDim.x) ap[i] = d.adj_ptr[i];
+        const int nnz = d.adj_ptr[d.N];
+        for (int i = threadIdx.x; i < nnz; i += blockDim.x) ai[i] = d.adj_idx[i];
+        kv.adj_ptr = ap; kv.adj_idx = ai;
+    }
     __syncthreads();
     kv.flt = flog_tab;
     const Chain& k = kv;
@@ -1215,13 +1257,13 @@ move_log_q_kernel(DevData d, ChainArrays st, StepParams sp, int chain, int kind,
     const int n_free = d.N - n_occ;
     double q, q_back;
     if (kind != SB_OP_SHRINK_ZONE) {
-        build_nbr_bits(d, k.zone_id, mem, size, -1, nbr, sp.nwords);
+        build_nbr_bits(d.adj_ptr, d.adj_idx, k.zone_id, mem, size, -1, nbr, sp.nwords);
         const int n_nbr = bits_count(nbr, sp.nwords, sh.redi);
         q = grow_q(bit_test(nbr, site_new), n_free, n_nbr, rho);
         q_back = kind == SB_OP_GROW_ZONE ? 1.0 / (double)(size + 1) : grow_q(false, n_free, n_nbr, rho);
     } else {
         q = 1.0 / (double)size;
-        build_nbr_bits(d, k.zone_id, mem, size, site_removed, nbr, sp.nwords);
+        build_nbr_bits(d.adj_ptr, d.adj_idx, k.zone_id, mem, size, site_removed, nbr, sp.nwords);
         const int n_nbr = bits_count(nbr, sp.nwords, sh.redi);
         q_back = grow_q(bit_test(nbr, site_removed), n_free + 1, n_nbr, rho);
         if (d.warmup) q_back = 1.0 / (double)(size + 1);

@@ -153,3 +153,25 @@ def test_source_sweep_variants_produce_the_same_states(built_lib):
         eng.close()
     finally:
         os.environ.pop('SBAYES_B200_SWEEP', None)
+
+
+@pytest.mark.parametrize('sample_source', [True, False])
+def test_zone_cache_does_not_change_the_trajectory(sample_source, built_lib, monkeypatch):
+    """The proposal phase of the zone moves reads the chain's zone ids / member lists / sizes and the adjacency CSR from
+    shared memory when they fit (every CTA of a team keeps its own copy); SBAYES_B200_ZONE_CACHE=0 reads the global
+    arrays: identical states either way, for teams of 1 and 2, in a zone-move-heavy mix."""
+    c = load_case('D_small')
+    ops = {'shrink_zone': 0.25, 'grow_zone': 0.25, 'swap_zone': 0.2}
+    ops.update({'gibbs_sample_weights': 0.1, 'gibbs_sample_p_zones': 0.2} if sample_source else
+               {'alter_weights': 0.1, 'alter_p_zones': 0.2})
+    monkeypatch.setenv('SBAYES_B200_ZONE_CACHE', '0')
+    ref, ll_ref, pr_ref = _run_chains(c, 2, 0, 400, ops, sample_source, team=1)
+    monkeypatch.delenv('SBAYES_B200_ZONE_CACHE')
+    for team in (1, 2):
+        got, ll, pr = _run_chains(c, 2, 0, 400, ops, sample_source, team=team)
+        assert np.allclose(ll, ll_ref, rtol=1e-10) and np.allclose(pr, pr_ref, rtol=1e-10, atol=1e-10), team
+        for a, b in zip(ref, got):
+            assert np.array_equal(a['zones'], b['zones']), team
+            if sample_source:
+                assert np.array_equal(a['source'], b['source']), team
+    assert not np.array_equal(ref[0]['zones'], c['g']['zones'])            # the zones did move
