@@ -127,36 +127,54 @@ __device__ double lt_correction(const DevData& d, const ChainArrays& st, int cha
                     const double* __restrict__ pzz = pz + (size_t)z * FS + (size_t)fb * S;
                     const double* __restrict__ pff = pf + (size_t)max(fam, 0) * FS + (size_t)fb * S;
                     const double* __restrict__ pgg = pg + (size_t)fb * S;
-                    for (int fi = lane; fi < nfb; fi += 32) {
-                        const int xs = xr[fi];
-                        if (xs == SB_NA) continue;
-                        const double* wr = wn + (size_t)fi * 12;
-                        const int o = fi * S + xs;
-                        const double pgv = pgg[o], pzv = pzz[o];
-                        double mix, vf;
-                        if (fam >= 0) {
-                            const double pfv = pff[o];
-                            mix = wr[9] * pgv + wr[10] * pzv + wr[11] * pfv;       // cfg = 3
-                            vf = wr[6] * pgv + wr[8] * pfv;                          // cfg = 2
-                        } else {
-                            mix = wr[3] * pgv + wr[4] * pzv;                         // cfg = 1
-                            vf = wr[0] * pgv;                                        // cfg = 0
+                    // four feature columns per lane in flight: the state codes first, then the table entries they
+                    // select, then the arithmetic -- two dependent global loads per four cells instead of per cell
+                    for (int fi0 = lane; fi0 < nfb; fi0 += 128) {
+                        int xs4[4];
+                        double pg4[4], pz4[4], pf4[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int fi = fi0 + 32 * u;
+                            xs4[u] = fi < nfb ? (int)xr[fi] : SB_NA;
                         }
-                        const bool vf_ok = __double2hiint(vf) >= LT_TINY_HI;   // else: the main pass skipped the cell
-                        if (__double2hiint(mix) < LT_TINY_HI) {
-                            num.side += log(mix);                                    // exact path (may be -inf)
-                            if (!vf_ok) continue;
-                        } else {
-                            nm *= mix;
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int o = (fi0 + 32 * u) * S + xs4[u];
+                            const bool ok = xs4[u] != SB_NA;
+                            pg4[u] = ok ? pgg[o] : 1.0;
+                            pz4[u] = ok ? pzz[o] : 1.0;
+                            pf4[u] = (ok && fam >= 0) ? pff[o] : 0.0;
                         }
-                        if (vf_ok) dm *= vf;
-                        if (++fill == 8) {                 // factors in [2^-60, 1]: renormalise every 8
-                            fill = 0;
-                            const int h0 = __double2hiint(nm), h1 = __double2hiint(dm);
-                            num.e += ((h0 >> 20) & 0x7ff) - 1023;
-                            den.e += ((h1 >> 20) & 0x7ff) - 1023;
-                            nm = __hiloint2double((h0 & 0x800fffff) | 0x3ff00000, __double2loint(nm));
-                            dm = __hiloint2double((h1 & 0x800fffff) | 0x3ff00000, __double2loint(dm));
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            if (xs4[u] == SB_NA) continue;
+                            const double* wr = wn + (size_t)(fi0 + 32 * u) * 12;
+                            const double pgv = pg4[u], pzv = pz4[u];
+                            double mix, vf;
+                            if (fam >= 0) {
+                                const double pfv = pf4[u];
+                                mix = wr[9] * pgv + wr[10] * pzv + wr[11] * pfv;       // cfg = 3
+                                vf = wr[6] * pgv + wr[8] * pfv;                          // cfg = 2
+                            } else {
+                                mix = wr[3] * pgv + wr[4] * pzv;                         // cfg = 1
+                                vf = wr[0] * pgv;                                        // cfg = 0
+                            }
+                            const bool vf_ok = __double2hiint(vf) >= LT_TINY_HI;   // else: the main pass skipped the cell
+                            if (__double2hiint(mix) < LT_TINY_HI) {
+                                num.side += log(mix);                                    // exact path (may be -inf)
+                                if (!vf_ok) continue;
+                            } else {
+                                nm *= mix;
+                            }
+                            if (vf_ok) dm *= vf;
+                            if (++fill == 8) {                 // factors in [2^-60, 1]: renormalise every 8
+                                fill = 0;
+                                const int h0 = __double2hiint(nm), h1 = __double2hiint(dm);
+                                num.e += ((h0 >> 20) & 0x7ff) - 1023;
+                                den.e += ((h1 >> 20) & 0x7ff) - 1023;
+                                nm = __hiloint2double((h0 & 0x800fffff) | 0x3ff00000, __double2loint(nm));
+                                dm = __hiloint2double((h1 & 0x800fffff) | 0x3ff00000, __double2loint(dm));
+                            }
                         }
                     }
                 }
@@ -177,12 +195,20 @@ lh_table_kernel(DevData d, ChainArrays st, LhTab t, int chain_begin, double* __r
     extern __shared__ __align__(256) unsigned char lt_smem[];
     __shared__ double red[33];
     __shared__ int is_last;
-    const int chain = chain_begin + blockIdx.z;
-    const int split = blockIdx.x, chunk = blockIdx.y;
+    // grid = (group splits, chains, n_corr correction parts + n_chunks feature chunks).  The correction CTAs have the
+    // lowest blockIdx.z, so the block scheduler starts ALL of them first: they carry the longest dependent-load chain,
+    // and placed at the end of every chain's range they were the tail of the launch (108 -> ~95 us at N = 20000)
+    const int n_corr = gridDim.z - t.n_chunks;
+    const int chain = chain_begin + blockIdx.y;
+    const int split = blockIdx.x, chunk = (int)blockIdx.z - n_corr;
     double v;
-    if (chunk >= t.n_chunks) {      // correction CTAs: blockIdx.y = n_chunks .. gridDim.y-1
-        v = lt_correction(d, st, chain, (chunk - t.n_chunks) * gridDim.x + split, (gridDim.y - t.n_chunks) * gridDim.x,
+    if (chunk < 0) {                // correction CTAs: blockIdx.z = 0 .. n_corr-1
+#ifdef LT_NO_CORR
+        v = 0.0;
+#else
+        v = lt_correction(d, st, chain, (int)blockIdx.z * gridDim.x + split, n_corr * gridDim.x,
                           reinterpret_cast<double*>(lt_smem));
+#endif
     } else {
     const int f0 = chunk * t.fc, nf = min(d.F, f0 + t.fc) - f0;
     const int g0 = split * t.gsplit, g1 = min(t.n_groups, g0 + t.gsplit);
@@ -294,22 +320,22 @@ lh_table_kernel(DevData d, ChainArrays st, LhTab t, int chain_begin, double* __r
     v = block_sum(v, red);
 
     // ---- deterministic per-chain reduction: the last CTA of the chain sums the partials in fixed order ---
-    const int n_parts = gridDim.x * gridDim.y;
-    const int part = blockIdx.y * gridDim.x + blockIdx.x;
+    const int n_parts = gridDim.x * gridDim.z;
+    const int part = blockIdx.z * gridDim.x + blockIdx.x;
     if (threadIdx.x == 0) {
-        partial[(size_t)blockIdx.z * n_parts + part] = v;
+        partial[(size_t)blockIdx.y * n_parts + part] = v;
         __threadfence();
-        is_last = atomicAdd(&ticket[blockIdx.z], 1u) == (unsigned)(n_parts - 1);
+        is_last = atomicAdd(&ticket[blockIdx.y], 1u) == (unsigned)(n_parts - 1);
     }
     __syncthreads();
     if (is_last) {
         __threadfence();
         double s = 0.0;
-        for (int i = threadIdx.x; i < n_parts; i += LT_THREADS) s += __ldcg(&partial[(size_t)blockIdx.z * n_parts + i]);
+        for (int i = threadIdx.x; i < n_parts; i += LT_THREADS) s += __ldcg(&partial[(size_t)blockIdx.y * n_parts + i]);
         s = block_sum(s, red);
         if (threadIdx.x == 0) {
             st.ll[chain] = s;
-            ticket[blockIdx.z] = 0u;
+            ticket[blockIdx.y] = 0u;
         }
     }
 }
