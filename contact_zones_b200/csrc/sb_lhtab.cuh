@@ -22,7 +22,10 @@
 #define LT_THREADS 128
 #define LT_ROW 32                      // padded entries per table row (hi words, then lo words: 256 B per row)
 #define LT_CORR_FB 256                 // features per pass of a correction CTA (its w~ rows live in shared memory)
-#define LT_CORR_CTAS 4                 // correction CTAs per (chain, split)
+#ifndef LT_CORR_CTAS
+#define LT_CORR_CTAS 2                 // correction CTAs per (chain, split): every one of them costs a fixed ~10 us of
+                                       // dependent loads; measured 1 / 2 / 4 / 8 / 16 -> 46 / 39 / 44 / 49 / 68 us at N = 500
+#endif
 #define LT_TINY_HI 0x3C300000          // hi word of 2^-60: smaller factors (and 0) take the exact log path
 
 struct LhTab {
@@ -198,15 +201,22 @@ lh_table_kernel(DevData d, ChainArrays st, LhTab t, int chain_begin, double* __r
     // grid = (group splits, chains, n_corr correction parts + n_chunks feature chunks).  The correction CTAs have the
     // lowest blockIdx.z, so the block scheduler starts ALL of them first: they carry the longest dependent-load chain,
     // and placed at the end of every chain's range they were the tail of the launch (108 -> ~95 us at N = 20000)
+    // The parts alternate correction / streaming while both kinds last (z = 0, 2, 4, ... correction), so that the
+    // latency-bound correction CTAs share their SMs with streaming CTAs from the start.
     const int n_corr = gridDim.z - t.n_chunks;
     const int chain = chain_begin + blockIdx.y;
-    const int split = blockIdx.x, chunk = (int)blockIdx.z - n_corr;
+    const int split = blockIdx.x;
+    const int zi = (int)blockIdx.z, m2 = 2 * min(n_corr, t.n_chunks);
+    int corr_idx = -1, chunk = -1;
+    if (zi < m2) { if (zi & 1) chunk = zi >> 1; else corr_idx = zi >> 1; }
+    else if (n_corr > t.n_chunks) corr_idx = (m2 >> 1) + (zi - m2);
+    else chunk = (m2 >> 1) + (zi - m2);
     double v;
-    if (chunk < 0) {                // correction CTAs: blockIdx.z = 0 .. n_corr-1
+    if (chunk < 0) {                // correction CTA
 #ifdef LT_NO_CORR
         v = 0.0;
 #else
-        v = lt_correction(d, st, chain, (int)blockIdx.z * gridDim.x + split, n_corr * gridDim.x,
+        v = lt_correction(d, st, chain, corr_idx * gridDim.x + split, n_corr * gridDim.x,
                           reinterpret_cast<double*>(lt_smem));
 #endif
     } else {
