@@ -1067,11 +1067,14 @@ int sb_set_operators(sb_ctx* ctx, const sb_operator_cfg* cfg, const double* p_gr
     sp.p_grow = ctx->d_pgrow; sp.max_size = ctx->d_maxsize;
     sp.prim_cap = d.geo_type == SB_GEO_COST_BASED ? cap : 0;
     ctx->step_smem = step_smem_bytes(d, sp, cap, ctx->adj_nnz);
+    if (getenv("SBAYES_B200_DEBUG"))
+        fprintf(stderr, "[sbayes_b200] step kernel: smem %zu B (work_off %d counts %d par_off %d zc_off %d zc_cap %d adj_off %d), nwords %d prim_cap %d\n",
+                ctx->step_smem, sp.work_off, sp.work_counts, sp.par_off, sp.zc_off, sp.zc_cap, sp.adj_off, sp.nwords, sp.prim_cap);
     if (ctx->step_smem > 200 * 1024) FAIL(SB_E_ARG, "step kernel scratch exceeds shared memory (N or MAX_M too large)");
-    if (ctx->step_smem > 48 * 1024) {
-        CK(cudaFuncSetAttribute(mcmc_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->step_smem));
-        CK(cudaFuncSetAttribute(move_log_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->step_smem));
-    }
+    // always opt in: the 48 KB default limit applies to static + dynamic shared memory together, and the kernel's
+    // static part (look-ahead tables, reduction scratch, flog table) is ~14 KB
+    CK(cudaFuncSetAttribute(mcmc_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->step_smem));
+    CK(cudaFuncSetAttribute(move_log_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->step_smem));
     // team (thread-block cluster) size: as many CTAs per chain as the SM count allows, each with at least one
     // 16-feature block of work; SBAYES_B200_TEAM overrides (1, 2, 4 or 8)
     {
@@ -1184,8 +1187,7 @@ int sb_move_log_q(sb_ctx* ctx, int chain, int kind, int zone, int site_new, int 
     r = ensure_step_scratch(ctx);
     if (r != SB_OK) return r;
     const size_t smem = step_smem_base(ctx->sp);
-    if (smem > 48 * 1024)
-        CK(cudaFuncSetAttribute(move_log_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CK(cudaFuncSetAttribute(move_log_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     double* dout;
     CK(cudaMalloc((void**)&dout, 2 * sizeof(double)));
     move_log_q_kernel<<<1, STEP_THREADS, smem, ctx->stream>>>(d, ctx->st, ctx->sp, chain, kind, zone, site_new,

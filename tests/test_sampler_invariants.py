@@ -175,3 +175,42 @@ def test_zone_cache_does_not_change_the_trajectory(sample_source, built_lib, mon
             if sample_source:
                 assert np.array_equal(a['source'], b['source']), team
     assert not np.array_equal(ref[0]['zones'], c['g']['zones'])            # the zones did move
+
+
+@pytest.mark.parametrize('sample_source', [True, False])
+def test_large_site_count_keeps_running_values_exact(sample_source, built_lib):
+    """20000 sites (configs[4]'s largest shape): the adjacency CSR no longer fits in shared memory (the zone cache
+    does), teams of 8 CTAs per chain, 1250 groups in the likelihood tables.  Running ll / prior / counts == a
+    from-scratch evaluation after a zone-move-heavy mix, zones stay disjoint and within their size bounds."""
+    from contact_zones_b200 import synthetic
+    from contact_zones_b200.engine import Engine, state_index
+    n, f, s_, z = 20000, 32, 4, 4
+    data = synthetic.make_data(n, f, s_, n_families=3, seed=5, with_dist=False, planted_zones=z, planted_size=15)
+    eng = Engine(state_index(data.features), data.states, data.families, data.network['adj_mat'], None, n_zones=z,
+                 n_chains=3, inheritance=True, sample_source=sample_source)
+    for ch in range(3):
+        st = synthetic.random_state(data, z, 8, True, sample_source, seed=20 + ch)
+        eng.set_state(ch, st['zones'], st['weights'], st['p_global'], st['p_zones'], st['p_families'],
+                      np.argmax(st['source'], -1) if sample_source else None)
+    eng.eval()
+    ops = {'shrink_zone': 0.2, 'grow_zone': 0.3, 'swap_zone': 0.2}
+    ops.update({'gibbs_sample_weights': 0.1, 'gibbs_sample_p_zones': 0.1, 'gibbs_sample_p_global': 0.05,
+                'gibbs_sample_p_families': 0.05} if sample_source else
+               {'alter_weights': 0.1, 'alter_p_zones': 0.1, 'alter_p_global': 0.05, 'alter_p_families': 0.05})
+    eng.set_operators(ops, PRECISION, min_size=3, max_size=40, p_grow_connected=0.85, seed=9)
+    eng.run(300)
+    ll_run, pr_run = eng.chain_scalars()
+    cnt_run = [eng.counts(ch, recount=False) for ch in range(3)] if sample_source else None
+    ll_new, pr_new, _ = eng.eval()
+    assert np.allclose(ll_run, ll_new, rtol=1e-9) and np.allclose(pr_run, pr_new, rtol=1e-9, atol=1e-9)
+    acc, _ = eng.op_stats()
+    assert acc[:, :3].sum() > 0                                            # zone moves were accepted
+    for ch in range(3):
+        zz = eng.get_state(ch, fields=('zones',))['zones']
+        assert (zz.sum(axis=0) <= 1).all() and (zz.sum(axis=1) >= 3).all() and (zz.sum(axis=1) <= 40).all()
+        if sample_source:
+            new = eng.counts(ch, recount=True)
+            for k in new:
+                if new[k] is not None:
+                    assert np.array_equal(cnt_run[ch][k], new[k]), (ch, k)
+    eng.close()
