@@ -756,7 +756,9 @@ int sb_copy_state(sb_ctx* ctx, int dst, int src) {
 // ---------------------------------------------------------------------------------------------
 static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source) {
     const DevData& d = ctx->d;
-    if (!use_source) {      // table-driven K1: one launch (weights normalisation and the per-chain reduction are fused)
+    // table-driven K1: one launch (weights normalisation and the per-chain reduction are fused).  Its table rows hold
+    // 32 codes, i.e. S + 1 <= 32 digits: S = 32 (SB_MAX_S) takes the tile-per-site kernel below
+    if (!use_source && d.S + 1 <= LT_ROW) {
         LhTab t = ctx->lt;
         // grid = (group splits, feature chunks, chains).  Every CTA pays a fixed latency chain (tables, zone-member
         // correction, reduction); measured best on B200 (scripts/gpu_k1_sweep.sh) at about two waves of
@@ -798,7 +800,7 @@ static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source
     dim3 gw((d.F + 127) / 128, n);
     wnorm_kernel<<<gw, 128, 0, ctx->stream>>>(d, ctx->st, chain_begin);
     const size_t lb_smem = lh_source_block_smem(d.S, d.Z, d.Fam);
-    if (lb_smem <= 200 * 1024 && blocked_kernels_allowed()) {
+    if (use_source && lb_smem <= 200 * 1024 && blocked_kernels_allowed()) {
         // blocked form: parameter tables of a 16-feature block staged in shared memory
         const int nb = d.ldx >> 4;
         if (lb_smem > 48 * 1024)
@@ -809,10 +811,15 @@ static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source
         CK(cudaGetLastError());
         return SB_OK;
     }
-    // fallback (tables of a feature block exceed shared memory): one CTA per (site tile, chain), global gathers
+    // fallbacks (with source: tables of a feature block exceed shared memory; source-free: S = 32): one CTA per
+    // (site tile, chain), global gathers
     dim3 grid(ctx->n_tiles, n);
-    lh_full_kernel<1><<<grid, LH_THREADS, 0, ctx->stream>>>(d, ctx->st, chain_begin, ctx->sites_per_tile, ctx->partial,
-                                                           ctx->n_tiles);
+    if (use_source)
+        lh_full_kernel<1><<<grid, LH_THREADS, 0, ctx->stream>>>(d, ctx->st, chain_begin, ctx->sites_per_tile, ctx->partial,
+                                                               ctx->n_tiles);
+    else
+        lh_full_kernel<0><<<grid, LH_THREADS, 0, ctx->stream>>>(d, ctx->st, chain_begin, ctx->sites_per_tile, ctx->partial,
+                                                               ctx->n_tiles);
     lh_reduce_kernel<<<n, 32, 0, ctx->stream>>>(ctx->partial, ctx->n_tiles, ctx->st.ll, chain_begin);
     ctx->launches += 3;
     CK(cudaGetLastError());

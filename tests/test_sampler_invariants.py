@@ -214,3 +214,68 @@ def test_large_site_count_keeps_running_values_exact(sample_source, built_lib):
                 if new[k] is not None:
                     assert np.array_equal(cnt_run[ch][k], new[k]), (ch, k)
     eng.close()
+
+
+ODD_SHAPES = {
+    # name: (N, F, S, Fam, Z, zone_size, ragged, max_size)
+    'tiny': (12, 3, 2, 0, 1, 3, False, 12),                  # max_size = N, one zone, two weights (C = 2)
+    'max_states': (150, 20, 32, 2, 2, 5, True, 30),          # S = SB_MAX_S, ragged state counts
+    'many_families': (400, 24, 8, 120, 3, 6, False, 30),     # the sweep's tables exceed shared memory: fallbacks
+    'one_feature_block': (200, 16, 5, 4, 7, 4, True, 20),    # F = 16: a single feature block, teams stay at 1
+    'wide': (120, 530, 3, 3, 2, 6, False, 25),               # F > 256 (several correction passes in K1), F % 16 != 0
+}
+
+
+@pytest.mark.parametrize('shape', sorted(ODD_SHAPES))
+@pytest.mark.parametrize('sample_source', [True, False])
+def test_odd_shapes_keep_running_values_exact(shape, sample_source, built_lib):
+    """Corners of the shape space through the whole sampler: running ll / prior / count tables == from-scratch values,
+    zones disjoint and within bounds, every launch succeeds (shared-memory layouts, fallbacks, team sizes)."""
+    from contact_zones_b200 import synthetic
+    from contact_zones_b200.engine import Engine, state_index
+    n, f, s_, fam, z, zs, ragged, max_size = ODD_SHAPES[shape]
+    inh = fam > 0
+    data = synthetic.make_data(n, f, s_, n_families=fam, seed=3, with_dist=False, ragged_states=ragged, na_frac=0.05)
+    n_chains = 3
+    eng = Engine(state_index(data.features), data.states, data.families if inh else None, data.network['adj_mat'], None,
+                 n_zones=z, n_chains=n_chains, inheritance=inh, sample_source=sample_source)
+    for ch in range(n_chains):
+        st = synthetic.random_state(data, z, zs, inh, sample_source, seed=40 + ch)
+        eng.set_state(ch, st['zones'], st['weights'], st['p_global'], st['p_zones'], st['p_families'] if inh else None,
+                      np.argmax(st['source'], -1) if sample_source else None)
+    # the evaluation kernels against the oracle on the last uploaded state (chain n_chains - 1)
+    import sbayes_oracle as orc
+    fam_b = np.asarray(data.families, bool)
+    args = (data.features, fam_b, inh, st['zones'], st['weights'], st['p_global'], st['p_zones'],
+            st['p_families'] if inh else None)
+    ll_free = eng.eval(use_source=False)[0][n_chains - 1]
+    ref_free = orc.log_likelihood(*args, source=None)
+    assert abs(ll_free - ref_free) <= 1e-9 * abs(ref_free), (ll_free, ref_free)
+    if sample_source:
+        ll_src = eng.eval(use_source=True)[0][n_chains - 1]
+        ref_src = orc.log_likelihood(*args, source=st['source'])
+        assert abs(ll_src - ref_src) <= 1e-9 * abs(ref_src), (ll_src, ref_src)
+    eng.eval()
+    ops = {'shrink_zone': 0.15, 'grow_zone': 0.2, 'swap_zone': 0.15}
+    gib = {'gibbs_sample_weights': 0.15, 'gibbs_sample_p_zones': 0.15, 'gibbs_sample_p_global': 0.1,
+           'gibbs_sample_p_families': 0.05, 'gibbs_sample_sources': 0.05}
+    alt = {'alter_weights': 0.15, 'alter_p_zones': 0.15, 'alter_p_global': 0.1, 'alter_p_families': 0.1}
+    ops.update({k: v for k, v in (gib if sample_source else alt).items() if inh or 'families' not in k})
+    eng.set_operators(ops, PRECISION, min_size=3, max_size=max_size, p_grow_connected=0.85, seed=13)
+    for _ in range(2):
+        eng.run(250)
+        ll_run, pr_run = eng.chain_scalars()
+        cnt_run = [eng.counts(ch, recount=False) for ch in range(n_chains)] if sample_source else None
+        ll_new, pr_new, _ = eng.eval()
+        assert np.all(np.isfinite(ll_new)), ll_new
+        assert np.allclose(ll_run, ll_new, rtol=1e-9), (ll_run, ll_new)
+        assert np.allclose(pr_run, pr_new, rtol=1e-9, atol=1e-9), (pr_run, pr_new)
+        for ch in range(n_chains):
+            zz = eng.get_state(ch, fields=('zones',))['zones']
+            assert (zz.sum(axis=0) <= 1).all() and (zz.sum(axis=1) >= 3).all() and (zz.sum(axis=1) <= max_size).all()
+            if sample_source:
+                new = eng.counts(ch, recount=True)
+                for k in new:
+                    if new[k] is not None:
+                        assert np.array_equal(cnt_run[ch][k], new[k]), (ch, k)
+    eng.close()
