@@ -3,7 +3,7 @@
 * every operator on its own keeps the incrementally maintained log-likelihood / log-prior / count tables equal to a
   from-scratch evaluation (K1, K2, K3, K4) and the zone book-keeping consistent (disjoint zones, MIN_M <= size <= MAX_M);
 * a chain's trajectory depends on (seed, global chain id) only -- not on how chains are sharded over contexts;
-* teams of 1, 2 and 4 CTAs per chain (thread-block clusters) walk the same trajectory: the team size only changes the
+* teams of 1, 2, 4 and 8 CTAs per chain (thread-block clusters) walk the same trajectory: the team size only changes the
   order of fp64 partial sums (1e-16 relative), which cannot flip an accept decision within a few hundred steps."""
 import os
 
@@ -116,7 +116,7 @@ def test_team_sizes_walk_the_same_trajectory(sample_source, built_lib):
     ops = MIX if sample_source else {'shrink_zone': 0.1, 'grow_zone': 0.1, 'swap_zone': 0.05, 'alter_weights': 0.3,
                                      'alter_p_global': 0.1, 'alter_p_zones': 0.25, 'alter_p_families': 0.1}
     ref, ll_ref, pr_ref = _run_chains(c, 2, 0, 300, ops, sample_source, team=1)
-    for team in (2, 4):
+    for team in (2, 4, 8):
         got, ll, pr = _run_chains(c, 2, 0, 300, ops, sample_source, team=team)
         assert np.allclose(ll, ll_ref, rtol=1e-10) and np.allclose(pr, pr_ref, rtol=1e-10, atol=1e-10), team
         for a, b in zip(ref, got):
@@ -278,4 +278,27 @@ def test_odd_shapes_keep_running_values_exact(shape, sample_source, built_lib):
                 for k in new:
                     if new[k] is not None:
                         assert np.array_equal(cnt_run[ch][k], new[k]), (ch, k)
+    eng.close()
+
+
+def test_more_chains_than_sms(built_lib):
+    """200 chains on 148 SMs: one CTA per chain, the launch runs in two waves of persistent CTAs; every chain keeps
+    its running values consistent and chains with different global ids differ."""
+    c = load_case('B_balkan_like')
+    n_chains = 200
+    eng = make_engine(c, n_chains=n_chains, sample_source=True)
+    for ch in range(n_chains):
+        set_golden_state(eng, c, ch)
+    eng.eval()
+    eng.set_operators(MIX, PRECISION, min_size=3, max_size=20, p_grow_connected=0.85, seed=5)
+    eng.run(200)
+    ll_run, pr_run = eng.chain_scalars()
+    ll_new, pr_new, _ = eng.eval()
+    assert np.allclose(ll_run, ll_new, rtol=1e-9) and np.allclose(pr_run, pr_new, rtol=1e-9, atol=1e-9)
+    assert len(set(np.round(ll_run, 6))) > n_chains // 2
+    for ch in (0, 147, 148, 199):
+        a, b = eng.counts(ch, recount=False), eng.counts(ch, recount=True)
+        for k in a:
+            if a[k] is not None:
+                assert np.array_equal(a[k], b[k]), (ch, k)
     eng.close()
