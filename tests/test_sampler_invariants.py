@@ -302,3 +302,47 @@ def test_more_chains_than_sms(built_lib):
             if a[k] is not None:
                 assert np.array_equal(a[k], b[k]), (ch, k)
     eng.close()
+
+
+@pytest.mark.parametrize('shape', ['tiny', 'many_families', 'wide'])
+@pytest.mark.parametrize('sample_source', [True, False])
+def test_warmup_mode_on_odd_shapes(shape, sample_source, built_lib):
+    """Warm-up variant of the operators (zone_sampling.py:1272-1577: per-chain max_size / p_grow_connected, forced
+    accepts of the source moves, quirk Q3) on corner shapes: every accepted zone move pays the source sweep and the
+    zone-cache update, so this is the densest exercise of both; running values == from-scratch values."""
+    from contact_zones_b200 import synthetic
+    from contact_zones_b200.engine import Engine, state_index
+    n, f, s_, fam, z, zs, ragged, max_size = ODD_SHAPES[shape]
+    inh = fam > 0
+    data = synthetic.make_data(n, f, s_, n_families=fam, seed=3, with_dist=False, ragged_states=ragged, na_frac=0.05)
+    n_chains = 4
+    eng = Engine(state_index(data.features), data.states, data.families if inh else None, data.network['adj_mat'], None,
+                 n_zones=z, n_chains=n_chains, inheritance=inh, sample_source=sample_source, warmup=True)
+    for ch in range(n_chains):
+        st = synthetic.random_state(data, z, zs, inh, sample_source, seed=60 + ch)
+        eng.set_state(ch, st['zones'], st['weights'], st['p_global'], st['p_zones'], st['p_families'] if inh else None,
+                      np.argmax(st['source'], -1) if sample_source else None)
+    eng.eval()
+    ops = {'shrink_zone': 0.2, 'grow_zone': 0.25, 'swap_zone': 0.15}
+    ops.update({'gibbs_sample_weights': 0.2, 'gibbs_sample_p_zones': 0.2} if sample_source else
+               {'alter_weights': 0.2, 'alter_p_zones': 0.2})
+    sizes = np.linspace(max(4, (zs + max_size) // 4), max_size, n_chains).astype(np.int32)       # util.py:1182-1199
+    eng.set_operators(ops, PRECISION, min_size=3, max_size=sizes, p_grow_connected=[0.95, 0.85, 0.95, 0.85], seed=21)
+    eng.run(300)
+    ll_run, pr_run = eng.chain_scalars()
+    cnt_run = [eng.counts(ch, recount=False) for ch in range(n_chains)] if sample_source else None
+    ll_new, pr_new, _ = eng.eval()
+    assert np.all(np.isfinite(ll_new))
+    assert np.allclose(ll_run, ll_new, rtol=1e-9) and np.allclose(pr_run, pr_new, rtol=1e-9, atol=1e-9)
+    acc, rej = eng.op_stats()
+    assert acc[:, :3].sum() > 0
+    for ch in range(n_chains):
+        zz = eng.get_state(ch, fields=('zones',))['zones']
+        assert (zz.sum(axis=0) <= 1).all() and (zz.sum(axis=1) >= 3).all()
+        assert (zz.sum(axis=1) <= max(int(sizes[ch]), zs)).all(), (ch, zz.sum(axis=1), sizes)
+        if sample_source:
+            new = eng.counts(ch, recount=True)
+            for k in new:
+                if new[k] is not None:
+                    assert np.array_equal(cnt_run[ch][k], new[k]), (ch, k)
+    eng.close()
