@@ -1081,7 +1081,7 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
     Team tm = {(int)(blockIdx.x % sp.team), sp.team, 0u, 31 - __clz(sp.team)};
     unsigned* nbr = reinterpret_cast<unsigned*>(step_smem);
     unsigned* freeb = nbr + sp.nwords;
-    double* prim_key = reinterpret_cast<double*>(freeb + sp.nwords + (sp.nwords & 1));
+    double* prim_key = reinterpret_cast<double*>(freeb + sp.nwords);       // 2 * nwords words from the start: 8 B aligned
     unsigned char* prim_tree = reinterpret_cast<unsigned char*>(prim_key + sp.prim_cap);
 
     Chain kv = chain_view(st, sp, chain);

@@ -346,3 +346,56 @@ def test_warmup_mode_on_odd_shapes(shape, sample_source, built_lib):
                 if new[k] is not None:
                     assert np.array_equal(cnt_run[ch][k], new[k]), (ch, k)
     eng.close()
+
+
+@pytest.mark.parametrize('shape', ['tiny', 'max_states', 'one_feature_block'])
+@pytest.mark.parametrize('sample_source', [True, False])
+def test_informative_priors_on_odd_shapes(shape, sample_source, built_lib):
+    """Cost-based geo prior (Prim MST over the last zone, K3), uniform size prior and count-based Dirichlet priors on
+    corner shapes: the prior of the uploaded state matches the oracle, and after a run the incrementally maintained
+    prior (size + geo + Dirichlet caches) equals a from-scratch evaluation."""
+    import sbayes_oracle as orc
+    from contact_zones_b200 import synthetic
+    from contact_zones_b200.engine import Engine, state_index
+    n, f, s_, fam, z, zs, ragged, max_size = ODD_SHAPES[shape]
+    inh = fam > 0
+    data = synthetic.make_data(n, f, s_, n_families=fam, seed=3, with_dist=True, ragged_states=ragged, na_frac=0.05,
+                               counts_prior=True)
+    gibbs_g, alpha_g = orc.dirichlet_prior_tables(np.array(data.prior_universal['counts'], float), 10.)
+    gibbs_f = alpha_f = None
+    if inh:
+        gibbs_f, alpha_f = orc.dirichlet_prior_tables(np.array(data.prior_inheritance['counts'], float), 10.)
+    cost = data.geo_prior['cost_matrix']
+    n_chains = 2
+    eng = Engine(state_index(data.features), data.states, data.families if inh else None, data.network['adj_mat'], cost,
+                 n_zones=z, n_chains=n_chains, inheritance=inh, sample_source=sample_source)
+    eng.set_priors(size_type='uniform', geo_type='cost_based', geo_scale=120.0, p_global_type='counts',
+                   p_families_type='counts' if inh else 'uniform', gibbs_counts_global=gibbs_g, alpha_global=alpha_g,
+                   gibbs_counts_fam=gibbs_f, alpha_fam=alpha_f)
+    for ch in range(n_chains):
+        st = synthetic.random_state(data, z, zs, inh, sample_source, seed=80 + ch)
+        eng.set_state(ch, st['zones'], st['weights'], st['p_global'], st['p_zones'], st['p_families'] if inh else None,
+                      np.argmax(st['source'], -1) if sample_source else None)
+    _, prior, _ = eng.eval()
+    cfg = {'geo': {'type': 'cost_based', 'scale': 120.0}, 'area_size': {'type': 'uniform'}, 'weights': {'type': 'uniform'},
+           'contact': {'type': 'uniform'}, 'universal': {'type': 'counts'},
+           'inheritance': {'type': 'counts' if inh else 'uniform'}}
+    ref = orc.log_prior(st['zones'], st['p_global'], st['p_families'] if inh else None, data.states, inh, cfg,
+                        cost_mat=cost, alpha_global=alpha_g, alpha_families=alpha_f)
+    assert abs(prior[n_chains - 1] - ref) <= 1e-9 * max(1.0, abs(ref)), (prior, ref)
+    ops = {'shrink_zone': 0.15, 'grow_zone': 0.2, 'swap_zone': 0.15}
+    gib = {'gibbs_sample_weights': 0.1, 'gibbs_sample_p_zones': 0.1, 'gibbs_sample_p_global': 0.2,
+           'gibbs_sample_p_families': 0.1}
+    alt = {'alter_weights': 0.1, 'alter_p_zones': 0.1, 'alter_p_global': 0.2, 'alter_p_families': 0.1}
+    ops.update({k: v for k, v in (gib if sample_source else alt).items() if inh or 'families' not in k})
+    eng.set_operators(ops, PRECISION, min_size=3, max_size=max_size, p_grow_connected=0.85, seed=31)
+    eng.run(400)
+    ll_run, pr_run = eng.chain_scalars()
+    ll_new, pr_new, _ = eng.eval()
+    assert np.allclose(ll_run, ll_new, rtol=1e-9), (ll_run, ll_new)
+    assert np.allclose(pr_run, pr_new, rtol=1e-9, atol=1e-9), (pr_run, pr_new)
+    s1 = eng.get_state(n_chains - 1, one_hot_source=False)
+    ref = orc.log_prior(s1['zones'].astype(bool), s1['p_global'], s1['p_families'] if inh else None, data.states, inh, cfg,
+                        cost_mat=cost, alpha_global=alpha_g, alpha_families=alpha_f)
+    assert abs(pr_new[n_chains - 1] - ref) <= 1e-9 * max(1.0, abs(ref)), (pr_new, ref)
+    eng.close()
