@@ -399,3 +399,44 @@ def test_informative_priors_on_odd_shapes(shape, sample_source, built_lib):
                         cost_mat=cost, alpha_global=alpha_g, alpha_families=alpha_f)
     assert abs(pr_new[n_chains - 1] - ref) <= 1e-9 * max(1.0, abs(ref)), (pr_new, ref)
     eng.close()
+
+
+@pytest.mark.parametrize('n_chains,inheritance,p_grow', [(1, True, 0.85), (2, True, 1.0), (3, False, 0.0)])
+def test_bench_shape_with_few_chains(n_chains, inheritance, p_grow, built_lib):
+    """The benchmark shape (2000 x 200 x 8, 7 zones, 20 families) with 1-3 chains: the automatic team size is 8 CTAs per
+    chain (a whole GPC per chain); also without families (two mixture components) and with p_grow_connected at its
+    extremes.  Running values == from-scratch values, count tables bit-exact, likelihood == oracle."""
+    import sbayes_oracle as orc
+    from contact_zones_b200 import synthetic
+    from contact_zones_b200.engine import Engine, state_index
+    data = synthetic.make_data(2000, 200, 8, n_families=20 if inheritance else 0, seed=0, with_dist=False,
+                               planted_zones=7, planted_size=20)
+    eng = Engine(state_index(data.features), data.states, data.families if inheritance else None,
+                 data.network['adj_mat'], None, n_zones=7, n_chains=n_chains, inheritance=inheritance, sample_source=True)
+    for ch in range(n_chains):
+        st = synthetic.random_state(data, 7, 5, inheritance, True, seed=100 + ch)
+        eng.set_state(ch, st['zones'], st['weights'], st['p_global'], st['p_zones'],
+                      st['p_families'] if inheritance else None, np.argmax(st['source'], -1))
+    ops = {'shrink_zone': 0.1, 'grow_zone': 0.1, 'swap_zone': 0.05, 'gibbs_sample_weights': 0.3,
+           'gibbs_sample_p_global': 0.1, 'gibbs_sample_p_zones': 0.25}
+    if inheritance:
+        ops['gibbs_sample_p_families'] = 0.1
+    eng.eval()
+    eng.set_operators(ops, PRECISION, min_size=3, max_size=50, p_grow_connected=p_grow, seed=3)
+    eng.run(500)
+    ll_run, pr_run = eng.chain_scalars()
+    cnt_run = eng.counts(n_chains - 1, recount=False)
+    ll_new, pr_new, _ = eng.eval()
+    assert np.allclose(ll_run, ll_new, rtol=1e-9) and np.allclose(pr_run, pr_new, rtol=1e-9, atol=1e-9)
+    cnt_new = eng.counts(n_chains - 1, recount=True)
+    for k in cnt_new:
+        if cnt_new[k] is not None:
+            assert np.array_equal(cnt_run[k], cnt_new[k]), k
+    s1 = eng.get_state(n_chains - 1)
+    ref = orc.log_likelihood(data.features, np.asarray(data.families, bool), inheritance, s1['zones'].astype(bool),
+                             s1['weights'], s1['p_global'], s1['p_zones'], s1['p_families'] if inheritance else None,
+                             source=s1['source'].astype(bool))
+    assert abs(ll_new[n_chains - 1] - ref) <= 1e-9 * abs(ref), (ll_new, ref)
+    acc, _ = eng.op_stats()
+    assert acc[:, :3].sum() > 0
+    eng.close()
