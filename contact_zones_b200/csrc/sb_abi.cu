@@ -777,7 +777,9 @@ static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source
         }
         t.fc = std::max(1, (d.F + chunks - 1) / chunks);
         while (t.fc > 1 && lt_smem_bytes(t.fc, t.max_cls, d.S) > 46 * 1024) --t.fc;
-        if (lt_smem_bytes(t.fc, t.max_cls, d.S) > 46 * 1024) FAIL(SB_E_ARG, "K1 tables exceed shared memory (too many families)");
+        // (hundreds of family classes in one split: even one feature's rows do not fit -> tile-per-site kernel below)
+        const bool tables_fit = lt_smem_bytes(t.fc, t.max_cls, d.S) <= 46 * 1024;
+        if (tables_fit) {
         t.n_chunks = (d.F + t.fc - 1) / t.fc;
         t.smem = std::max(lt_smem_bytes(t.fc, t.max_cls, d.S), (size_t)std::min(d.F, LT_CORR_FB) * 12 * sizeof(double));
         // blockIdx.z < n_corr: correction CTAs (zone members), scheduled first, concurrent with the streaming CTAs
@@ -796,6 +798,7 @@ static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source
         ++ctx->launches;
         CK(cudaGetLastError());
         return SB_OK;
+        }
     }
     dim3 gw((d.F + 127) / 128, n);
     wnorm_kernel<<<gw, 128, 0, ctx->stream>>>(d, ctx->st, chain_begin);
@@ -811,8 +814,8 @@ static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source
         CK(cudaGetLastError());
         return SB_OK;
     }
-    // fallbacks (with source: tables of a feature block exceed shared memory; source-free: S = 32): one CTA per
-    // (site tile, chain), global gathers
+    // fallbacks (with source: tables of a feature block exceed shared memory; source-free: S = 32 or too many family
+    // classes for K1's tables): one CTA per (site tile, chain), global gathers
     dim3 grid(ctx->n_tiles, n);
     if (use_source)
         lh_full_kernel<1><<<grid, LH_THREADS, 0, ctx->stream>>>(d, ctx->st, chain_begin, ctx->sites_per_tile, ctx->partial,

@@ -222,6 +222,7 @@ ODD_SHAPES = {
     'max_states': (150, 20, 32, 2, 2, 5, True, 30),          # S = SB_MAX_S, ragged state counts
     'many_families': (400, 24, 8, 120, 3, 6, False, 30),     # the sweep's tables exceed shared memory: fallbacks
     'one_feature_block': (200, 16, 5, 4, 7, 4, True, 20),    # F = 16: a single feature block, teams stay at 1
+    'hundreds_of_families': (1500, 20, 6, 700, 2, 5, False, 20),   # no shared-memory table fits: every fallback kernel
     'wide': (120, 530, 3, 3, 2, 6, False, 25),               # F > 256 (several correction passes in K1), F % 16 != 0
 }
 
