@@ -441,3 +441,83 @@ def test_bench_shape_with_few_chains(n_chains, inheritance, p_grow, built_lib):
     acc, _ = eng.op_stats()
     assert acc[:, :3].sum() > 0
     eng.close()
+
+
+@pytest.mark.parametrize('seed', range(int(os.environ.get('SB_FUZZ_SEEDS', '24'))))     # more seeds: SB_FUZZ_SEEDS=400
+def test_random_shapes(seed, built_lib):
+    """Seeded random shapes, priors and operator mixes (5..600 sites, 1..70 features, 2..12 states, 0..12 families,
+    1..5 zones, both sampler modes, warm-up on / off, cost-based geo / size / count priors on / off): likelihood and
+    prior of the uploaded state == oracle, running values == from-scratch values after a run."""
+    import sbayes_oracle as orc
+    from contact_zones_b200 import synthetic
+    from contact_zones_b200.engine import Engine, state_index
+    rng = np.random.default_rng(1000 + seed)
+    z = int(rng.integers(1, 6))
+    zs = int(rng.integers(3, 7))
+    n = int(rng.integers(max(5, z * zs + 2), 600))
+    f, s_ = int(rng.integers(1, 71)), int(rng.integers(2, 13))
+    fam = int(rng.integers(0, 13)) if n > 30 else 0
+    inh = fam > 0
+    sample_source, warmup = bool(rng.integers(0, 2)), bool(rng.integers(0, 4) == 0)
+    geo, size = bool(rng.integers(0, 2)), ['none', 'uniform', 'quadratic'][int(rng.integers(0, 3))]
+    counts = bool(rng.integers(0, 2))
+    data = synthetic.make_data(n, f, s_, n_families=fam, seed=seed, with_dist=True, ragged_states=bool(rng.integers(0, 2)),
+                               na_frac=float(rng.choice([0.0, 0.05, 0.3])), counts_prior=counts)
+    cost = data.geo_prior['cost_matrix'] if geo else None
+    n_chains = int(rng.integers(1, 5))
+    try:
+        states = [synthetic.random_state(data, z, zs, inh, sample_source, seed=seed * 10 + ch) for ch in range(n_chains)]
+    except ValueError:
+        pytest.skip('could not place the random zones')
+    eng = Engine(state_index(data.features), data.states, data.families if inh else None, data.network['adj_mat'], cost,
+                 n_zones=z, n_chains=n_chains, inheritance=inh, sample_source=sample_source, warmup=warmup)
+    gg = ag = gf = af = None
+    if counts:
+        gg, ag = orc.dirichlet_prior_tables(np.array(data.prior_universal['counts'], float), 10.)
+        if inh:
+            gf, af = orc.dirichlet_prior_tables(np.array(data.prior_inheritance['counts'], float), 10.)
+    scale = float(rng.uniform(20, 300))
+    eng.set_priors(size_type=size, geo_type='cost_based' if geo else 'uniform', geo_scale=scale,
+                   p_global_type='counts' if counts else 'uniform', p_families_type='counts' if (counts and inh) else 'uniform',
+                   gibbs_counts_global=gg, alpha_global=ag, gibbs_counts_fam=gf, alpha_fam=af)
+    for ch, st in enumerate(states):
+        eng.set_state(ch, st['zones'], st['weights'], st['p_global'], st['p_zones'], st['p_families'] if inh else None,
+                      np.argmax(st['source'], -1) if sample_source else None)
+    st = states[-1]
+    ll, prior, _ = eng.eval()
+    args = (data.features, np.asarray(data.families, bool), inh, st['zones'], st['weights'], st['p_global'], st['p_zones'],
+            st['p_families'] if inh else None)
+    ref = orc.log_likelihood(*args, source=st['source'] if sample_source else None)
+    assert abs(ll[-1] - ref) <= 1e-9 * max(1.0, abs(ref)), (ll, ref)
+    cfg = {'geo': {'type': 'cost_based' if geo else 'uniform', 'scale': scale}, 'area_size': {'type': size},
+           'weights': {'type': 'uniform'}, 'contact': {'type': 'uniform'},
+           'universal': {'type': 'counts' if counts else 'uniform'},
+           'inheritance': {'type': 'counts' if (counts and inh) else 'uniform'}}
+    refp = orc.log_prior(st['zones'], st['p_global'], st['p_families'] if inh else None, data.states, inh, cfg,
+                         cost_mat=cost, alpha_global=ag, alpha_families=af)
+    assert abs(prior[-1] - refp) <= 1e-9 * max(1.0, abs(refp)), (prior, refp)
+    names = ['shrink_zone', 'grow_zone', 'swap_zone'] + (
+        ['gibbs_sample_weights', 'gibbs_sample_p_global', 'gibbs_sample_p_zones', 'gibbs_sample_sources'] +
+        (['gibbs_sample_p_families'] if inh else []) if sample_source else
+        ['alter_weights', 'alter_p_global', 'alter_p_zones'] + (['alter_p_families'] if inh else []))
+    if f * 1 < 1 or (not sample_source and int(data.states.sum(1).min()) < 2):
+        names = [k for k in names if not k.startswith('alter_p')]
+    ops = {k: float(w) for k, w in zip(names, rng.dirichlet(np.ones(len(names)))) if w > 0.02}
+    max_size = int(rng.integers(zs + 1, max(zs + 2, min(n, 60))))
+    eng.set_operators(ops, PRECISION, min_size=3, max_size=max_size, p_grow_connected=float(rng.uniform(0, 1)), seed=seed)
+    eng.run(200)
+    ll_run, pr_run = eng.chain_scalars()
+    cnt_run = [eng.counts(ch, recount=False) for ch in range(n_chains)] if sample_source else None
+    ll_new, pr_new, _ = eng.eval()
+    ok = np.isfinite(ll_new)
+    assert np.allclose(ll_run[ok], ll_new[ok], rtol=1e-9) and np.array_equal(np.isfinite(ll_run), ok), (ll_run, ll_new)
+    assert np.allclose(pr_run, pr_new, rtol=1e-9, atol=1e-9), (pr_run, pr_new)
+    for ch in range(n_chains):
+        zz = eng.get_state(ch, fields=('zones',))['zones']
+        assert (zz.sum(axis=0) <= 1).all() and (zz.sum(axis=1) >= 3).all() and (zz.sum(axis=1) <= max(max_size, zs)).all()
+        if sample_source:
+            new = eng.counts(ch, recount=True)
+            for k in new:
+                if new[k] is not None:
+                    assert np.array_equal(cnt_run[ch][k], new[k]), (ch, k)
+    eng.close()
