@@ -419,8 +419,8 @@ class ZoneMCMC(object):
         for t in stops:
             eng.run(t - done)
             done = t
-            if t in log_at or t in swap_at or t in screen_at:
-                self._refresh_scalars()
+            if t in log_at or t in swap_at or t in screen_at or t == n_steps:
+                self._refresh_scalars()                     # (ll, prior) of every chain after t steps
             if t in log_at:
                 c0 = self.chain_idx[0]
                 self.log_sample_statistics(self._fetch_sample(c0, with_source=False), c=c0, sample_id=log_at[t])

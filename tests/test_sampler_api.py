@@ -123,3 +123,59 @@ def test_cli_end_to_end(built_lib, tmp_path):
     assert all(np.isfinite(float(v['likelihood'])) and np.isfinite(float(v['prior'])) for v in vals)
     assert float(vals[0]['prior']) != 0.0                                  # counts + cost-based priors are active
     assert last.zones.shape == (2, 60) and last.source.shape == (60, 4, 3)
+
+
+@pytest.mark.parametrize('seed', range(12))
+def test_api_on_random_shapes(seed, built_lib):
+    """The host mirror (Model, ZoneMCMCWarmup, ZoneMCMC) on seeded random synthetic data sets, the reference's call
+    sequence: warm-up -> best sample -> sampling; the logged values are the model's values of the logged states."""
+    from contact_zones_b200 import synthetic
+    from contact_zones_b200.model import Model
+    from contact_zones_b200.sampling import Sample, ZoneMCMC, ZoneMCMCWarmup
+    rng = np.random.default_rng(500 + seed)
+    z = int(rng.integers(1, 4))
+    n = int(rng.integers(25, 200))
+    f, s_ = int(rng.integers(2, 40)), int(rng.integers(2, 7))
+    fam = int(rng.integers(0, 6))
+    inh = fam > 0
+    sample_source = bool(rng.integers(0, 2))
+    geo = bool(rng.integers(0, 2))
+    data = synthetic.make_data(n, f, s_, n_families=fam, seed=seed, with_dist=True, ragged_states=bool(rng.integers(0, 2)),
+                               na_frac=0.05, counts_prior=bool(rng.integers(0, 2)))
+    has_counts = bool(data.prior_universal)
+    prior = {'geo': {'type': 'cost_based', 'scale': 150.} if geo else {'type': 'uniform'},
+             'area_size': {'type': ['none', 'uniform', 'quadratic'][int(rng.integers(0, 3))]},
+             'weights': {'type': 'uniform'}, 'contact': {'type': 'uniform'},
+             'universal': {'type': 'counts', 'scale_counts': 10., 'file': 'x'} if has_counts else {'type': 'uniform'}}
+    if inh:
+        prior['inheritance'] = ({'type': 'counts', 'scale_counts': 10., 'files': {}} if has_counts
+                                else {'type': 'uniform'})
+    max_m = int(rng.integers(8, 25))
+    cfg = {'N_AREAS': z, 'MIN_M': 3, 'MAX_M': max_m, 'INHERITANCE': inh, 'SAMPLE_SOURCE': sample_source, 'PRIOR': prior}
+    model = Model(data, cfg)
+    kind = 'gibbs_sample' if sample_source else 'alter'
+    ops = {'shrink_zone': 0.04, 'grow_zone': 0.04, 'swap_zone': 0.02, 'gibbsish_sample_zones': 0.0,
+           f'{kind}_weights': 0.4, f'{kind}_p_global': 0.1, f'{kind}_p_zones': 0.3}
+    if inh:
+        ops[f'{kind}_p_families'] = 0.1
+    kw = dict(data=data, model=model, operators=ops, var_proposal=PRECISION, p_grow_connected=0.85, initial_size=4,
+              seed=seed)
+    warm = ZoneMCMCWarmup(n_chains=int(rng.integers(1, 6)), **kw)
+    best = warm.generate_samples(n_steps=0, n_samples=0, warm_up=True, warm_up_steps=200)
+    warm.close()
+    assert (best.zones.sum(axis=0) <= 1).all() and (best.zones.sum(axis=1) >= 3).all()
+    n_chains = int(rng.integers(1, 4))
+    smp = ZoneMCMC(n_chains=n_chains, initial_sample=best, mc3=n_chains > 1, swap_period=50, chain_swaps=1, **kw)
+    smp.generate_samples(600, 6)
+    st = smp.statistics
+    assert len(st['sample_zones']) == 6 and st['sample_zones'][0].shape == (z, n)
+    for i in (0, 5):
+        s = Sample(st['sample_zones'][i], st['sample_weights'][i], st['sample_p_global'][i], st['sample_p_zones'][i],
+                   st['sample_p_families'][i])
+        assert abs(model.prior(s) - st['sample_prior'][i]) <= 1e-9 * max(1., abs(st['sample_prior'][i]))
+        if not sample_source:
+            assert abs(model.likelihood(s) - st['sample_likelihood'][i]) <= 1e-9 * abs(st['sample_likelihood'][i])
+    last = st['last_sample']
+    c0 = smp.chain_idx[0]
+    assert abs(model.likelihood(last) - smp._ll[c0]) <= 1e-9 * abs(smp._ll[c0])
+    smp.close()
