@@ -179,3 +179,47 @@ def test_api_on_random_shapes(seed, built_lib):
     c0 = smp.chain_idx[0]
     assert abs(model.likelihood(last) - smp._ll[c0]) <= 1e-9 * abs(smp._ll[c0])
     smp.close()
+
+
+@pytest.mark.parametrize('seed', range(6))
+def test_mcmc_facade_on_random_shapes(seed, built_lib, tmp_path):
+    """`MCMC` end to end (warm-up, sampling, contribution_per_area, match / rank, result files) on seeded random data
+    sets: Z = 1..4 zones, with / without families, MC3 on / off; the files parse back to consistent values."""
+    from contact_zones_b200 import synthetic
+    from contact_zones_b200.mcmc_setup import MCMC
+    from contact_zones_b200.results import parse_area_columns
+    rng = np.random.default_rng(900 + seed)
+    z, n = int(rng.integers(1, 5)), int(rng.integers(30, 150))
+    f, s_, fam = int(rng.integers(2, 30)), int(rng.integers(2, 6)), int(rng.integers(0, 5))
+    inh = fam > 0
+    data = synthetic.make_data(n, f, s_, n_families=fam, seed=seed, with_dist=True, ragged_states=True, na_frac=0.05)
+    prior = {'geo': {'type': 'cost_based', 'scale': 100.} if seed % 2 else {'type': 'uniform'},
+             'area_size': {'type': 'uniform'}, 'weights': {'type': 'uniform'}, 'contact': {'type': 'uniform'},
+             'universal': {'type': 'uniform'}}
+    if inh:
+        prior['inheritance'] = {'type': 'uniform'}
+    model_cfg = {'N_AREAS': z, 'MIN_M': 3, 'MAX_M': 15, 'INHERITANCE': inh, 'SAMPLE_SOURCE': bool(seed % 3), 'PRIOR': prior}
+    n_chains = 1 + seed % 3
+    mcmc_cfg = _mcmc_config(600, 6, n_chains=n_chains,
+                            mc3={'ACTIVATE': True, 'N_CHAINS': n_chains, 'SWAP_PERIOD': 100, 'N_SWAPS': 1} if n_chains > 1 else None)
+    if not inh:
+        # (the Experiment sets the inheritance steps to 0 when inheritance is disabled, experiment_setup.py:223-227)
+        mcmc_cfg['STEPS'] = {'area': 0.1, 'weights': 0.4, 'universal': 0.1, 'contact': 0.4, 'inheritance': 0.0, 'source': 0.0}
+    cfg = {'model': model_cfg, 'mcmc': mcmc_cfg, 'results': {'FILE_INFO': 'n'}}
+    exp = SimpleNamespace(config=cfg, path_results=pathlib.Path(tmp_path), logger=logging.getLogger('t'))
+    mc = MCMC(data, exp)
+    mc.warm_up()
+    mc.sample()
+    mc.save_samples(run=0)
+    mc.log_statistics()
+    fi = f'n{z}'
+    stats = (tmp_path / fi / f'stats_{fi}_0.txt').read_text().splitlines()
+    areas = (tmp_path / fi / f'areas_{fi}_0.txt').read_text().splitlines()
+    assert len(stats) == 7 and len(areas) == 6
+    hdr = stats[0].split('\t')
+    for line, arow in zip(stats[1:], areas):
+        row = dict(zip(hdr, line.split('\t')))
+        assert abs(float(row['posterior']) - float(row['likelihood']) - float(row['prior'])) < 1e-6
+        zz = parse_area_columns(arow)
+        assert zz.shape == (z, n) and (zz.sum(axis=0) <= 1).all() and (zz.sum(axis=1) >= 3).all()
+        assert all(int(row[f'size_a{k}']) == zz[k].sum() for k in range(z))
