@@ -261,3 +261,48 @@ def test_fallback_evaluation_kernels(name, built_lib, monkeypatch):
     for k in fast:
         if fast[k] is not None:
             assert np.array_equal(fast[k], slow[k]), k
+
+
+@pytest.mark.parametrize('seed', range(int(__import__('os').environ.get('SB_FUZZ_SEEDS_K1', '10'))))
+def test_likelihood_kernels_on_random_large_shapes(seed, built_lib):
+    """K1 (table-driven, source-free), K1 with source and the K4 recount on seeded random shapes up to 20000 sites,
+    40 families, 8 zones, 1..300 chains (the chain count drives K1's split into feature chunks / group splits):
+    likelihood == oracle within 1e-9, count tables == oracle bit for bit."""
+    from contact_zones_b200 import synthetic
+    from contact_zones_b200.engine import Engine, state_index
+    rng = np.random.default_rng(7000 + seed)
+    n = int(rng.choice([40, 333, 1000, 4097, 9000, 20000]))
+    f, s_ = int(rng.integers(1, 50)), int(rng.integers(2, 9))
+    fam = int(rng.integers(0, 41))
+    z, zs = int(rng.integers(1, 9)), int(rng.integers(3, 30))
+    inh = fam > 0
+    n_chains = int(rng.choice([1, 2, 7, 64, 300]))
+    data = synthetic.make_data(n, f, s_, n_families=fam, seed=seed, with_dist=False, ragged_states=bool(rng.integers(0, 2)),
+                               na_frac=float(rng.choice([0.0, 0.02, 0.5])))
+    try:
+        sts = [synthetic.random_state(data, z, min(zs, max(3, n // (2 * z))), inh, True, seed=seed * 7 + i) for i in range(2)]
+    except ValueError:
+        pytest.skip('could not place the random zones')
+    eng = Engine(state_index(data.features), data.states, data.families if inh else None, data.network['adj_mat'], None,
+                 n_zones=z, n_chains=n_chains, inheritance=inh, sample_source=True)
+    for ch in range(n_chains):
+        st = sts[ch % 2]
+        eng.set_state(ch, st['zones'], st['weights'], st['p_global'], st['p_zones'], st['p_families'] if inh else None,
+                      np.argmax(st['source'], -1))
+    ll_free = eng.eval(use_source=False)[0]
+    ll_src = eng.eval(use_source=True)[0]
+    fam_b = np.asarray(data.families, bool)
+    for ch in sorted({0, n_chains - 1, min(1, n_chains - 1)}):
+        st = sts[ch % 2]
+        args = (data.features, fam_b, inh, st['zones'], st['weights'], st['p_global'], st['p_zones'],
+                st['p_families'] if inh else None)
+        ref = orc.log_likelihood(*args, source=None)
+        assert abs(ll_free[ch] - ref) <= RTOL * abs(ref), (ch, ll_free[ch], ref)
+        ref = orc.log_likelihood(*args, source=st['source'])
+        assert abs(ll_src[ch] - ref) <= RTOL * abs(ref), (ch, ll_src[ch], ref)
+    st = sts[(n_chains - 1) % 2]
+    cnt = eng.counts(n_chains - 1, recount=True)
+    assert np.array_equal(cnt['cnt_glob'], orc.state_counts_global(data.features, st['source']))
+    for k in range(z):
+        assert np.array_equal(cnt['cnt_zone'][k], orc.state_counts_zone(data.features, st['source'], st['zones'][k]))
+    eng.close()
