@@ -28,7 +28,7 @@ ERRORS = {-1: 'SB_E_ARG', -2: 'SB_E_CUDA', -3: 'SB_E_STATE', -4: 'SB_E_OVERLAP',
 SYMBOLS = [
     'sb_version', 'sb_device_count', 'sb_create', 'sb_destroy', 'sb_last_error', 'sb_set_stream', 'sb_sync',
     'sb_upload_data', 'sb_set_priors', 'sb_set_state', 'sb_set_states', 'sb_get_state', 'sb_copy_state',
-    'sb_eval', 'sb_eval_likelihood_async', 'sb_read_ll', 'sb_eval_components', 'sb_source_posterior',
+    'sb_eval', 'sb_eval_likelihood_async', 'sb_read_ll', 'sb_eval_likelihood_noalloc', 'sb_eval_components', 'sb_source_posterior',
     'sb_counts', 'sb_move_log_q', 'sb_set_operators', 'sb_run', 'sb_read_chain_scalars', 'sb_read_op_stats',
     'sb_step_counter', 'sb_kernel_launches', 'sb_rng_sample',
 ]
@@ -85,6 +85,7 @@ def load():
         'sb_eval': ([vp, i32, i32, i32, vp, vp, vp], i32),
         'sb_eval_likelihood_async': ([vp, i32, i32, i32], i32),
         'sb_read_ll': ([vp, i32, i32, vp], i32),
+        'sb_eval_likelihood_noalloc': ([vp, i32, i32, vp], i32),
         'sb_eval_components': ([vp, i32, vp, vp], i32),
         'sb_source_posterior': ([vp, i32, vp], i32),
         'sb_counts': ([vp, i32, i32] + [vp] * 5, i32),

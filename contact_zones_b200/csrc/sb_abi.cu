@@ -12,6 +12,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -850,6 +851,101 @@ int sb_read_ll(sb_ctx* ctx, int chain_begin, int n, double* ll) {
     int r = check_range(ctx, chain_begin, n, 0);
     if (r != SB_OK) return r;
     D2H(ll, ctx->st.ll + chain_begin, n);
+    return SB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free likelihood evaluation (no counterpart in the reference; see include/sbayes_b200.h).
+// The scratch of the table-driven K1 -- the per-CTA partial sums and the per-chain arrival tickets -- lives in ONE
+// file-scope device array instead of the context's cudaMalloc'ed buffers.  Every GPU that loads the library holds
+// the array (SB_NA_SCRATCH_BYTES = 528 KiB) until the process exits; every call on a device shares it.
+//   [0, SB_NA_MAX_PARTIALS * 8)            double  partial[chains][parts]
+//   [SB_NA_MAX_PARTIALS * 8, ... + 4 * SB_NA_MAX_CHAINS)   unsigned ticket[chains]   (must start at zero)
+// In host code `sb_na_scratch` is only a stand-in for the symbol: its device address is resolved once per device, with
+// that device current, through cudaGetSymbolAddress (na_scratch_address) and handed to the kernel as a pointer.
+// ---------------------------------------------------------------------------------------------
+#define SB_NA_MAX_PARTIALS 65536
+#define SB_NA_MAX_CHAINS 4096
+#define SB_NA_MAX_DEVICES 64
+#define SB_NA_SCRATCH_BYTES (SB_NA_MAX_PARTIALS * 8 + SB_NA_MAX_CHAINS * 4)
+static __device__ __align__(256) unsigned char sb_na_scratch[SB_NA_SCRATCH_BYTES];
+static std::mutex g_na_mutex;
+static unsigned char* g_na_address[SB_NA_MAX_DEVICES] = {};
+
+// device address of sb_na_scratch on ctx->device (which the caller has made current)
+static int na_scratch_address(sb_ctx* ctx, unsigned char** out) {
+    if (ctx->device < 0 || ctx->device >= SB_NA_MAX_DEVICES) FAIL(SB_E_ARG, "sb_eval_likelihood_noalloc: device index beyond 63");
+    std::lock_guard<std::mutex> lock(g_na_mutex);
+    if (!g_na_address[ctx->device]) {
+        void* p = nullptr;
+        CK(cudaGetSymbolAddress(&p, sb_na_scratch));
+        if (!p) FAIL(SB_E_CUDA, "cudaGetSymbolAddress(sb_na_scratch) returned a null address");
+        g_na_address[ctx->device] = static_cast<unsigned char*>(p);
+    }
+    *out = g_na_address[ctx->device];
+    return SB_OK;
+}
+
+int sb_eval_likelihood_noalloc(sb_ctx* ctx, int chain_begin, int n, double* ll_out) {
+    if (!ctx || !ll_out) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    int r = check_range(ctx, chain_begin, n, 0);
+    if (r != SB_OK) return r;
+    const DevData& d = ctx->d;
+    if (d.S + 1 > LT_ROW) FAIL(SB_E_ARG, "sb_eval_likelihood_noalloc: n_states = 32 is not served by the table-driven kernel");
+    if (n > SB_NA_MAX_CHAINS) FAIL(SB_E_ARG, "sb_eval_likelihood_noalloc: more than 4096 chains per call (static scratch limit)");
+    // launch geometry of the table-driven K1, as in launch_likelihood
+    LhTab t = ctx->lt;
+    const int n_tiles = (t.n_groups + LT_THREADS - 1) / LT_THREADS;
+    const long want = ctx->lt_want;
+    const int fc_min = std::min(d.F, 4);
+    const int chunks = (int)std::min<long>((d.F + fc_min - 1) / fc_min, std::max<long>(1, (want + n - 1) / n));
+    t.n_splits = (int)std::min<long>(n_tiles, std::max<long>(1, (want + (long)chunks * n - 1) / ((long)chunks * n)));
+    t.gsplit = (n_tiles + t.n_splits - 1) / t.n_splits * LT_THREADS;
+    t.n_splits = (t.n_groups + t.gsplit - 1) / t.gsplit;
+    t.max_cls = 1;
+    for (int sp = 0; sp < t.n_splits; ++sp) {
+        const int g0 = sp * t.gsplit, g1 = std::min(t.n_groups, g0 + t.gsplit);
+        t.max_cls = std::max(t.max_cls, ctx->h_gclass[g1 - 1] - ctx->h_gclass[g0] + 1);
+    }
+    t.fc = std::max(1, (d.F + chunks - 1) / chunks);
+    while (t.fc > 1 && lt_smem_bytes(t.fc, t.max_cls, d.S) > 46 * 1024) --t.fc;
+    if (lt_smem_bytes(t.fc, t.max_cls, d.S) > 46 * 1024)
+        FAIL(SB_E_ARG, "sb_eval_likelihood_noalloc: the family-class tables of one feature exceed shared memory");
+    t.n_chunks = (d.F + t.fc - 1) / t.fc;
+    t.smem = std::max(lt_smem_bytes(t.fc, t.max_cls, d.S), (size_t)std::min(d.F, LT_CORR_FB) * 12 * sizeof(double));
+    const int n_corr = d.Z > 0 ? (d.N >= 16384 ? 1 : std::max(1, LT_CORR_CTAS / t.n_splits)) : 0;
+    if (t.n_chunks + n_corr > 65535) FAIL(SB_E_ARG, "sb_eval_likelihood_noalloc: more than 65535 feature chunks");
+    const size_t parts = (size_t)t.n_splits * (t.n_chunks + n_corr);
+    if ((size_t)n * parts > SB_NA_MAX_PARTIALS) {
+        ctx->err = "sb_eval_likelihood_noalloc: " + std::to_string((size_t)n * parts) +
+                   " partial sums exceed the static scratch (65536); evaluate fewer chains per call";
+        return SB_E_ARG;
+    }
+    unsigned char* scratch = nullptr;
+    r = na_scratch_address(ctx, &scratch);
+    if (r != SB_OK) return r;
+    double* part = reinterpret_cast<double*>(scratch);
+    unsigned* tick = reinterpret_cast<unsigned*>(scratch + (size_t)SB_NA_MAX_PARTIALS * 8);
+    // the array keeps the previous call's contents: the tickets must start at zero (the partials are all rewritten)
+    CK(cudaMemsetAsync(tick, 0, (size_t)n * sizeof(unsigned), ctx->stream));
+    dim3 grid(t.n_splits, n, t.n_chunks + n_corr);
+    if (t.cpb == 1)
+        lh_table_kernel<1><<<grid, LT_THREADS, t.smem, ctx->stream>>>(d, ctx->st, t, chain_begin, part, tick);
+    else if (t.cpb == 2)
+        lh_table_kernel<2><<<grid, LT_THREADS, t.smem, ctx->stream>>>(d, ctx->st, t, chain_begin, part, tick);
+    else
+        lh_table_kernel<3><<<grid, LT_THREADS, t.smem, ctx->stream>>>(d, ctx->st, t, chain_begin, part, tick);
+    ++ctx->launches;
+    CK(cudaGetLastError());
+    // result: device memory is written stream-ordered (no synchronisation), host memory is filled before returning
+    cudaPointerAttributes attr;
+    bool on_device = false;
+    if (cudaPointerGetAttributes(&attr, ll_out) == cudaSuccess) on_device = attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged;
+    else cudaGetLastError();
+    CK(cudaMemcpyAsync(ll_out, ctx->st.ll + chain_begin, (size_t)n * sizeof(double),
+                       on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, ctx->stream));
+    if (!on_device) CK(cudaStreamSynchronize(ctx->stream));
     return SB_OK;
 }
 

@@ -186,6 +186,18 @@ class Engine:
         n = self.n_chains - chain_begin if n_chains is None else int(n_chains)
         self._check(self.lib.sb_eval_likelihood_async(self._ctx, int(chain_begin), n, int(bool(use_source))))
 
+    def eval_likelihood_noalloc(self, chain_begin=0, n_chains=None, device_ptr=None):
+        """`sb_eval_likelihood_noalloc`: the source-free likelihood with the kernel's scratch in the library's static
+        device array (no cudaMalloc in the call).  Returns the host array, or writes `n_chains` doubles to the
+        DEVICE address `device_ptr` (stream-ordered, no synchronisation) and returns None."""
+        n = self.n_chains - chain_begin if n_chains is None else int(n_chains)
+        if device_ptr is not None:
+            self._check(self.lib.sb_eval_likelihood_noalloc(self._ctx, int(chain_begin), n, C.c_void_p(int(device_ptr))))
+            return None
+        ll = np.zeros(n)
+        self._check(self.lib.sb_eval_likelihood_noalloc(self._ctx, int(chain_begin), n, ptr(ll)))
+        return ll
+
     def read_ll(self, chain_begin=0, n_chains=None):
         n = self.n_chains - chain_begin if n_chains is None else int(n_chains)
         ll = np.zeros(n)

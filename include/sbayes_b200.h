@@ -139,6 +139,20 @@ int sb_eval(sb_ctx* ctx, int chain_begin, int n_chains, int use_source, double* 
 /* launch-only variant for timing the likelihood kernel with device-resident inputs (no D2H, no sync) */
 int sb_eval_likelihood_async(sb_ctx* ctx, int chain_begin, int n_chains, int use_source);
 int sb_read_ll(sb_ctx* ctx, int chain_begin, int n_chains, double* ll);
+/* Allocation-free variant of the source-free likelihood evaluation (kernel K1).  It has NO counterpart in the reference:
+ * it was added for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  It evaluates Likelihood.__call__ (model.py:174-176) of the
+ * resident chains [chain_begin, chain_begin + n_chains) like sb_eval_likelihood_async, but the kernel's scratch (per-CTA
+ * partial sums + per-chain tickets) is a file-scope `static __device__` array of 528 KiB inside the library instead of
+ * context-owned cudaMalloc memory, and the call itself performs no cudaMalloc / cudaFree / allocating library call.
+ *   ll_out : n_chains doubles, DEVICE memory (written stream-ordered on the context's stream, no synchronisation) or
+ *            HOST memory (filled and synchronised before the call returns).
+ * Limits (SB_E_ARG with a message beyond them): n_chains <= 4096 per call and n_chains * CTAs-per-chain <= 65536
+ * partial sums (a launch uses about max(n_chains, 2 * 148 * 14) of them); n_states <= 31; a context whose family-class
+ * tables do not fit the kernel's shared memory is refused.  Every call on a GPU shares the one array: calls that
+ * overlap on the GPU (different streams or contexts on the same device) race; serialise them.  The first call on a
+ * device resolves the array's address (cudaGetSymbolAddress) -- make it once outside a graph capture. */
+int sb_eval_likelihood_noalloc(sb_ctx* ctx, int chain_begin, int n_chains, double* ll_out);
 
 /* debug / parity: per-cell arrays of update_component_likelihoods (:230-249) and update_weights (:257-294) */
 int sb_eval_components(sb_ctx* ctx, int chain, double* all_lh /* (N,F,C) */, double* wnorm /* (N,F,C) */);
