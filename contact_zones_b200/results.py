@@ -27,14 +27,17 @@ def contribution_per_area(mcmc_sampler, batch=256):
                               with_cost=kw['geo_type'] == 'cost_based')
         eng.set_priors(**kw)
         eng.prior_token = None
+        inh = model.inheritance
         for b0 in range(0, len(pairs), batch):
             chunk = pairs[b0:b0 + batch]
-            for slot, (s, z) in enumerate(chunk):
-                zone = np.asarray(stats['sample_zones'][s])[np.newaxis, z]
-                if kw['geo_type'] == 'cost_based' and zone.sum() < 2:
-                    raise ValueError("Too few locations to compute distance.")
-                eng.set_state(slot, zone, stats['sample_weights'][s], stats['sample_p_global'][s],
-                              np.asarray(stats['sample_p_zones'][s])[np.newaxis, z], stats['sample_p_families'][s], None)
+            zones = np.stack([np.asarray(stats['sample_zones'][s])[np.newaxis, z] for s, z in chunk])
+            if kw['geo_type'] == 'cost_based' and (zones.reshape(len(chunk), -1).sum(axis=1) < 2).any():
+                raise ValueError("Too few locations to compute distance.")
+            # ONE bulk upload per batch (sb_set_states): the (sample, zone) pairs fill consecutive chain slots
+            eng.set_states(0, zones, np.stack([stats['sample_weights'][s] for s, _ in chunk]),
+                           np.stack([np.asarray(stats['sample_p_global'][s]) for s, _ in chunk]),
+                           np.stack([np.asarray(stats['sample_p_zones'][s])[np.newaxis, z] for s, z in chunk]),
+                           np.stack([np.asarray(stats['sample_p_families'][s]) for s, _ in chunk]) if inh else None, None)
             ll, prior, _ = eng.eval(0, len(chunk), use_source=False)
             for slot, (s, z) in enumerate(chunk):
                 lh[s][z], pr[s][z] = float(ll[slot]), float(prior[slot])

@@ -56,6 +56,20 @@ CASES = {
     # model as in its config.json (1 area, MAX_M 200, no families, uniform priors); starts at the simulated area
     'run_F_simexp1': dict(simulated='sim_exp1', Z=1, inh=False, src=True, cp=False, geo='uniform', size='none',
                           n_steps=40000, n_samples=2000, max_m=200),
+    # ---- full-form fixtures (BASELINE.json configs[1], configs[2]): the bundled experiments with the number of areas,
+    # MC3 chains, operator mix (STEPS), PROPOSAL_PRECISION, M_INITIAL and MAX_M of their own config.json, run through
+    # ZoneMCMC(mc3=True, swap_period, chain_swaps) -- the logged chain is chain_idx[0] (mcmc_generative.py:214-223)
+    'run_G_balkan_mc3': dict(bundled='balkan', Z=3, inh=True, src=True, cp=True, geo='uniform', size='none',
+                             n_steps=60000, n_samples=3000, max_m=30, use_cfg=True, n_chains=4, mc3=(100, 3), n_runs=8),
+    'run_H_samerica_mc3': dict(bundled='south_america', Z=5, inh=True, src=True, cp=True, geo='uniform', size='none',
+                               n_steps=40000, n_samples=2000, max_m=30, use_cfg=True, n_chains=8, mc3=(100, 3),
+                               n_runs=8, zone_size0=5),
+    # experiments/simulation/sim_exp2 (its config.json): 951 bundled sites, 50 features and one family drawn by the
+    # reference's seeded simulator, SAMPLE_SOURCE = false (alter_* operators), cost-based geo prior (scale 100),
+    # 1 area, MAX_M 200, the config's STEPS / PROPOSAL_PRECISION; starts at the simulated area
+    'run_I_simexp2': dict(simulated='sim_exp2', Z=1, inh=True, src=False, cp=False, geo='cost_based', size='none',
+                          n_steps=40000, n_samples=2000, max_m=200, use_cfg=True, n_runs=8, skip_port=True,
+                          cost_from_locations=True),
 }
 
 
@@ -86,15 +100,27 @@ def build(case, seed=7):
         c.update(N=data.features.shape[0], F=data.features.shape[1], S=data.features.shape[2],
                  Fam=data.families.shape[0], scales=(info['scale_universal'], info['scale_inheritance']))
         # "planted" = the sites of the initial zones: planted_occ then tracks how much of the start survives
-        data.planted_zones = synthetic.random_state(data, c['Z'], 5, c['inh'], False, seed=seed + 1)['zones']
+        data.planted_zones = synthetic.random_state(data, c['Z'], c.get('zone_size0', 5), c['inh'], False,
+                                                    seed=seed + 1)['zones']
     elif 'simulated' in c:
         import refdata
-        data, info = refdata.load_simulated(c['simulated'], seed=seed)
-        c.update(N=data.features.shape[0], F=data.features.shape[1], S=data.features.shape[2], Fam=0)
+        if c['simulated'] == 'sim_exp1':
+            data, info = refdata.load_simulated(c['simulated'], seed=seed)
+        else:
+            data, info = refdata.load_simulated(c['simulated'], seed=seed, i_contact=None, e_contact=None, area=None,
+                                                inheritance=c['inh'])
+        c.update(N=data.features.shape[0], F=data.features.shape[1], S=data.features.shape[2],
+                 Fam=data.families.shape[0])
     else:
         data = synthetic.make_data(c['N'], c['F'], c['S'], n_families=c['Fam'], na_frac=0.03, seed=seed,
                                    counts_prior=c['cp'], planted_zones=max(1, c['Z']), planted_size=10,
                                    planted_conc=0.3)
+    c['steps'], c['precision'], c['m_initial'] = dict(STEPS), dict(PRECISION), 5
+    if c.get('use_cfg'):
+        m = info['mcmc']
+        c['steps'] = dict(m['STEPS'], source=0.0)
+        c['precision'] = dict(m['PROPOSAL_PRECISION'])
+        c['m_initial'] = int(m['M_INITIAL'])
     raw_u = np.array(data.prior_universal['counts'], float) if c['cp'] else None
     raw_f = np.array(data.prior_inheritance['counts'], float) if (c['cp'] and c['inh']) else None
     st = synthetic.random_state(data, c['Z'], 5, c['inh'], with_source=c['src'], seed=seed + 1)
@@ -108,14 +134,18 @@ def run_reference(c, data, st, seed):
     model_cfg = {'N_AREAS': c['Z'], 'MIN_M': 3, 'MAX_M': c.get('max_m', 30), 'INHERITANCE': c['inh'],
                  'SAMPLE_SOURCE': c['src'], 'PRIOR': prior_config(c)}
     model = ref.model.Model(data, model_cfg)
-    ops = so.default_operators(c['inh'], c['src'], STEPS)
+    ops = so.default_operators(c['inh'], c['src'], c['steps'])
     init = ref.zone_sampling.Sample(zones=st['zones'].copy(), weights=st['weights'].copy(),
                                     p_global=st['p_global'].copy(), p_zones=st['p_zones'].copy(),
                                     p_families=None if st['p_families'] is None else st['p_families'].copy())
     random.seed(seed)
     np.random.seed(seed)
-    sampler = ref.zone_sampling.ZoneMCMC(data=data, model=model, n_chains=1, initial_sample=init, operators=ops,
-                                         var_proposal=PRECISION, p_grow_connected=0.85, initial_size=5)
+    mc3 = {}
+    if c.get('mc3'):
+        mc3 = dict(mc3=True, swap_period=c['mc3'][0], chain_swaps=c['mc3'][1])
+    sampler = ref.zone_sampling.ZoneMCMC(data=data, model=model, n_chains=c.get('n_chains', 1), initial_sample=init,
+                                         operators=ops, var_proposal=c['precision'], p_grow_connected=0.85,
+                                         initial_size=c['m_initial'], **mc3)
     t0 = time.perf_counter()
     sampler.generate_samples(c['n_steps'], c['n_samples'])
     dt = time.perf_counter() - t0
@@ -126,13 +156,14 @@ def run_reference(c, data, st, seed):
     names = sorted(ops)
     out['acc'] = np.array([s['accept_operator'].get(k, 0) / max(1, s['accept_operator'].get(k, 0) +
                                                                s['reject_operator'].get(k, 0)) for k in names])
-    return out, names, c['n_steps'] / dt, model
+    out['swap_ratio'] = np.float64(s['swap_ratio'] if c.get('mc3') else 0.0)
+    return out, names, c['n_steps'] * c.get('n_chains', 1) / dt, model
 
 
 def run_oracle(c, data, st, seed, gibbs_g, alpha_g, gibbs_f, alpha_f, n_steps=None):
-    ops = so.default_operators(c['inh'], c['src'], STEPS)
+    ops = so.default_operators(c['inh'], c['src'], c['steps'])
     smp = so.OracleSampler(data.features, data.states, data.families, data.network['adj_mat'], c['inh'], c['src'],
-                           prior_config(c), ops, PRECISION, 3, c.get('max_m', 30), 0.85, st, seed=seed,
+                           prior_config(c), ops, c['precision'], 3, c.get('max_m', 30), 0.85, st, seed=seed,
                            cost_mat=data.geo_prior['cost_matrix'], gibbs_counts_global=gibbs_g, alpha_global=alpha_g,
                            gibbs_counts_fam=gibbs_f, alpha_fam=alpha_f)
     if c['src']:
@@ -169,8 +200,9 @@ def main(cases):
     os.chdir('/tmp')
     for case in cases:
         c, data, raw_u, raw_f, st = build(case)
-        with mp.get_context('fork').Pool(N_RUNS) as pool:
-            res = pool.starmap(_ref_job, [(case, 100 + r) for r in range(N_RUNS)])
+        n_runs = c.get('n_runs', N_RUNS)
+        with mp.get_context('fork').Pool(min(n_runs, os.cpu_count() or 1)) as pool:
+            res = pool.starmap(_ref_job, [(case, 100 + r) for r in range(n_runs)])
         runs, rate, names = [r[0] for r in res], [r[2] for r in res], res[0][1]
         model = ref.model.Model(data, {'N_AREAS': c['Z'], 'MIN_M': 3, 'MAX_M': c.get('max_m', 30), 'INHERITANCE': c['inh'],
                                        'SAMPLE_SOURCE': c['src'], 'PRIOR': prior_config(c)})
@@ -180,29 +212,46 @@ def main(cases):
             assert np.array_equal(gibbs_g, model.prior.prior_p_global.counts)
             if c['inh']:
                 gibbs_f, alpha_f = orc.dirichlet_prior_tables(raw_f, c.get('scales', (10., 10.))[1])
-        o_out, o_rate = run_oracle(c, data, st, 5, gibbs_g, alpha_g, gibbs_f, alpha_f)
-        keys = ['occ_freq', 'zone_size', 'planted_occ', 'w_mean', 'w_comp', 'pg_mean', 'll_mean', 'prior_mean', 'acc']
+        keys = ['occ_freq', 'zone_size', 'planted_occ', 'w_mean', 'w_comp', 'pg_mean', 'll_mean', 'prior_mean', 'acc',
+                'swap_ratio']
+        if c.get('skip_port'):
+            o_out, o_rate = {k: np.mean([r[k] for r in runs], axis=0) for k in keys}, float('nan')
+        else:
+            o_out, o_rate = run_oracle(c, data, st, 5, gibbs_g, alpha_g, gibbs_f, alpha_f)
+            o_out['swap_ratio'] = np.mean([r['swap_ratio'] for r in runs])
         ref_stack = {k: np.stack([np.asarray(r[k]) for r in runs]) for k in keys}
         print(f'== {case}: reference {np.mean(rate):.0f} steps/s, oracle port {o_rate:.0f} steps/s')
         for k in keys:
             m, s = ref_stack[k].mean(0), ref_stack[k].std(0, ddof=1)
-            z = np.abs(np.asarray(o_out[k]) - m) / np.maximum(s * np.sqrt(1 + 1 / N_RUNS), 1e-3 + 0.02 * np.abs(m))
+            z = np.abs(np.asarray(o_out[k]) - m) / np.maximum(s * np.sqrt(1 + 1 / n_runs), 1e-3 + 0.02 * np.abs(m))
             print(f'   {k:11s} ref mean {np.ravel(m)[:3]} port {np.ravel(o_out[k])[:3]} max|z| {np.max(z):.2f}')
         adj = data.network['adj_mat'].tocsr()
         save = dict(
             features_idx=orc.state_index(data.features), n_states=np.int64(c['S']), states=data.states,
             families=np.asarray(data.families, bool), adj_indptr=adj.indptr.astype(np.int32),
             adj_indices=adj.indices.astype(np.int32),
-            cost=(data.geo_prior['cost_matrix'] if c['geo'] == 'cost_based' else np.zeros((0, 0))),
+            cost=(data.geo_prior['cost_matrix'] if (c['geo'] == 'cost_based' and not c.get('cost_from_locations'))
+                  else np.zeros((0, 0))),
             inheritance=np.bool_(c['inh']), sample_source=np.bool_(c['src']), counts_prior=np.bool_(c['cp']),
             geo_type=np.str_(c['geo']), size_type=np.str_(c['size']), geo_scale=np.float64(100.),
             zones=st['zones'], weights=st['weights'], p_global=st['p_global'], p_zones=st['p_zones'],
             n_steps=np.int64(c['n_steps']), n_samples=np.int64(c['n_samples']), op_names=np.array(names),
             max_m=np.int64(c.get('max_m', 30)),
-            op_weights=np.array([so.default_operators(c['inh'], c['src'], STEPS)[k] for k in names]),
+            op_weights=np.array([so.default_operators(c['inh'], c['src'], c['steps'])[k] for k in names]),
+            precision=np.array([c['precision'][k] for k in ('weights', 'universal', 'contact', 'inheritance')], float),
+            m_initial=np.int64(c['m_initial']), n_chains=np.int64(c.get('n_chains', 1)),
+            swap_period=np.int64(c['mc3'][0] if c.get('mc3') else 0),
+            chain_swaps=np.int64(c['mc3'][1] if c.get('mc3') else 0),
             planted=data.planted_zones.any(0),
             ref_steps_per_s=np.array(rate), port_steps_per_s=np.float64(o_rate),
             **{'ref_' + k: v for k, v in ref_stack.items()})
+        if c.get('cost_from_locations'):
+            # the cost matrix is the Euclidean distance matrix of the sites (simulation.py:155-156,
+            # preprocessing.py:101-174): the fixture keeps the 951 x 2 locations instead of 951 x 951 doubles
+            from scipy.spatial.distance import cdist
+            loc = np.asarray(data.network['locations'], float)
+            assert np.array_equal(cdist(loc, loc), data.geo_prior['cost_matrix'])
+            save['locations'] = loc
         if c['inh']:
             save['p_families'] = st['p_families']
         if c['src']:

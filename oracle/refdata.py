@@ -55,7 +55,7 @@ def load_bundled(name):
     return data, info
 
 
-def load_simulated(name='sim_exp1', seed=0, i_contact=3, e_contact=0.5, area=4):
+def load_simulated(name='sim_exp1', seed=0, i_contact=3, e_contact=0.5, area=4, inheritance=False):
     """experiments/simulation/<name>: the bundled sites with features drawn by the reference's OWN simulator
     (sbayes/simulation.py:Simulation.run_simulation, seeded), as `run_sim_exp1.py` does for one (strength, area) setup."""
     import pathlib
@@ -66,8 +66,9 @@ def load_simulated(name='sim_exp1', seed=0, i_contact=3, e_contact=0.5, area=4):
     cfg = json.load(open(os.path.join(base, 'config.json')))
     sim_cfg = json.load(open(os.path.join(refshim.REFERENCE_ROOT, 'sbayes', 'config', 'default_config_simulation.json')))
     sim_cfg.update(cfg['simulation'])
-    sim_cfg.update(SITES=os.path.join(base, cfg['simulation']['SITES']), I_CONTACT=i_contact, E_CONTACT=e_contact,
-                   AREA=area)
+    sim_cfg.update(SITES=os.path.join(base, cfg['simulation']['SITES']))
+    if i_contact is not None:       # sim_exp1 leaves these to its run script; sim_exp2 / 3 fix them in config.json
+        sim_cfg.update(I_CONTACT=i_contact, E_CONTACT=e_contact, AREA=area)
     exp = types.SimpleNamespace(path_results=pathlib.Path('/tmp'), config={'simulation': sim_cfg})
     random.seed(seed)
     np.random.seed(seed)
@@ -76,10 +77,12 @@ def load_simulated(name='sim_exp1', seed=0, i_contact=3, e_contact=0.5, area=4):
         sim.run_simulation()
     n = sim.features.shape[0]
     data = types.SimpleNamespace(
-        features=np.asarray(sim.features, bool), families=np.zeros((0, n), bool), states=np.asarray(sim.states, bool),
+        features=np.asarray(sim.features, bool),
+        families=np.asarray(sim.families, bool) if inheritance else np.zeros((0, n), bool),
+        states=np.asarray(sim.states, bool),
         network=sim.network, prior_universal={}, prior_inheritance={}, geo_prior=sim.geo_prior,
         state_names=sim.state_names, feature_names=sim.feature_names, family_names=None, site_names=sim.site_names,
         is_simulated=True, crs=None, planted_zones=np.asarray(sim.areas, bool))
-    info = {'inheritance': False, 'scale_universal': None, 'scale_inheritance': None, 'mcmc': cfg['mcmc'],
+    info = {'inheritance': bool(inheritance), 'scale_universal': None, 'scale_inheritance': None, 'mcmc': cfg['mcmc'],
             'model': cfg['model']}
     return data, info
