@@ -22,15 +22,17 @@ OP_IDS = {
     'alter_weights': 8, 'alter_p_global': 9, 'alter_p_zones': 10, 'alter_p_families': 11,
 }
 OP_NAMES = {v: k for k, v in OP_IDS.items()}
-ERRORS = {-1: 'SB_E_ARG', -2: 'SB_E_CUDA', -3: 'SB_E_STATE', -4: 'SB_E_OVERLAP', -5: 'SB_E_NOGPU'}
+ERRORS = {-1: 'SB_E_ARG', -2: 'SB_E_CUDA', -3: 'SB_E_STATE', -4: 'SB_E_OVERLAP', -5: 'SB_E_NOGPU', -6: 'SB_E_NUMERIC'}
+SB_ERR_NONFINITE, SB_ERR_GEO_CAP, SB_ERR_NAPP = 1, 2, 4
 
 # every symbol include/sbayes_b200.h declares (tests/test_abi_symbols.py checks the .so exports them all)
 SYMBOLS = [
     'sb_version', 'sb_device_count', 'sb_create', 'sb_destroy', 'sb_last_error', 'sb_set_stream', 'sb_sync',
     'sb_upload_data', 'sb_set_priors', 'sb_set_state', 'sb_set_states', 'sb_get_state', 'sb_copy_state',
     'sb_eval', 'sb_eval_likelihood_async', 'sb_read_ll', 'sb_eval_likelihood_noalloc', 'sb_eval_components', 'sb_source_posterior',
-    'sb_counts', 'sb_move_log_q', 'sb_set_operators', 'sb_run', 'sb_read_chain_scalars', 'sb_read_op_stats',
-    'sb_step_counter', 'sb_kernel_launches', 'sb_rng_sample',
+    'sb_counts', 'sb_move_log_q', 'sb_pair_log_q', 'sb_set_operators', 'sb_run', 'sb_set_sample_from_prior',
+    'sb_run_events', 'sb_read_event_scalars', 'sb_read_snapshot', 'sb_read_chain_scalars', 'sb_chain_errors',
+    'sb_read_op_stats', 'sb_step_counter', 'sb_kernel_launches', 'sb_rng_sample',
 ]
 
 
@@ -92,6 +94,12 @@ def load():
         'sb_move_log_q': ([vp, i32, i32, i32, i32, i32, dbl, C.POINTER(dbl), C.POINTER(dbl)], i32),
         'sb_set_operators': ([vp, C.POINTER(SbOperatorCfg), vp, vp], i32),
         'sb_run': ([vp, i64], i32),
+        'sb_pair_log_q': ([vp, dbl, dbl, dbl, dbl, dbl, C.POINTER(dbl)], i32),
+        'sb_set_sample_from_prior': ([vp, i32], i32),
+        'sb_run_events': ([vp, i64, i32, vp, vp, i32], i32),
+        'sb_read_event_scalars': ([vp, i32, vp, vp], i32),
+        'sb_read_snapshot': ([vp, i32, i32] + [vp] * 5, i32),
+        'sb_chain_errors': ([vp, vp], i32),
         'sb_read_chain_scalars': ([vp, vp, vp], i32),
         'sb_read_op_stats': ([vp, vp, vp], i32),
         'sb_step_counter': ([vp, C.POINTER(i64)], i32),

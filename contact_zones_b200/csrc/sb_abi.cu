@@ -55,6 +55,15 @@ struct sb_ctx {
     struct Staging stage[2];         // pinned upload staging (sb_set_state)
     size_t stage_bytes = 0;
     int stage_next = 0;
+    bool has_layout = false;         // shared-memory layout / team size of the step kernel chosen (configure_step)
+    ForcedMove* d_forced = nullptr;  // device record of sb_move_log_q
+    double* d_pair = nullptr;        // device result of sb_pair_log_q
+    // events of sb_run_events: device copies + the snapshot ring (grown on demand, freed by sb_destroy)
+    int2* d_events = nullptr;        int events_cap = 0;
+    double2* d_ev_scalars = nullptr; size_t ev_scalars_cap = 0;
+    unsigned char* d_ring = nullptr; size_t ring_cap = 0;
+    size_t ring_rec = 0;
+    int ring_slots = 0;              // slots of the last sb_run_events
 };
 
 #define CK(call)                                                                                  \
@@ -206,6 +215,9 @@ int sb_destroy(sb_ctx* ctx) {
     }
     if (ctx->direct_done) cudaEventDestroy(ctx->direct_done);
     if (ctx->src_scratch) cudaFree(ctx->src_scratch);
+    if (ctx->d_events) cudaFree(ctx->d_events);
+    if (ctx->d_ev_scalars) cudaFree(ctx->d_ev_scalars);
+    if (ctx->d_ring) cudaFree(ctx->d_ring);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
     return SB_OK;
@@ -649,6 +661,7 @@ static int set_states_impl(sb_ctx* ctx, int chain, int n, const uint8_t* zones, 
         CK(cudaMemcpyAsync(st.source + chain * st.s_source, b + o_src, nn * st.s_source, cudaMemcpyHostToDevice, sm));
     CK(cudaEventRecord(sg->done, sm));
     sg->pending = true;
+    CK(cudaMemsetAsync(st.err + chain, 0, nn * sizeof(int), sm));          // a new state starts without error flags
     dim3 grid((F + 127) / 128, n);
     wnorm_kernel<<<grid, 128, 0, ctx->stream>>>(d, st, chain);
     ++ctx->launches;
@@ -956,11 +969,13 @@ int sb_eval(sb_ctx* ctx, int chain_begin, int n, int use_source, double* ll, dou
     if (r != SB_OK) return r;
     if (!ctx->has_priors) FAIL(SB_E_STATE, "sb_set_priors has not been called");
     const DevData& d = ctx->d;
-    if (d.geo_type == SB_GEO_COST_BASED && d.Z > 0) {
-        for (int c = chain_begin; c < chain_begin + n; ++c) {
-            const int m = ctx->h_zone_size[c * ctx->st.s_zone_size + d.Z - 1];
-            if (m > ctx->geo_cap) FAIL(SB_E_ARG, "geo prior: last zone larger than the Prim scratch (4096 members)");
-        }
+    if (d.geo_type == SB_GEO_COST_BASED && d.Z > 0 && d.N > ctx->geo_cap) {
+        // zone sizes as they are on the DEVICE (sb_run moves zones; the host mirror only follows sb_set_state)
+        std::vector<int> zs((size_t)n * ctx->st.s_zone_size);
+        D2H(zs.data(), ctx->st.zone_size + chain_begin * ctx->st.s_zone_size, zs.size());
+        for (int c = 0; c < n; ++c)
+            if (zs[c * ctx->st.s_zone_size + d.Z - 1] > ctx->geo_cap)
+                FAIL(SB_E_ARG, "geo prior: last zone larger than the Prim scratch (4096 members)");
     }
     r = launch_likelihood(ctx, chain_begin, n, use_source);
     if (r != SB_OK) return r;
@@ -1111,6 +1126,82 @@ static int ensure_step_scratch(sb_ctx* ctx) {
     return SB_OK;
 }
 
+// Shared-memory layout and team (thread-block cluster) size of the step kernel for zones of up to `cap` members.
+static int configure_step(sb_ctx* ctx, int cap) {
+    const DevData& d = ctx->d;
+    StepParams& sp = ctx->sp;
+    const int nc = ctx->dims.n_chains;
+    int r = ensure_step_scratch(ctx);
+    if (r != SB_OK) return r;
+    sp.s_shift = 0;
+    while ((1 << sp.s_shift) < d.S) ++sp.s_shift;         // S <= SB_MAX_S = 32
+    sp.prim_cap = d.geo_type == SB_GEO_COST_BASED ? cap : 0;
+    ctx->step_smem = step_smem_bytes(d, sp, cap, ctx->adj_nnz);
+    if (getenv("SBAYES_B200_DEBUG"))
+        fprintf(stderr, "[sbayes_b200] step kernel: smem %zu B (work_off %d counts %d par_off %d zc_off %d zc_cap %d adj_off %d), nwords %d prim_cap %d\n",
+                ctx->step_smem, sp.work_off, sp.work_counts, sp.par_off, sp.zc_off, sp.zc_cap, sp.adj_off, sp.nwords, sp.prim_cap);
+    if (ctx->step_smem > 200 * 1024) FAIL(SB_E_ARG, "step kernel scratch exceeds shared memory (N or MAX_M too large)");
+    // always opt in: the 48 KB default limit applies to static + dynamic shared memory together, and the kernel's
+    // static part (look-ahead tables, reduction scratch, flog table) is ~14 KB
+    CK(cudaFuncSetAttribute(mcmc_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->step_smem));
+    // team (thread-block cluster) size: as many CTAs per chain as the SM count allows, each with at least one
+    // 16-feature block of work; SBAYES_B200_TEAM overrides (1, 2, 4, 8 or 16 -- 16 is a non-portable cluster size)
+    int sms = 0;
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
+    int team = 1;
+    for (int t = 8; t >= 2; t >>= 1)
+        if (nc * t <= sms && d.F >= 16 * t) { team = t; break; }
+    if (const char* env = getenv("SBAYES_B200_TEAM")) {
+        const int t = atoi(env);
+        if (t == 1 || t == 2 || t == 4 || t == 8 || t == 16) team = t;
+    }
+    if (d.sample_source && !sp.work_counts) team = 1;     // the global-atomics source sweep is single-CTA
+    if (team > 8) CK(cudaFuncSetAttribute(mcmc_step_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    while (team > 1) {      // the hardware must be able to co-schedule the cluster
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)(nc * team), 1, 1);
+        cfg.blockDim = dim3(STEP_THREADS, 1, 1);
+        cfg.dynamicSmemBytes = ctx->step_smem;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = (unsigned)team; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        int n_clusters = 0;
+        if (cudaOccupancyMaxActiveClusters(&n_clusters, mcmc_step_kernel, &cfg) == cudaSuccess && n_clusters >= 1) break;
+        cudaGetLastError();
+        team >>= 1;
+    }
+    sp.team = team;
+    ctx->has_layout = true;
+    return SB_OK;
+}
+
+// one launch of the step kernel: a thread-block cluster (team) of sp.team CTAs per chain
+static int launch_steps(sb_ctx* ctx, const StepParams& sp_in, long long n_steps) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(ctx->dims.n_chains * sp_in.team), 1, 1);
+    cfg.blockDim = dim3(STEP_THREADS, 1, 1);
+    cfg.dynamicSmemBytes = ctx->step_smem;
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)sp_in.team;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    // a state uploaded after sb_set_operators may hold a zone that outgrows the member capacity of the shared
+    // zone cache: such a launch reads the global lists instead
+    StepParams sp = sp_in;
+    if (sp.zc_off >= 0 && sp.zc_cap < ctx->d.N)
+        for (int v : ctx->h_zone_size)
+            if (v + 1 > sp.zc_cap) { sp.zc_off = -1; break; }
+    CK(cudaLaunchKernelEx(&cfg, mcmc_step_kernel, ctx->d, ctx->st, sp, n_steps));
+    ++ctx->launches;
+    CK(cudaGetLastError());
+    return SB_OK;
+}
+
 int sb_set_operators(sb_ctx* ctx, const sb_operator_cfg* cfg, const double* p_grow, const int32_t* max_size) {
     if (!ctx || !cfg || !p_grow || !max_size) return SB_E_ARG;
     CK(cudaSetDevice(ctx->device));
@@ -1152,8 +1243,6 @@ int sb_set_operators(sb_ctx* ctx, const sb_operator_cfg* cfg, const double* p_gr
     sp.prec_z = cfg->precision_p_zones; sp.prec_f = cfg->precision_p_families;
     sp.min_size = cfg->min_size;
     sp.frac = cfg->gibbs_feature_fraction;
-    sp.s_shift = 0;
-    while ((1 << sp.s_shift) < d.S) ++sp.s_shift;         // S <= SB_MAX_S = 32
     if ((uint64_t)d.F * d.S >= ((uint64_t)1 << 27)) FAIL(SB_E_ARG, "F*S too large for the step kernel");
     sp.seed_lo = (uint32_t)cfg->seed; sp.seed_hi = (uint32_t)(cfg->seed >> 32);
     int r = ensure_step_scratch(ctx);
@@ -1171,45 +1260,8 @@ int sb_set_operators(sb_ctx* ctx, const sb_operator_cfg* cfg, const double* p_gr
     H2D(ctx->d_pgrow, p_grow, nc);
     H2D(ctx->d_maxsize, max_size, nc);
     sp.p_grow = ctx->d_pgrow; sp.max_size = ctx->d_maxsize;
-    sp.prim_cap = d.geo_type == SB_GEO_COST_BASED ? cap : 0;
-    ctx->step_smem = step_smem_bytes(d, sp, cap, ctx->adj_nnz);
-    if (getenv("SBAYES_B200_DEBUG"))
-        fprintf(stderr, "[sbayes_b200] step kernel: smem %zu B (work_off %d counts %d par_off %d zc_off %d zc_cap %d adj_off %d), nwords %d prim_cap %d\n",
-                ctx->step_smem, sp.work_off, sp.work_counts, sp.par_off, sp.zc_off, sp.zc_cap, sp.adj_off, sp.nwords, sp.prim_cap);
-    if (ctx->step_smem > 200 * 1024) FAIL(SB_E_ARG, "step kernel scratch exceeds shared memory (N or MAX_M too large)");
-    // always opt in: the 48 KB default limit applies to static + dynamic shared memory together, and the kernel's
-    // static part (look-ahead tables, reduction scratch, flog table) is ~14 KB
-    CK(cudaFuncSetAttribute(mcmc_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->step_smem));
-    CK(cudaFuncSetAttribute(move_log_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->step_smem));
-    // team (thread-block cluster) size: as many CTAs per chain as the SM count allows, each with at least one
-    // 16-feature block of work; SBAYES_B200_TEAM overrides (1, 2, 4 or 8)
-    {
-        int sms = 0;
-        CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
-        int team = 1;
-        for (int t = 8; t >= 2; t >>= 1)
-            if (nc * t <= sms && d.F >= 16 * t) { team = t; break; }
-        if (const char* env = getenv("SBAYES_B200_TEAM")) {
-            const int t = atoi(env);
-            if (t == 1 || t == 2 || t == 4 || t == 8) team = t;
-        }
-        if (d.sample_source && !sp.work_counts) team = 1;     // the global-atomics source sweep is single-CTA
-        while (team > 1) {      // the hardware must be able to co-schedule the cluster
-            cudaLaunchConfig_t cfg = {};
-            cfg.gridDim = dim3((unsigned)(nc * team), 1, 1);
-            cfg.blockDim = dim3(STEP_THREADS, 1, 1);
-            cfg.dynamicSmemBytes = ctx->step_smem;
-            cudaLaunchAttribute attr[1];
-            attr[0].id = cudaLaunchAttributeClusterDimension;
-            attr[0].val.clusterDim.x = (unsigned)team; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-            cfg.attrs = attr; cfg.numAttrs = 1;
-            int n_clusters = 0;
-            if (cudaOccupancyMaxActiveClusters(&n_clusters, mcmc_step_kernel, &cfg) == cudaSuccess && n_clusters >= 1) break;
-            cudaGetLastError();
-            team >>= 1;
-        }
-        sp.team = team;
-    }
+    r = configure_step(ctx, cap);
+    if (r != SB_OK) return r;
     ctx->has_ops = true;
     return SB_OK;
 }
@@ -1219,31 +1271,158 @@ int sb_run(sb_ctx* ctx, int64_t n_steps) {
     CK(cudaSetDevice(ctx->device));
     if (!ctx->has_ops) FAIL(SB_E_STATE, "sb_set_operators has not been called");
     if (n_steps == 0) return SB_OK;
-    {
-        // one thread-block cluster (team) of sp.team CTAs per chain
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3((unsigned)(ctx->dims.n_chains * ctx->sp.team), 1, 1);
-        cfg.blockDim = dim3(STEP_THREADS, 1, 1);
-        cfg.dynamicSmemBytes = ctx->step_smem;
-        cfg.stream = ctx->stream;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = (unsigned)ctx->sp.team;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        // a state uploaded after sb_set_operators may hold a zone that outgrows the member capacity of the shared
-        // zone cache: such a launch reads the global lists instead
-        StepParams sp = ctx->sp;
-        if (sp.zc_off >= 0 && sp.zc_cap < ctx->d.N)
-            for (int v : ctx->h_zone_size)
-                if (v + 1 > sp.zc_cap) { sp.zc_off = -1; break; }
-        CK(cudaLaunchKernelEx(&cfg, mcmc_step_kernel, ctx->d, ctx->st, sp, (long long)n_steps));
-    }
-    ++ctx->launches;
+    StepParams sp = ctx->sp;
+    sp.forced = nullptr; sp.n_events = 0; sp.events = nullptr;
+    int r = launch_steps(ctx, sp, (long long)n_steps);
+    if (r != SB_OK) return r;
     ctx->steps_done += n_steps;
-    CK(cudaGetLastError());
+    return SB_OK;
+}
+
+int sb_set_sample_from_prior(sb_ctx* ctx, int on) {
+    if (!ctx) return SB_E_ARG;
+    ctx->sp.from_prior = on ? 1 : 0;
+    return SB_OK;
+}
+
+static size_t ring_record_bytes(const ChainArrays& st) {
+    return ring_align(st.s_zone_id) + ring_align(st.s_weights * 8) + ring_align(st.s_p_global * 8) +
+           ring_align(st.s_p_zones * 8) + ring_align(st.s_p_fam * 8);
+}
+
+int sb_run_events(sb_ctx* ctx, int64_t n_steps, int n_events, const int32_t* event_steps, const int32_t* event_slots,
+                  int ring_chain) {
+    if (!ctx || n_steps < 0 || n_events < 0 || (n_events > 0 && (!event_steps || !event_slots))) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    if (!ctx->has_ops) FAIL(SB_E_STATE, "sb_set_operators has not been called");
+    if (ring_chain < -1 || ring_chain >= ctx->dims.n_chains) FAIL(SB_E_ARG, "ring_chain out of range");
+    if (n_steps == 0) return SB_OK;
+    const size_t nc = (size_t)ctx->dims.n_chains;
+    int n_slots = 0;
+    std::vector<int2> ev((size_t)n_events);
+    for (int k = 0; k < n_events; ++k) {
+        if (event_steps[k] < 1 || event_steps[k] > n_steps || (k > 0 && event_steps[k] <= event_steps[k - 1]))
+            FAIL(SB_E_ARG, "event steps must be ascending in [1, n_steps]");
+        if (event_slots[k] < -1) FAIL(SB_E_ARG, "event slot < -1");
+        ev[k] = make_int2(event_steps[k], event_slots[k]);
+        n_slots = std::max(n_slots, event_slots[k] + 1);
+    }
+    StepParams sp = ctx->sp;
+    sp.forced = nullptr;
+    if (n_events > 0) {
+        // device buffers grow on demand (the stream is drained first: an earlier launch may still use the old ones)
+        if (n_events > ctx->events_cap) {
+            CK(cudaStreamSynchronize(ctx->stream));
+            if (ctx->d_events) CK(cudaFree(ctx->d_events));
+            ctx->d_events = nullptr;
+            CK(cudaMalloc((void**)&ctx->d_events, (size_t)n_events * sizeof(int2)));
+            ctx->events_cap = n_events;
+        }
+        if ((size_t)n_events * nc > ctx->ev_scalars_cap) {
+            CK(cudaStreamSynchronize(ctx->stream));
+            if (ctx->d_ev_scalars) CK(cudaFree(ctx->d_ev_scalars));
+            ctx->d_ev_scalars = nullptr;
+            CK(cudaMalloc((void**)&ctx->d_ev_scalars, (size_t)n_events * nc * sizeof(double2)));
+            ctx->ev_scalars_cap = (size_t)n_events * nc;
+        }
+        ctx->ring_rec = ring_record_bytes(ctx->st);
+        const size_t need = (size_t)n_slots * nc * ctx->ring_rec;
+        if (need > ctx->ring_cap) {
+            CK(cudaStreamSynchronize(ctx->stream));
+            if (ctx->d_ring) CK(cudaFree(ctx->d_ring));
+            ctx->d_ring = nullptr;
+            CK(cudaMalloc((void**)&ctx->d_ring, need));
+            ctx->ring_cap = need;
+        }
+        // the events travel through the pinned staging buffer (the call returns without a synchronisation)
+        Staging* sg;
+        int r = staging_acquire(ctx, std::max<size_t>(ctx->stage_bytes, (size_t)n_events * sizeof(int2)), &sg);
+        if (r != SB_OK) return r;
+        memcpy(sg->buf, ev.data(), (size_t)n_events * sizeof(int2));
+        CK(cudaMemcpyAsync(ctx->d_events, sg->buf, (size_t)n_events * sizeof(int2), cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaEventRecord(sg->done, ctx->stream));
+        sg->pending = true;
+    }
+    sp.events = ctx->d_events; sp.n_events = n_events; sp.ev_scalars = ctx->d_ev_scalars;
+    sp.ring = ctx->d_ring; sp.ring_rec = ctx->ring_rec; sp.ring_chain = ring_chain;
+    ctx->ring_slots = n_slots;
+    int r = launch_steps(ctx, sp, (long long)n_steps);
+    if (r != SB_OK) return r;
+    ctx->steps_done += n_steps;
+    return SB_OK;
+}
+
+static int check_chain_errors(sb_ctx* ctx) {
+    std::vector<int> e((size_t)ctx->dims.n_chains);
+    D2H(e.data(), ctx->st.err, e.size());
+    for (size_t c = 0; c < e.size(); ++c)
+        if (e[c]) {
+            ctx->err = "chain " + std::to_string(c + ctx->dims.chain_offset) + " carries error flags " + std::to_string(e[c]) +
+                       " (1 = non-finite log-likelihood / prior, 2 = zone beyond the geo-prior scratch, "
+                       "4 = alter_p_* on a feature with < 2 applicable states)";
+            return SB_E_NUMERIC;
+        }
+    return SB_OK;
+}
+
+int sb_chain_errors(sb_ctx* ctx, int32_t* flags) {
+    if (!ctx || !flags) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    D2H(flags, ctx->st.err, (size_t)ctx->dims.n_chains);
+    return SB_OK;
+}
+
+int sb_read_event_scalars(sb_ctx* ctx, int n_events, double* ll, double* prior) {
+    if (!ctx || n_events < 0) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    const size_t n = (size_t)n_events * ctx->dims.n_chains;
+    if (n > ctx->ev_scalars_cap) FAIL(SB_E_ARG, "more events than the last sb_run_events recorded");
+    std::vector<double2> h(n);
+    if (n) D2H(h.data(), ctx->d_ev_scalars, n);
+    for (size_t i = 0; i < n; ++i) {
+        if (ll) ll[i] = h[i].x;
+        if (prior) prior[i] = h[i].y;
+    }
+    return check_chain_errors(ctx);
+}
+
+int sb_read_snapshot(sb_ctx* ctx, int slot, int chain, uint8_t* zones, double* weights, double* p_global,
+                     double* p_zones, double* p_families) {
+    if (!ctx) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    int r = check_chain(ctx, chain);
+    if (r != SB_OK) return r;
+    if (slot < 0 || slot >= ctx->ring_slots) FAIL(SB_E_ARG, "snapshot slot out of range");
+    const DevData& d = ctx->d;
+    const ChainArrays& st = ctx->st;
+    const int N = d.N, F = d.F, S = d.S, Z = d.Z, C = d.C, Fam = d.Fam;
+    const size_t FS = (size_t)F * S;
+    Staging* sg;
+    r = staging_acquire(ctx, std::max(ctx->stage_bytes, ctx->ring_rec), &sg);
+    if (r != SB_OK) return r;
+    unsigned char* b = sg->buf;
+    const unsigned char* rec = ctx->d_ring + ((size_t)slot * ctx->dims.n_chains + chain) * ctx->ring_rec;
+    CK(cudaMemcpyAsync(b, rec, ctx->ring_rec, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    size_t off = 0;
+    if (zones && Z > 0) {
+        const int8_t* zid = reinterpret_cast<const int8_t*>(b);
+        memset(zones, 0, (size_t)Z * N);
+        for (int n = 0; n < N; ++n)
+            if (zid[n] >= 0) zones[(size_t)zid[n] * N + n] = 1;
+    }
+    off += ring_align(st.s_zone_id);
+    if (weights) {
+        const double* w3 = reinterpret_cast<const double*>(b + off);
+        for (int f = 0; f < F; ++f)
+            for (int c = 0; c < C; ++c) weights[(size_t)f * C + c] = w3[(size_t)f * 3 + c];
+    }
+    off += ring_align(st.s_weights * 8);
+    if (p_global) memcpy(p_global, b + off, FS * sizeof(double));
+    off += ring_align(st.s_p_global * 8);
+    if (p_zones && Z > 0) memcpy(p_zones, b + off, (size_t)Z * FS * sizeof(double));
+    off += ring_align(st.s_p_zones * 8);
+    if (p_families && d.inheritance) memcpy(p_families, b + off, (size_t)Fam * FS * sizeof(double));
     return SB_OK;
 }
 
@@ -1252,8 +1431,7 @@ int sb_read_chain_scalars(sb_ctx* ctx, double* ll, double* prior) {
     CK(cudaSetDevice(ctx->device));
     if (ll) D2H(ll, ctx->st.ll, ctx->dims.n_chains);
     if (prior) D2H(prior, ctx->st.prior, ctx->dims.n_chains);
-    CK(cudaStreamSynchronize(ctx->stream));
-    return SB_OK;
+    return check_chain_errors(ctx);
 }
 
 int sb_read_op_stats(sb_ctx* ctx, int64_t* accepted, int64_t* rejected) {
@@ -1290,20 +1468,39 @@ int sb_move_log_q(sb_ctx* ctx, int chain, int kind, int zone, int site_new, int 
     if (kind != SB_OP_GROW_ZONE && kind != SB_OP_SHRINK_ZONE && kind != SB_OP_SWAP_ZONE) FAIL(SB_E_ARG, "kind");
     if (kind != SB_OP_SHRINK_ZONE && (site_new < 0 || site_new >= d.N)) FAIL(SB_E_ARG, "site_new out of range");
     if (kind != SB_OP_GROW_ZONE && (site_removed < 0 || site_removed >= d.N)) FAIL(SB_E_ARG, "site_removed out of range");
-    r = ensure_step_scratch(ctx);
+    // the step kernel itself evaluates the proposal (its own set-up: zone cache, staged adjacency).  Without
+    // sb_set_operators the layout is chosen for the zones as they are now
+    if (!ctx->has_layout) {
+        int cap = 2;
+        for (int v : ctx->h_zone_size) cap = std::max(cap, v + 2);
+        r = configure_step(ctx, std::min(cap, d.N));
+        if (r != SB_OK) return r;
+    }
+    if (!ctx->d_forced) DA(ctx->d_forced, 1);
+    ForcedMove fm = {kind, zone, site_new, site_removed, rho, {NAN, NAN}};
+    CK(cudaMemcpyAsync(ctx->d_forced, &fm, sizeof(fm), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    StepParams sp = ctx->sp;
+    sp.forced = ctx->d_forced; sp.n_events = 0; sp.events = nullptr;
+    // the kernel runs on the whole grid (one team per chain); only the team of `chain` stores its result
+    sp.forced_chain = chain;
+    r = launch_steps(ctx, sp, 0);
     if (r != SB_OK) return r;
-    const size_t smem = step_smem_base(ctx->sp);
-    CK(cudaFuncSetAttribute(move_log_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    double* dout;
-    CK(cudaMalloc((void**)&dout, 2 * sizeof(double)));
-    move_log_q_kernel<<<1, STEP_THREADS, smem, ctx->stream>>>(d, ctx->st, ctx->sp, chain, kind, zone, site_new,
-                                                             site_removed, rho, dout);
+    CK(cudaMemcpyAsync(&fm, ctx->d_forced, sizeof(fm), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    *log_q = fm.out[0]; *log_q_back = fm.out[1];
+    return SB_OK;
+}
+
+int sb_pair_log_q(sb_ctx* ctx, double c0, double c1, double n0, double n1, double precision, double* log_q_ratio) {
+    if (!ctx || !log_q_ratio) return SB_E_ARG;
+    if (!(c0 > 0.0 && c1 > 0.0 && n0 > 0.0 && n1 > 0.0 && precision >= 0.0)) FAIL(SB_E_ARG, "sb_pair_log_q: pairs must be positive");
+    CK(cudaSetDevice(ctx->device));
+    if (!ctx->d_pair) DA(ctx->d_pair, 1);
+    pair_log_q_kernel<<<1, 32, 0, ctx->stream>>>(c0, c1, n0, n1, precision, ctx->d_pair);
     ++ctx->launches;
-    double h[2] = {0, 0};
-    r = d2h(ctx, h, dout, 2);
-    cudaFree(dout);
-    if (r != SB_OK) return r;
-    *log_q = h[0]; *log_q_back = h[1];
+    CK(cudaGetLastError());
+    D2H(log_q_ratio, ctx->d_pair, 1);
     return SB_OK;
 }
 

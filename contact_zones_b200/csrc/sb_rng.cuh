@@ -146,8 +146,10 @@ __device__ __forceinline__ void rng_gamma2(RngKey key, uint64_t step, uint32_t p
         if (need_a && (ka0 || ka1)) { ga = ka0 ? a0 : a1; need_a = false; }
         if (need_b && (kb0 || kb1)) { gb = kb0 ? b0 : b1; need_b = false; }
     }
-    if (need_a) ga = da;
-    if (need_b) gb = db;
+    // 64 rejected attempts (probability < 1e-80 per draw): poison the draw -- the NaN reaches the running
+    // log-likelihood and is reported as SB_ERR_NONFINITE instead of passing for a sample
+    if (need_a) ga = __longlong_as_double(0x7ff8000000000000LL);
+    if (need_b) gb = __longlong_as_double(0x7ff8000000000000LL);
 }
 
 // Single draw (same stream as rng_gamma2 for that (purpose, index)); alpha < 1 uses Gamma(alpha+1) * U^(1/alpha).
@@ -166,7 +168,7 @@ __device__ double rng_gamma(RngKey key, uint64_t step, uint32_t purpose, uint32_
         if (mt_accept(m.x0, m.u0, c, d, g)) return boost * g;
         if (mt_accept(m.x1, m.u1, c, d, g)) return boost * g;
     }
-    return boost * d;   // unreachable in practice (acceptance > 95 % per candidate)
+    return __longlong_as_double(0x7ff8000000000000LL);   // unreachable in practice (acceptance > 95 % per candidate); see rng_gamma2
 }
 
 // debug / parity surface of K6 (sb_rng_sample): n independent draws, kind 0 = uniform(0,1), 1 = Gamma(alpha, 1),

@@ -58,6 +58,25 @@ struct StepParams {
     int adj_off;              // byte offset of the adjacency CSR { int ptr[N+1]; int idx[nnz] } in shared memory, or -1
     int* tmp_members;         // [chains][N]     candidate member list for the geo prior
     size_t s_tmp;
+    int from_prior;           // sample_from_prior (mcmc_generative.py:115-116): the likelihood is identically 0
+    struct ForcedMove* forced;   // non-null: evaluate ONE forced zone-move proposal and return (sb_move_log_q)
+    int forced_chain;         // the chain whose team evaluates it
+    // host-visible events inside a launch (logged samples, MC3 swap points): after `events[k].x` completed steps of the
+    // launch every chain records (ll, prior) in ev_scalars[k][chain]; if events[k].y >= 0 the chain also copies its
+    // state into snapshot slot events[k].y of the ring
+    const int2* events;
+    int n_events;
+    double2* ev_scalars;      // [n_events][chains]
+    unsigned char* ring;      // [slots][chains][ring_rec] snapshot records
+    size_t ring_rec;          // bytes of one record: zone_id | weights | p_global | p_zones | p_fam  (16 B aligned parts)
+    int ring_chain;           // local chain whose states are recorded, or -1 = every chain (MC3: the logged label moves)
+};
+// forced zone-move proposal (parity surface of zone_sampling.py:704-933, 1328-1574): the proposal code of op_zone_move
+// runs with the zone / sites given instead of drawn and stores log q, log q_back
+struct ForcedMove {
+    int kind, zone, site_new, site_removed;
+    double rho;
+    double out[2];
 };
 
 // ---- shared scratch of the step kernel -----------------------------------------------------------
@@ -81,6 +100,7 @@ struct StepShared {
     int pick;           // bits_select result
     double dshare[4];
     double wpart[2][2][STEP_WARPS];   // per-warp partial sums of the team reductions (double-buffered pair), read by peers
+    double wcta[2][2][STEP_WARPS];    // the same for CTA-scope sums: never read by a peer CTA, own parity (Team::cturn)
     // per-step scalar draws of the next SB_AHEAD steps (operator id and the uniforms behind "which zone / family /
     // fixed component"), filled by four warps once per SB_AHEAD steps instead of by every thread in every step
     int op_ahead[SB_AHEAD];
@@ -182,6 +202,7 @@ struct Team {
     int rank, size;
     unsigned turn;      // parity of the reduction buffer (advances identically in every CTA)
     int shift;          // log2(size)
+    unsigned cturn;     // parity of the CTA-scope reduction buffer
 };
 __device__ __forceinline__ void team_sync(const Team& t) {
     if (t.size > 1) cg::this_cluster().sync(); else __syncthreads();
@@ -233,8 +254,11 @@ __device__ __noinline__ double2 sum2_impl(double a, double b, double* wpart, uns
     return make_double2(sa, sb);
 }
 __device__ __forceinline__ void sum2_scope(double& a, double& b, StepShared& sh, Team& t, int scope) {
-    const double2 r = sum2_impl(a, b, &sh.wpart[0][0][0], t.turn, scope);
-    ++t.turn;
+    // CTA-scope sums use their own double-buffered scratch and parity: they meet in a __syncthreads only, so they must
+    // not rewrite a slot that a slower peer CTA may still be reading through DSMEM
+    const bool cta = scope <= 1;
+    const double2 r = sum2_impl(a, b, cta ? &sh.wcta[0][0][0] : &sh.wpart[0][0][0], cta ? t.cturn : t.turn, scope);
+    if (cta) ++t.cturn; else ++t.turn;
     a = r.x; b = r.y;
 }
 __device__ __forceinline__ void team_sum2(double& a, double& b, StepShared& sh, Team& t) { sum2_scope(a, b, sh, t, t.size); }
@@ -625,18 +649,22 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
                              RngKey key, uint64_t step, double& ll, double& prior, double& geo,
                              unsigned* nbr, unsigned* freeb, double* prim_key, unsigned char* prim_tree,
                              StepShared& sh, Team& tm, const double* ua, bool& synced, bool& wrote_nothing,
-                             bool& need_sweep) {
+                             bool& need_sweep, int* err) {
     wrote_nothing = true;       // until the proposal is accepted: a rejected move only read the chain state
     // ua: this step's column of the look-ahead table (ua[q * SB_AHEAD] = uniform q of the step)
     PROF_T(tzp);
-    const double rho = sp.p_grow[chain];
-    const int max_size = sp.max_size[chain];
-    const int z = ahead_int(ua[UA_ZONE * SB_AHEAD], d.Z);
+    // fm != null (sb_move_log_q): the zone and the sites are given, the proposal probabilities are stored and the
+    // move is dropped -- the SAME code computes q / q_back for the sampler and for the parity surface
+    ForcedMove* fm = sp.forced;
+    const double rho = fm ? fm->rho : sp.p_grow[chain];
+    const int z = fm ? fm->zone : ahead_int(ua[UA_ZONE * SB_AHEAD], d.Z);
     const int size = k.szq[z];
     int* mem = k.members + (size_t)z * d.N;                 // global list (written on accept)
     const int* memq = k.memq + (size_t)z * k.zq_ld;         // the list the proposal reads (shared-memory cache if any)
-    if (kind == SB_OP_GROW_ZONE && size >= max_size) return false;        // :818-820
-    if (kind == SB_OP_SHRINK_ZONE && size <= sp.min_size) return false;   // :894-896
+    if (!fm) {
+        if (kind == SB_OP_GROW_ZONE && size >= sp.max_size[chain]) return false;      // :818-820
+        if (kind == SB_OP_SHRINK_ZONE && size <= sp.min_size) return false;           // :894-896
+    }
 
     int n_occ = 0;
     for (int i = 0; i < d.Z; ++i) n_occ += k.szq[i];
@@ -650,7 +678,7 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
         build_nbr_bits(k.adj_ptr, k.adj_idx, k.zq, memq, size, -1, nbr, sp.nwords);
         PROF_T(tz1);
         PROF_ADD(8, tz0, tz1);
-        const bool connected = ua[UA_CONNECTED * SB_AHEAD] < rho;                 // :731,823
+        const bool connected = fm ? true : ua[UA_CONNECTED * SB_AHEAD] < rho;     // :731,823
         // warp 0 counts the neighbourhood and, for a connected step, picks the candidate in the same scan; the
         // other warps meanwhile build the bitmap of free sites if the step is not connected
         bits_select(nbr, sp.nwords, 0, connected ? &sh.pick : &sh.redi[1], &sh.redi[0], ua[UA_SITE_NEW * SB_AHEAD]);
@@ -660,21 +688,21 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
         PROF_T(tz2);
         PROF_ADD(9, tz1, tz2);
         const int n_cand = connected ? n_nbr : n_free;
-        if (n_cand == 0) return false;                                            // :740-741, 832-833
+        if (n_cand == 0 && !fm) return false;                                     // :740-741, 832-833
         if (!connected) {
             bits_select(freeb, sp.nwords, ahead_int(ua[UA_SITE_NEW * SB_AHEAD], n_cand), &sh.pick);
             __syncthreads();
         }
-        site_new = sh.pick;
+        site_new = fm ? fm->site_new : sh.pick;
         q = grow_q(bit_test(nbr, site_new), n_free, n_nbr, rho);
         if (kind == SB_OP_GROW_ZONE) {
             q_back = 1.0 / (double)(size + 1);                                    // :848
         } else {
-            site_removed = memq[ahead_int(ua[UA_SITE_REMOVED * SB_AHEAD], size)];  // :748-750
+            site_removed = fm ? fm->site_removed : memq[ahead_int(ua[UA_SITE_REMOVED * SB_AHEAD], size)];  // :748-750
             q_back = grow_q(false, n_free, n_nbr, rho);    // old zone's neighbourhood never holds a member (:753,768)
         }
     } else {
-        site_removed = memq[ahead_int(ua[UA_SITE_REMOVED * SB_AHEAD], size)];      // :899-901
+        site_removed = fm ? fm->site_removed : memq[ahead_int(ua[UA_SITE_REMOVED * SB_AHEAD], size)];      // :899-901
         q = 1.0 / (double)size;                                                   // :904
         build_nbr_bits(k.adj_ptr, k.adj_idx, k.zq, memq, size, site_removed, nbr, sp.nwords);    // :906-908
         bits_select(nbr, sp.nwords, 0, &sh.redi[1], &sh.redi[0], 0.0);            // warp 0: the count only
@@ -686,9 +714,13 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
     __syncthreads();
     PROF_T(tz3);
     PROF_ADD(10, tz0, tz3);
+    if (fm) {
+        if (threadIdx.x == 0 && tm.rank == 0) { fm->out[0] = log(q); fm->out[1] = log(q_back); }
+        return false;
+    }
 
-    // likelihood ratio of the moved site(s)
-    const double dll = zone_move_delta(d, k, site_new, site_removed, z, sh, tm);
+    // likelihood ratio of the moved site(s); sample_from_prior: the likelihood is identically 0 (mcmc_generative.py:115-116)
+    const double dll = sp.from_prior ? 0.0 : zone_move_delta(d, k, site_new, site_removed, z, sh, tm);
     PROF_T(tz4);
     PROF_ADD(11, tz3, tz4);
 
@@ -705,7 +737,11 @@ __device__ bool op_zone_move(const DevData& d, const StepParams& sp, const Chain
             if (site_new >= 0) k.tmp[m++] = site_new;
         }
         __syncthreads();
-        geo_new = geo_prior_of(d, k.tmp, min(new_size, sp.prim_cap), prim_key, prim_tree, sh);
+        if (new_size > sp.prim_cap) {      // cannot happen through the operators (prim_cap > every max_size): a state
+            if (threadIdx.x == 0 && tm.rank == 0) atomicOr(err, SB_ERR_GEO_CAP);      // uploaded later with a larger zone
+            return false;
+        }
+        geo_new = geo_prior_of(d, k.tmp, new_size, prim_key, prim_tree, sh);
         dprior += geo_new - geo;
     }
 
@@ -904,6 +940,28 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
 // then lane l takes one of the six lgamma terms and one of the four x log y terms.  (Every thread used to evaluate all of
 // it -- ~3000 instructions per warp and step, which is what an alter_* step cost whatever the number of sites.)
 // Ends in a CTA barrier; sh.dshare[0..2] is rewritten only after the caller's reduction barrier.
+// log q(t -> v) - log q(v -> t) of the pair proposal; called by (at least) 8 consecutive lanes of a warp with
+// l = lane & 7, result valid in all of them
+__device__ __forceinline__ double pair_log_q_ratio(int l, double t0, double t1, double v0, double v1, double kappa) {
+    const double a0 = 1.0 + kappa * t0, a1 = 1.0 + kappa * t1;
+    const double b0 = 1.0 + kappa * v0, b1 = 1.0 + kappa * v1;
+    const double X = l == 0 ? a0 : l == 1 ? a1 : l == 2 ? b0 : l == 3 ? b1 : l == 4 ? a0 + a1 : b0 + b1;
+    const double sgn = (l == 0 || l == 1 || l == 5) ? -1.0 : 1.0;
+    double term = l < 6 ? sgn * lgamma(X) : 0.0;
+    const double coef = l == 0 ? a0 - 1.0 : l == 1 ? a1 - 1.0 : l == 2 ? -(b0 - 1.0) : -(b1 - 1.0);
+    const double Y = l == 0 ? v0 : l == 1 ? v1 : l == 2 ? t0 : t1;
+    if (l < 4) term += xlogy_d(coef, Y);
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) term += __shfl_xor_sync(0xffffffffu, term, o);
+    return term;
+}
+// parity surface of dirichlet_proposal (zone_sampling.py:538-569) for a FORCED new pair: the log-density code of
+// pair_proposal with v' given instead of drawn.  out[0] = log_q - log_q_back
+__global__ void pair_log_q_kernel(double c0, double c1, double n0, double n1, double kappa, double* out) {
+    const double mass = c0 + c1;
+    const double term = pair_log_q_ratio(threadIdx.x & 7, c0 / mass, c1 / mass, n0 / mass, n1 / mass, kappa);
+    if (threadIdx.x == 0) out[0] = term;
+}
 __device__ void pair_proposal(RngKey key, uint64_t step, double c0, double c1, double kappa, double& n0, double& n1,
                               double& log_q_ratio, StepShared& sh) {
     if (threadIdx.x < 32) {
@@ -914,15 +972,7 @@ __device__ void pair_proposal(RngKey key, uint64_t step, double c0, double c1, d
         const double g = rng_gamma(key, step, RP_PROPOSAL, (uint32_t)(lane & 1), (lane & 1) ? a1 : a0);
         const double g0 = __shfl_sync(0xffffffffu, g, 0), g1 = __shfl_sync(0xffffffffu, g, 1);
         const double v0 = g0 / (g0 + g1), v1 = g1 / (g0 + g1);
-        const double b0 = 1.0 + kappa * v0, b1 = 1.0 + kappa * v1;
-        const double X = l == 0 ? a0 : l == 1 ? a1 : l == 2 ? b0 : l == 3 ? b1 : l == 4 ? a0 + a1 : b0 + b1;
-        const double sgn = (l == 0 || l == 1 || l == 5) ? -1.0 : 1.0;
-        double term = l < 6 ? sgn * lgamma(X) : 0.0;
-        const double coef = l == 0 ? a0 - 1.0 : l == 1 ? a1 - 1.0 : l == 2 ? -(b0 - 1.0) : -(b1 - 1.0);
-        const double Y = l == 0 ? v0 : l == 1 ? v1 : l == 2 ? t0 : t1;
-        if (l < 4) term += xlogy_d(coef, Y);
-#pragma unroll
-        for (int o = 1; o < 8; o <<= 1) term += __shfl_xor_sync(0xffffffffu, term, o);
+        const double term = pair_log_q_ratio(l, t0, t1, v0, v1, kappa);
         if (lane == 0) { sh.dshare[0] = v0 * mass; sh.dshare[1] = v1 * mass; sh.dshare[2] = term; }
     }
     __syncthreads();
@@ -982,7 +1032,7 @@ __device__ double column_delta(const DevData& d, const Chain& k, int f, const in
 
 // alter_weights / alter_p_global / alter_p_zones / alter_p_families (zone_sampling.py:408-612). Returns accepted.
 __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k, int op, RngKey key, uint64_t step,
-                         double& ll, double& prior, StepShared& sh, Team& tm, const double* ua, bool& synced) {
+                         double& ll, double& prior, StepShared& sh, Team& tm, const double* ua, bool& synced, int* err) {
     // ua: this step's column of the look-ahead table (ua[q * SB_AHEAD] = uniform q of the step)
     const int f = ahead_int(ua[UA_FEATURE * SB_AHEAD], d.F);          // np.random.choice(range(n_features))
     double lqr, n0, n1, dll, dprior = 0.0;
@@ -998,7 +1048,9 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
             wnorm_row(v, wrow_new, d.C);
         }
         __syncthreads();
-        dll = column_delta(d, k, f, nullptr, d.N, wrow_new, -1, 0, 0, 0, 0.0, 0.0, sh, tm);
+        // sample_from_prior: no likelihood term; the team barrier of the reduction is still needed
+        if (sp.from_prior) { team_sync(tm); dll = 0.0; }
+        else dll = column_delta(d, k, f, nullptr, d.N, wrow_new, -1, 0, 0, 0, 0.0, 0.0, sh, tm);
         const bool accept = flog(ua[UA_ACCEPT * SB_AHEAD], k.flt) < dll - lqr;
         synced = !accept;       // a rejected proposal wrote nothing after the reduction's barrier
         if (accept) {
@@ -1014,7 +1066,10 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
     }
     const uint32_t mask = d.app_mask[f];
     const int napp = d.n_app[f];
-    if (napp < 2) return false;       // the reference's random.sample(list, 2) raises here; we reject the step
+    if (napp < 2) {                   // the reference's random.sample(list, 2) raises ValueError here: the step is
+        if (threadIdx.x == 0 && tm.rank == 0) atomicOr(err, SB_ERR_NAPP);      // rejected and the chain flagged
+        return false;
+    }
     int ia, ib;
     pick_pair(ua, napp, ia, ib);                                      // _random.sample(list(f_states), 2)
     const int s0 = nth_state(mask, ia), s1 = nth_state(mask, ib);
@@ -1056,7 +1111,8 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
         new_prior_term = sh.dshare[3];
         dprior = new_prior_term - *pcache;
     }
-    dll = column_delta(d, k, f, sites, n_sites, nullptr, which, tab, s0, s1, n0, n1, sh, tm);
+    if (sp.from_prior) { team_sync(tm); dll = 0.0; }
+    else dll = column_delta(d, k, f, sites, n_sites, nullptr, which, tab, s0, s1, n0, n1, sh, tm);
     const bool accept = flog(ua[UA_ACCEPT * SB_AHEAD], k.flt) < dll - lqr + dprior;
     synced = !accept;
     if (accept) {
@@ -1072,13 +1128,36 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
     return accept;
 }
 
+// ---- snapshot of one chain's state into the ring: record = zone_id i8[s_zone_id] | weights
+// f64[F][3] | p_global | p_zones | p_fam, every part 16 B aligned.  All CTAs of the team copy, 16 bytes per thread and
+// iteration; the caller has published the team's writes (team barrier) before and fences with one after.
+__host__ __device__ __forceinline__ size_t ring_align(size_t v) { return (v + 15) & ~(size_t)15; }
+__device__ void snapshot_state(const DevData& d, const ChainArrays& st, const StepParams& sp, int chain, int slot,
+                               int n_chains, const Team& tm) {
+    unsigned char* rec = sp.ring + ((size_t)slot * n_chains + chain) * sp.ring_rec;
+    const void* src[5] = {st.zone_id + chain * st.s_zone_id, st.weights + chain * st.s_weights,
+                          st.p_global + chain * st.s_p_global, st.p_zones + chain * st.s_p_zones,
+                          st.p_fam + chain * st.s_p_fam};
+    const size_t len[5] = {st.s_zone_id, st.s_weights * 8, st.s_p_global * 8, st.s_p_zones * 8, st.s_p_fam * 8};
+    size_t off = 0;
+    const int tid = tm.rank * blockDim.x + threadIdx.x, nthr = tm.size * blockDim.x;
+    for (int a = 0; a < 5; ++a) {
+        // every per-chain array starts 16 B aligned only if its stride is a multiple of 2 doubles: copy 8 B units
+        const size_t n8 = len[a] >> 3;
+        const unsigned long long* s8 = reinterpret_cast<const unsigned long long*>(src[a]);
+        unsigned long long* d8 = reinterpret_cast<unsigned long long*>(rec + off);
+        for (size_t i = tid; i < n8; i += nthr) d8[i] = __ldcg(s8 + i);
+        off += ring_align(len[a]);
+    }
+}
+
 // ---- K8: the persistent kernel ---------------------------------------------------------------------
 __global__ void __launch_bounds__(STEP_THREADS, STEP_MIN_CTAS)
 mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
     extern __shared__ unsigned char step_smem[];
     __shared__ StepShared sh;
     const int chain = blockIdx.x / sp.team;             // one cluster of sp.team CTAs per chain (cluster dims (team,1,1))
-    Team tm = {(int)(blockIdx.x % sp.team), sp.team, 0u, 31 - __clz(sp.team)};
+    Team tm = {(int)(blockIdx.x % sp.team), sp.team, 0u, 31 - __clz(sp.team), 0u};
     unsigned* nbr = reinterpret_cast<unsigned*>(step_smem);
     unsigned* freeb = nbr + sp.nwords;
     double* prim_key = reinterpret_cast<double*>(freeb + sp.nwords);       // 2 * nwords words from the start: 8 B aligned
@@ -1117,8 +1196,22 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
     const Chain& k = kv;
     const unsigned gchain = (unsigned)(sp.chain_offset + chain);
     const RngKey key = {sp.seed_lo ^ (gchain * 0x9E3779B9u), sp.seed_hi ^ gchain};
-    double ll = st.ll[chain], prior = st.prior[chain], geo = st.geo[chain];
+    double ll = sp.from_prior ? 0.0 : st.ll[chain], prior = st.prior[chain], geo = st.geo[chain];
     const uint64_t step0 = st.step[chain];
+    if (sp.forced) {
+        // parity surface (sb_move_log_q): one forced proposal through op_zone_move, behind the same set-up (zone cache,
+        // staged adjacency) as a sampling launch; nothing of the chain state is written
+        if (chain == sp.forced_chain) {
+            for (int i = threadIdx.x; i < SB_N_AHEAD; i += blockDim.x) sh.u_ahead[i][0] = 0.5;
+            __syncthreads();
+            bool f0 = false, f1 = false, f2 = false;
+            op_zone_move(d, sp, k, sp.forced->kind, chain, key, step0, ll, prior, geo, nbr, freeb, prim_key, prim_tree, sh,
+                         tm, &sh.u_ahead[0][0], f0, f1, f2, st.err + chain);
+        }
+        if (tm.size > 1) cg::this_cluster().sync();
+        return;
+    }
+    int ev = 0;                                         // cursor into sp.events (team-uniform)
 
     bool dirty = false;         // a Gibbs operator wrote chain tables since the last full team barrier
     // The Gibbs operators are always accepted, and nobody needs the absolute ll / prior inside a launch (the
@@ -1128,7 +1221,12 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
     // operator ran after the last from-scratch value.
     double prior_acc = 0.0;
     bool ll_stale = false;
-    for (long long it = 0; it < n_steps; ++it) {
+    // the steps run in segments that end at the next host-visible event (or at n_steps): the hot loop itself knows
+    // nothing about events
+    long long it = 0;
+    for (;;) {
+    const long long seg_end = ev < sp.n_events ? (long long)sp.events[ev].x : n_steps;
+    for (; it < seg_end; ++it) {
         const uint64_t step = step0 + (uint64_t)it;
         PROF_T(ts0);
         // operator choice: np.random.choice(fn_operators, p=p_operators)  (mcmc_generative.py:294).  The draws that
@@ -1175,7 +1273,8 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
         switch (op) {
             case SB_OP_SHRINK_ZONE: case SB_OP_GROW_ZONE: case SB_OP_SWAP_ZONE:
                 accepted = op_zone_move(d, sp, k, op, chain, key, step, ll, prior, geo, nbr, freeb, prim_key,
-                                        prim_tree, sh, tm, &sh.u_ahead[0][ia], synced, read_only, need_sweep);
+                                        prim_tree, sh, tm, &sh.u_ahead[0][ia], synced, read_only, need_sweep,
+                                        st.err + chain);
                 break;
             case SB_OP_GIBBS_SOURCES:
                 need_sweep = true;
@@ -1205,13 +1304,14 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
                 break;
             }
             default:
-                accepted = op_alter(d, sp, k, op, key, step, ll, prior, sh, tm, &sh.u_ahead[0][ia], synced);
+                accepted = op_alter(d, sp, k, op, key, step, ll, prior, sh, tm, &sh.u_ahead[0][ia], synced, st.err + chain);
                 break;
         }
         // the source sweep has ONE call site (gibbs_sample_sources and every accepted zone move): it is the largest
         // block of code of the kernel
         if (need_sweep) {
             resample_sources(d, k, key, step, sh, tm, ll, ll_stale);
+            if (sp.from_prior) ll = 0.0;
             synced = true;
         }
         PROF_T(ts2);
@@ -1232,41 +1332,34 @@ mcmc_step_kernel(DevData d, ChainArrays st, StepParams sp, long long n_steps) {
         PROF_T(ts3);
         PROF_ADD(4, ts0, ts1); PROF_ADD(5, ts1, ts2); PROF_ADD(6, ts2, ts3);
     }
+    if (ev >= sp.n_events) break;
+    // ---- host-visible event after `it` completed steps: (ll, prior) of the chain, optionally a snapshot of its
+    // state into the ring -- the launch goes on (generate_samples logs without ending the persistent kernel)
+    {
+        __syncthreads();                // the warps may arrive from barrier-free Gibbs steps
+        if (dirty) { team_sync(tm); dirty = false; }
+        if (ll_stale && !sp.from_prior) { ll = ll_from_counts(d, k, sh, tm); ll_stale = false; }
+        prior += team_sum(prior_acc, sh, tm);
+        prior_acc = 0.0;
+        const int n_chains = (int)(gridDim.x / sp.team);
+        if (threadIdx.x == 0 && tm.rank == 0) sp.ev_scalars[(size_t)ev * n_chains + chain] = make_double2(ll, prior);
+        const int slot = sp.events[ev].y;
+        if (slot >= 0 && (sp.ring_chain < 0 || sp.ring_chain == chain))
+            snapshot_state(d, st, sp, chain, slot, n_chains, tm);
+        ++ev;
+        team_sync(tm);                  // the copy read the whole state: done before the next step writes
+    }
+    }
     __syncthreads();            // the warps may arrive from barrier-free Gibbs steps
-    if (ll_stale) ll = ll_from_counts(d, k, sh, tm);       // reads this CTA's own feature range only
+    if (ll_stale && !sp.from_prior) ll = ll_from_counts(d, k, sh, tm);       // reads this CTA's own feature range only
     prior += team_sum(prior_acc, sh, tm);
     if (threadIdx.x == 0 && tm.rank == 0) {
         st.ll[chain] = ll; st.prior[chain] = prior; st.geo[chain] = geo;
         st.step[chain] = step0 + (uint64_t)n_steps;
+        // NaN (or +inf) in the running values: a Gamma draw that exhausted its attempts returns NaN, a NaN weight row
+        // poisons the likelihood -- surfaced by sb_read_chain_scalars / sb_chain_errors (SB_E_NUMERIC)
+        if (!(ll == ll) || !(prior == prior) || ll == INFINITY || prior == INFINITY) atomicOr(st.err + chain, SB_ERR_NONFINITE);
     }
     if (tm.size > 1) cg::this_cluster().sync();         // keep every CTA's shared memory alive until the last peer read
 }
 
-// ---- forced zone move: (log_q, log_q_back) without touching the state (parity of :704-933) --------
-__global__ void __launch_bounds__(STEP_THREADS)
-move_log_q_kernel(DevData d, ChainArrays st, StepParams sp, int chain, int kind, int z, int site_new,
-                  int site_removed, double rho, double* out) {
-    extern __shared__ unsigned char step_smem[];
-    __shared__ StepShared sh;
-    unsigned* nbr = reinterpret_cast<unsigned*>(step_smem);
-    const Chain k = chain_view(st, sp, chain);
-    const int size = k.zsize[z];
-    const int* mem = k.members + (size_t)z * d.N;
-    int n_occ = 0;
-    for (int i = 0; i < d.Z; ++i) n_occ += k.zsize[i];
-    const int n_free = d.N - n_occ;
-    double q, q_back;
-    if (kind != SB_OP_SHRINK_ZONE) {
-        build_nbr_bits(d.adj_ptr, d.adj_idx, k.zone_id, mem, size, -1, nbr, sp.nwords);
-        const int n_nbr = bits_count(nbr, sp.nwords, sh.redi);
-        q = grow_q(bit_test(nbr, site_new), n_free, n_nbr, rho);
-        q_back = kind == SB_OP_GROW_ZONE ? 1.0 / (double)(size + 1) : grow_q(false, n_free, n_nbr, rho);
-    } else {
-        q = 1.0 / (double)size;
-        build_nbr_bits(d.adj_ptr, d.adj_idx, k.zone_id, mem, size, site_removed, nbr, sp.nwords);
-        const int n_nbr = bits_count(nbr, sp.nwords, sh.redi);
-        q_back = grow_q(bit_test(nbr, site_removed), n_free + 1, n_nbr, rho);
-        if (d.warmup) q_back = 1.0 / (double)(size + 1);
-    }
-    if (threadIdx.x == 0) { out[0] = log(q); out[1] = log(q_back); }
-}

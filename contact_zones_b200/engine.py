@@ -230,6 +230,14 @@ class Engine:
                                            int(site_removed), float(p_grow_connected), C.byref(lq), C.byref(lqb)))
         return lq.value, lqb.value
 
+    def pair_log_q(self, c0, c1, n0, n1, precision):
+        """log_q - log_q_back of `dirichlet_proposal` (zone_sampling.py:538-569) for a forced new pair, evaluated by the
+        step kernel's own pair-proposal code."""
+        out = C.c_double()
+        self._check(self.lib.sb_pair_log_q(self._ctx, float(c0), float(c1), float(n0), float(n1), float(precision),
+                                           C.byref(out)))
+        return out.value
+
     def rng_sample(self, kind, n, alpha=1.0, seed=0):
         """n draws of the device generator: kind 'uniform', 'gamma', 'normal' (the Gamma sampler's candidates) or
         'flog' (K6 parity surface)."""
@@ -267,6 +275,45 @@ class Engine:
 
     def run(self, n_steps):
         self._check(self.lib.sb_run(self._ctx, int(n_steps)))
+
+    def set_sample_from_prior(self, on=True):
+        self._check(self.lib.sb_set_sample_from_prior(self._ctx, int(bool(on))))
+
+    def run_events(self, n_steps, event_steps, event_slots, ring_chain=-1):
+        """One persistent launch of `n_steps` steps with host-visible events inside it: after `event_steps[k]` completed
+        steps every chain records (ll, prior); `event_slots[k]` >= 0 also snapshots the state of `ring_chain` (-1 = of
+        every chain) into that slot of the device ring.  Asynchronous."""
+        es = np.ascontiguousarray(event_steps, dtype=np.int32)
+        sl = np.ascontiguousarray(event_slots, dtype=np.int32)
+        assert es.shape == sl.shape
+        self._check(self.lib.sb_run_events(self._ctx, int(n_steps), int(es.size), ptr(es), ptr(sl), int(ring_chain)))
+
+    def ring_record_bytes(self):
+        """Bytes of one snapshot record (sb_step.cuh:snapshot_state): zone ids + weights + the three p tables."""
+        a16 = (lambda v: (v + 15) & ~15)
+        fs = self.F * self.S
+        return (a16((self.N + 15) & ~15) + a16(self.F * 3 * 8) + a16(fs * 8) + a16(self.Z * fs * 8) +
+                a16(self.Fam * fs * 8))
+
+    def event_scalars(self, n_events):
+        ll, pr = np.zeros((n_events, self.n_chains)), np.zeros((n_events, self.n_chains))
+        self._check(self.lib.sb_read_event_scalars(self._ctx, int(n_events), ptr(ll), ptr(pr)))
+        return ll, pr
+
+    def read_snapshot(self, slot, chain):
+        zones = np.zeros((self.Z, self.N), np.uint8)
+        w = np.zeros((self.F, self.C))
+        pg = np.zeros((1, self.F, self.S))
+        pz = np.zeros((self.Z, self.F, self.S))
+        pf = np.zeros((self.Fam, self.F, self.S)) if self.inheritance else None
+        self._check(self.lib.sb_read_snapshot(self._ctx, int(slot), int(chain), ptr(zones), ptr(w), ptr(pg), ptr(pz), ptr(pf)))
+        return {'zones': zones.astype(bool), 'weights': w, 'p_global': pg, 'p_zones': pz, 'p_families': pf,
+                'source': None}
+
+    def chain_errors(self):
+        e = np.zeros(self.n_chains, np.int32)
+        self._check(self.lib.sb_chain_errors(self._ctx, ptr(e)))
+        return e
 
     def chain_scalars(self):
         ll, pr = np.zeros(self.n_chains), np.zeros(self.n_chains)

@@ -63,6 +63,28 @@ class ChainShard:
         pr = np.concatenate([out[r, 1, :self.counts[r]] for r in range(self.world)])
         return ll, pr
 
+    def all_gather_events(self, ll_local, prior_local, device=None):
+        """The batched form: (n_events, n_local) arrays of every rank -> (n_events, n_chains), ONE collective for all
+        the events of a persistent launch (16 B per chain and event)."""
+        ll_local, prior_local = np.asarray(ll_local, float), np.asarray(prior_local, float)
+        dist = _dist()
+        if dist is None or self.world == 1:
+            return ll_local.copy(), prior_local.copy()
+        import torch
+        e, m = ll_local.shape[0], max(self.counts)
+        buf = np.zeros((2, e, m))
+        buf[0, :, :self.n_local] = ll_local
+        buf[1, :, :self.n_local] = prior_local
+        t = torch.from_numpy(buf.ravel())
+        if device is not None:
+            t = t.to(device)
+        out = torch.empty(self.world * t.numel(), dtype=torch.float64, device=t.device)
+        dist.all_gather_into_tensor(out, t)
+        out = out.cpu().numpy().reshape(self.world, 2, e, m)
+        ll = np.concatenate([out[r, 0, :, :self.counts[r]] for r in range(self.world)], axis=1)
+        pr = np.concatenate([out[r, 1, :, :self.counts[r]] for r in range(self.world)], axis=1)
+        return ll, pr
+
     def broadcast_state(self, chain, arrays_local, template, device=None):
         """Every rank gets the state arrays of global `chain` from its owner (one broadcast of the packed arrays:
         ~0.4 MB at shape D, only at the N_SAMPLES logging points).  `arrays_local`: callable evaluated on the owner

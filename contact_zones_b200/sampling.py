@@ -105,8 +105,6 @@ class ZoneMCMC(object):
     def __init__(self, var_proposal, p_grow_connected, initial_size, initial_sample=None, *, model, data, operators,
                  n_chains, mc3=False, swap_period=None, chain_swaps=None, sample_from_prior=False,
                  show_screen_log=False, logger=None, seed=None, **kwargs):
-        if sample_from_prior:
-            raise NotImplementedError('sample_from_prior is not available on the device sampler')
         self.model, self.data = model, data
         self.n_chains = n_chains
         self.chain_idx = list(range(n_chains))
@@ -293,6 +291,8 @@ class ZoneMCMC(object):
                               n_chains=self.shard.n_local, with_cost=kw['geo_type'] == 'cost_based',
                               warmup=self.IS_WARMUP, chain_offset=self.shard.offset, pooled=False)
         eng.set_priors(**kw)
+        if self.sample_from_prior:          # mcmc_generative.py:115-116: the likelihood is identically 0
+            eng.set_sample_from_prior(True)
         self._engine = eng
         if self.shard.world > 1:
             import torch
@@ -342,7 +342,29 @@ class ZoneMCMC(object):
 
     def _refresh_scalars(self):
         ll, pr = self._engine.chain_scalars()
+        if self.sample_from_prior:
+            ll = np.zeros_like(ll)
         self._ll, self._prior = self.shard.all_gather_scalars(ll, pr, self._dist_device)
+
+    # events per persistent launch / bytes of snapshot ring per launch (the ring holds one record per logged sample
+    # and resident chain under MC3, one per logged sample otherwise)
+    MAX_EVENTS_PER_LAUNCH = 4096
+    RING_BYTES_PER_LAUNCH = 256 << 20
+
+    def _snapshot_sample(self, slot, chain):
+        """The logged `Sample` of GLOBAL chain `chain` from snapshot `slot` of its owner's ring, on every rank."""
+        eng = self._engine
+        owner, local = self.shard.owner(chain)
+
+        def local_arrays():
+            st = eng.read_snapshot(slot, local)
+            d = {'zones': st['zones'], 'weights': st['weights'], 'p_global': st['p_global'], 'p_zones': st['p_zones']}
+            if self.inheritance:
+                d['p_families'] = st['p_families']
+            return d
+
+        a = self.shard.broadcast_state(chain, local_arrays, self._template(False), self._dist_device)
+        return Sample(a['zones'], a['weights'], a['p_global'], a['p_zones'], a.get('p_families'), source=None, chain=chain)
 
     # evaluation API of the reference sampler (mcmc_generative.py:86-126)
     def prior(self, sample, chain):
@@ -415,21 +437,56 @@ class ZoneMCMC(object):
         swap_at = set(range(self.swap_period, n_steps + 1, self.swap_period)) if self.mc3 else set()
         screen_at = set(range(1000, n_steps + 1, 1000)) if self.show_screen_log else set()
         stops = sorted(set(log_at) | swap_at | screen_at | {n_steps})
+        # The steps between two host-visible events never end the persistent launch: one launch covers as many events
+        # as its snapshot ring holds (`sb_run_events`); (ll, prior) of every chain is recorded at each event and the
+        # logged chain's state at each logging point.  Without MC3 the logged chain never changes, so only that chain
+        # is snapshotted; with MC3 the label moves at the swap points, which are replayed on the host afterwards from
+        # the recorded scalars -- every chain snapshots and the host reads the one that carried label 0.
+        eng = self._engine
+        n_local = max(1, self.shard.n_local)
+        per_log = eng.ring_record_bytes() * (n_local if self.mc3 else 1)
+        max_logs = max(1, self.RING_BYTES_PER_LAUNCH // max(1, per_log))
+        ring_chain = -1
+        if not self.mc3:
+            owner, local = self.shard.owner(self.chain_idx[0])
+            ring_chain = local if owner == self.shard.rank else None
         done = 0
-        for t in stops:
-            eng.run(t - done)
-            done = t
-            if t in log_at or t in swap_at or t in screen_at or t == n_steps:
-                self._refresh_scalars()                     # (ll, prior) of every chain after t steps
-            if t in log_at:
-                c0 = self.chain_idx[0]
-                self.log_sample_statistics(self._fetch_sample(c0, with_source=False), c=c0, sample_id=log_at[t])
-            if t in swap_at:
-                self.swap_chains(None)
-            if t in screen_at:
-                self.print_screen_log(t, None)
-            if t == n_steps and n_steps > 1:
-                self.log_last_sample(self._fetch_sample(self.chain_idx[0], with_source=True))
+        i = 0
+        while i < len(stops):
+            batch, n_logs = [], 0
+            while i < len(stops) and len(batch) < self.MAX_EVENTS_PER_LAUNCH:
+                t = stops[i]
+                if t in log_at and n_logs == max_logs:
+                    break
+                batch.append(t)
+                n_logs += t in log_at
+                i += 1
+            slots, k = [], 0
+            for t in batch:
+                if t in log_at and ring_chain is not None:
+                    slots.append(k)
+                    k += 1
+                else:
+                    slots.append(-1)
+            eng.run_events(batch[-1] - done, [t - done for t in batch], slots, -1 if ring_chain is None else ring_chain)
+            ll_ev, pr_ev = eng.event_scalars(len(batch))
+            if self.sample_from_prior:
+                ll_ev = np.zeros_like(ll_ev)
+            ll_ev, pr_ev = self.shard.all_gather_events(ll_ev, pr_ev, self._dist_device)
+            k = 0
+            for j, t in enumerate(batch):
+                self._ll, self._prior = ll_ev[j], pr_ev[j]                 # (ll, prior) of every chain after t steps
+                if t in log_at:
+                    c0 = self.chain_idx[0]
+                    self.log_sample_statistics(self._snapshot_sample(k, c0), c=c0, sample_id=log_at[t])
+                    k += 1
+                if t in swap_at:
+                    self.swap_chains(None)
+                if t in screen_at:
+                    self.print_screen_log(t, None)
+            done = batch[-1]
+        if n_steps > 1:
+            self.log_last_sample(self._fetch_sample(self.chain_idx[0], with_source=True))
         eng.sync()
         t_end = time.time()
         self._collect_operator_stats(eng, base)

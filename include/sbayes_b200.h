@@ -36,7 +36,17 @@ enum {
     SB_E_CUDA = -2,       /* CUDA runtime error (message in sb_last_error) */
     SB_E_STATE = -3,      /* call order (data / state / operators not set) */
     SB_E_OVERLAP = -4,    /* sb_set_state: overlapping zones (quirk Q7)    */
-    SB_E_NOGPU = -5       /* no CUDA device                                */
+    SB_E_NOGPU = -5,      /* no CUDA device                                */
+    SB_E_NUMERIC = -6     /* a chain carries a sticky SB_ERR_* flag (sb_chain_errors) */
+};
+
+/* sticky per-chain error flags raised by the step kernel.  The reference's counterparts: the NaN / Inf warning and
+ * `assert 0 < q` of dirichlet_proposal (zone_sampling.py:559-567), the ValueError of random.sample(states, 2) on a
+ * feature with one applicable state (:471, 512, 588), the ValueError of geo_prior_distance (model.py:1134-1135). */
+enum {
+    SB_ERR_NONFINITE = 1, /* NaN or +inf in the running log-likelihood / log-prior (incl. an exhausted Gamma sampler) */
+    SB_ERR_GEO_CAP = 2,   /* last zone outgrew the geo prior's member scratch (state uploaded after sb_set_operators) */
+    SB_ERR_NAPP = 4       /* alter_p_* picked a feature with fewer than 2 applicable states (step rejected)           */
 };
 
 /* sb_create flags */
@@ -167,10 +177,16 @@ int sb_source_posterior(sb_ctx* ctx, int chain, double* post /* (N,F,C) */);
 int sb_counts(sb_ctx* ctx, int chain, int recount, int32_t* cnt_glob, int32_t* cnt_zone, int32_t* cnt_fam,
               int32_t* cnt_src_zone, int32_t* cnt_src_fam);
 
-/* ---- zone-move proposal probabilities for a forced move (parity of zone_sampling.py:704-933) ----
- * kind: SB_OP_GROW_ZONE / SB_OP_SHRINK_ZONE / SB_OP_SWAP_ZONE; unused site = -1.  Does not modify state. */
+/* ---- zone-move proposal probabilities for a forced move (parity of zone_sampling.py:704-933, warm-up :1328-1574) ----
+ * kind: SB_OP_GROW_ZONE / SB_OP_SHRINK_ZONE / SB_OP_SWAP_ZONE; unused site = -1.  Does not modify state.
+ * Runs the step kernel itself (same set-up, same proposal code as a sampling launch) with the zone and the sites
+ * given instead of drawn. */
 int sb_move_log_q(sb_ctx* ctx, int chain, int kind, int zone, int site_new, int site_removed,
                   double p_grow_connected, double* log_q, double* log_q_back);
+/* log_q - log_q_back of dirichlet_proposal (zone_sampling.py:538-569) for a forced new pair: the current pair (c0, c1)
+ * of weights / probabilities, the proposed pair (n0, n1) with n0 + n1 = c0 + c1, the proposal precision -- evaluated by
+ * the code alter_weights / alter_p_* use inside the step kernel (:408-612). */
+int sb_pair_log_q(sb_ctx* ctx, double c0, double c1, double n0, double n1, double precision, double* log_q_ratio);
 
 /* ---- sampler: MCMCGenerative.step / generate_samples (mcmc_generative.py:149-351) ---------------- */
 int sb_set_operators(sb_ctx* ctx, const sb_operator_cfg* cfg,
@@ -178,7 +194,21 @@ int sb_set_operators(sb_ctx* ctx, const sb_operator_cfg* cfg,
                      const int32_t* max_size);        /* (n_chains) MAX_M / warm-up list :1280-1285 */
 /* Run n_steps MH steps on every resident chain in one persistent launch (kernel K8). Asynchronous. */
 int sb_run(sb_ctx* ctx, int64_t n_steps);
-int sb_read_chain_scalars(sb_ctx* ctx, double* ll, double* prior);              /* (n_chains) each */
+/* sample_from_prior of MCMCGenerative (mcmc_generative.py:115-116): the likelihood is identically 0 in every
+ * Metropolis ratio and in the logged values.  Takes effect at the next sb_run. */
+int sb_set_sample_from_prior(sb_ctx* ctx, int on);
+/* The same launch with host-visible EVENTS inside it (generate_samples' logging and MC3 swap points,
+ * mcmc_generative.py:205-231) instead of one launch per event: after event_steps[k] completed steps of this launch
+ * (ascending, 1 <= step <= n_steps) every chain records (ll, prior); if event_slots[k] >= 0 the state of chain
+ * `ring_chain` (-1 = of every chain: under MC3 the logged label moves between chains) is copied into snapshot slot
+ * event_slots[k] of a device ring.  Asynchronous; read with sb_read_event_scalars / sb_read_snapshot. */
+int sb_run_events(sb_ctx* ctx, int64_t n_steps, int n_events, const int32_t* event_steps, const int32_t* event_slots,
+                  int ring_chain);
+int sb_read_event_scalars(sb_ctx* ctx, int n_events, double* ll, double* prior);   /* (n_events, n_chains) each */
+int sb_read_snapshot(sb_ctx* ctx, int slot, int chain, uint8_t* zones, double* weights, double* p_global,
+                     double* p_zones, double* p_families /* any may be NULL */);
+int sb_read_chain_scalars(sb_ctx* ctx, double* ll, double* prior);              /* (n_chains) each; SB_E_NUMERIC if flagged */
+int sb_chain_errors(sb_ctx* ctx, int32_t* flags);                                /* (n_chains) SB_ERR_* bits, sticky until sb_set_state */
 int sb_read_op_stats(sb_ctx* ctx, int64_t* accepted, int64_t* rejected);        /* (n_chains, SB_N_OPS) each */
 int sb_step_counter(sb_ctx* ctx, int64_t* steps_done);                          /* per context      */
 int sb_kernel_launches(sb_ctx* ctx, int64_t* launches);                         /* launches issued so far */

@@ -237,6 +237,8 @@ def main(cases):
             zones=st['zones'], weights=st['weights'], p_global=st['p_global'], p_zones=st['p_zones'],
             n_steps=np.int64(c['n_steps']), n_samples=np.int64(c['n_samples']), op_names=np.array(names),
             max_m=np.int64(c.get('max_m', 30)),
+            scale_universal=np.float64(np.nan if c.get('scales', (10., 10.))[0] is None else c.get('scales', (10., 10.))[0]),
+            scale_inheritance=np.float64(np.nan if c.get('scales', (10., 10.))[1] is None else c.get('scales', (10., 10.))[1]),
             op_weights=np.array([so.default_operators(c['inh'], c['src'], c['steps'])[k] for k in names]),
             precision=np.array([c['precision'][k] for k in ('weights', 'universal', 'contact', 'inheritance')], float),
             m_initial=np.int64(c['m_initial']), n_chains=np.int64(c.get('n_chains', 1)),

@@ -24,4 +24,5 @@ def built_lib():
 
 
 def golden_cases():
-    return sorted(f[:-4] for f in os.listdir(GOLDEN) if f.endswith('.npz') and not f.startswith('run_'))
+    """The fixed-state cases `A_...` .. `G_...` (oracle/make_golden.py); run_*, results_*, ops, swaps are other fixtures."""
+    return sorted(f[:-4] for f in os.listdir(GOLDEN) if f.endswith('.npz') and f[0].isupper() and f[1] == '_')

@@ -63,6 +63,13 @@ def set_golden_state(eng, c, chain=0, with_source=True):
 # ---- posterior-summary fixtures of the reference sampler (oracle/make_golden_runs.py) -------------------------
 PRECISION = {'weights': 15, 'universal': 40, 'contact': 20, 'inheritance': 20}
 RUN_KEYS = ['zone_size', 'planted_occ', 'w_comp', 'll_mean', 'prior_mean', 'acc']
+# the per-site / per-feature summaries north_star names ("zone membership frequencies, weight means"): one comparison
+# per site, per (feature, component), per (feature, state)
+VECTOR_KEYS = ['occ_freq', 'w_mean', 'pg_mean']
+# spread floors of the vector statistics: a site that no run of either side ever visits (or always holds) has zero
+# spread on both sides; differences below 1 % occupancy / 0.004 in a mean weight or probability are not resolved by
+# runs of this length
+VECTOR_FLOOR = {'occ_freq': 1e-2, 'w_mean': 4e-3, 'pg_mean': 4e-3}
 
 
 def run_cases():
@@ -80,10 +87,17 @@ def load_run(name):
     c['families'] = g['families'].astype(bool)
     c['adj'] = csr_matrix((np.ones(len(g['adj_indices']), dtype=np.int64), g['adj_indices'], g['adj_indptr']), shape=(n, n))
     c['cost'] = g['cost'] if g['cost'].size else None
+    if 'locations' in g and c['geo_type'] == 'cost_based':
+        # the fixture keeps the site locations; the cost matrix is their Euclidean distance matrix
+        # (simulation.py:155-156, checked bit for bit when the fixture was written)
+        from scipy.spatial.distance import cdist
+        c['cost'] = cdist(g['locations'], g['locations'])
     c['Z'] = g['zones'].shape[0]
     c['C'] = 3 if c['inheritance'] else 2
     c['p_families'] = g['p_families'] if c['inheritance'] else None
     c['operators'] = {str(k): float(v) for k, v in zip(g['op_names'], g['op_weights'])}
+    c['precision'] = (dict(zip(('weights', 'universal', 'contact', 'inheritance'), (float(v) for v in g['precision'])))
+                      if 'precision' in g else dict(PRECISION))
     c['prior_cfg'] = {
         'geo': {'type': c['geo_type'], 'scale': c['geo_scale']}, 'area_size': {'type': c['size_type']},
         'weights': {'type': 'uniform'}, 'contact': {'type': 'uniform'},
@@ -92,13 +106,45 @@ def load_run(name):
     return c
 
 
-def summarise_run(zones, weights, ll, prior, acc, planted, burn):
-    """The label-switching-invariant scalars of oracle/make_golden_runs.py:summarise for one chain."""
+def summarise_run(zones, weights, ll, prior, acc, planted, burn, p_global=None):
+    """The label-switching-invariant summaries of oracle/make_golden_runs.py:summarise for one chain."""
     zones, weights = np.asarray(zones)[burn:], np.asarray(weights)[burn:]
     occ = zones.any(axis=1)
-    return {'zone_size': occ.sum(axis=1).mean(), 'planted_occ': occ[:, planted].mean(),
-            'w_comp': weights.mean(axis=(0, 1)), 'll_mean': np.mean(np.asarray(ll)[burn:]),
-            'prior_mean': np.mean(np.asarray(prior)[burn:]), 'acc': np.asarray(acc, dtype=float)}
+    out = {'zone_size': occ.sum(axis=1).mean(), 'planted_occ': occ[:, planted].mean(),
+           'w_comp': weights.mean(axis=(0, 1)), 'll_mean': np.mean(np.asarray(ll)[burn:]),
+           'prior_mean': np.mean(np.asarray(prior)[burn:]), 'acc': np.asarray(acc, dtype=float),
+           'occ_freq': occ.mean(axis=0), 'w_mean': weights.mean(axis=0)}
+    if p_global is not None:
+        pg = np.asarray(p_global)[burn:]
+        out['pg_mean'] = pg.mean(axis=0)[0] if pg.ndim == 4 else pg.mean(axis=0)
+    return out
+
+
+def vector_z_scores(c, chains, keys=None):
+    """Per-element Welch z of the mean over `chains` against the reference runs' mean for the per-site / per-feature
+    summaries, with the bar that belongs to the number of comparisons: `max|z|` must stay below the two-sided
+    Student-t quantile at a family-wise 1e-3 (Bonferroni over the K elements, Welch-Satterthwaite degrees of freedom
+    of the least favourable element), and the mean of z^2 -- which a bias confined to a few sites or features moves
+    little but a diffuse bias moves a lot -- below 3.  Returns {key: (max|z|, bar, mean z^2)}."""
+    from scipy import stats
+    g = c['g']
+    out = {}
+    for k in (keys or VECTOR_KEYS):
+        if 'ref_' + k not in g or k not in chains[0]:
+            continue
+        ref = np.asarray(g['ref_' + k], dtype=float)
+        ours = np.stack([np.asarray(s[k], dtype=float) for s in chains])
+        ref, ours = ref.reshape(len(ref), -1), ours.reshape(len(ours), -1)
+        n1, n2 = len(ref), len(ours)
+        floor = VECTOR_FLOOR[k]
+        rs = np.maximum(ref.std(0, ddof=1), floor)
+        os_ = np.maximum(ours.std(0, ddof=1), floor)
+        a, b = rs ** 2 / n1, os_ ** 2 / n2
+        z = np.abs(ours.mean(0) - ref.mean(0)) / np.sqrt(a + b)
+        df = (a + b) ** 2 / (a ** 2 / (n1 - 1) + b ** 2 / (n2 - 1))
+        bar = float(stats.t.ppf(1.0 - 1e-3 / (2 * z.size), df.min()))
+        out[k] = (float(z.max()), bar, float(np.mean(z ** 2)))
+    return out
 
 
 def run_z_scores(c, chains):

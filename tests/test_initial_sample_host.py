@@ -60,6 +60,7 @@ def test_unknown_operator_is_an_error():
     with pytest.raises(AttributeError):
         ZoneMCMC(data=data, model=model, operators={'teleport_zone': 0.5}, var_proposal=PRECISION,
                  p_grow_connected=0.85, initial_size=5, n_chains=1)
-    with pytest.raises(NotImplementedError):
-        ZoneMCMC(data=data, model=model, operators={'grow_zone': 1.}, var_proposal=PRECISION, p_grow_connected=0.85,
-                 initial_size=5, n_chains=1, sample_from_prior=True)
+    # sample_from_prior is part of the constructor contract (mcmc_generative.py:33-36, 115-116): likelihood() is 0
+    smp = ZoneMCMC(data=data, model=model, operators={'grow_zone': 1.}, var_proposal=PRECISION, p_grow_connected=0.85,
+                   initial_size=5, n_chains=1, sample_from_prior=True)
+    assert smp.sample_from_prior and smp.likelihood(None, 0) == 0.
