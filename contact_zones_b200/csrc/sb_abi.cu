@@ -1031,6 +1031,21 @@ int sb_source_posterior(sb_ctx* ctx, int chain, double* post) {
     return run_components(ctx, chain, nullptr, nullptr, post);
 }
 
+int sb_recount_async(sb_ctx* ctx, int chain_begin, int n) {
+    if (!ctx) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    int r = check_range(ctx, chain_begin, n, 1);
+    if (r != SB_OK) return r;
+    return recount_chains(ctx, chain_begin, n);
+}
+
+int sb_device_scalars(sb_ctx* ctx, void** ll, void** prior) {
+    if (!ctx) return SB_E_ARG;
+    if (ll) *ll = ctx->st.ll;
+    if (prior) *prior = ctx->st.prior;
+    return SB_OK;
+}
+
 int sb_counts(sb_ctx* ctx, int chain, int recount, int32_t* cnt_glob, int32_t* cnt_zone, int32_t* cnt_fam,
               int32_t* cnt_src_zone, int32_t* cnt_src_fam) {
     if (!ctx) return SB_E_ARG;

@@ -63,6 +63,7 @@ class Engine:
         self.C = 3 if inheritance else 2
         self.n_chains = int(n_chains)
         self.chain_offset = int(chain_offset)
+        self.device = int(device)
         flags = ((_lib.SB_F_INHERITANCE if inheritance else 0) | (_lib.SB_F_SAMPLE_SOURCE if sample_source else 0) |
                  (_lib.SB_F_WARMUP if warmup else 0))
         dims = SbDims(self.N, self.F, self.S, self.Z, self.Fam, self.n_chains, self.chain_offset, flags)
@@ -223,6 +224,23 @@ class Engine:
         csf = np.zeros((self.F, self.C), np.int32)
         self._check(self.lib.sb_counts(self._ctx, int(chain), int(recount), ptr(cg), ptr(cz), ptr(cf), ptr(csz), ptr(csf)))
         return {'cnt_glob': cg, 'cnt_zone': cz, 'cnt_fam': cf, 'cnt_src_zone': csz, 'cnt_src_fam': csf}
+
+    def recount_async(self, chain_begin=0, n_chains=None):
+        n = self.n_chains - chain_begin if n_chains is None else int(n_chains)
+        self._check(self.lib.sb_recount_async(self._ctx, int(chain_begin), n))
+
+    def device_scalars(self):
+        """(ll, prior) of the resident chains as zero-copy torch views of the context's device arrays."""
+        import torch
+        a, b = C.c_void_p(), C.c_void_p()
+        self._check(self.lib.sb_device_scalars(self._ctx, C.byref(a), C.byref(b)))
+
+        class _Dev:
+            def __init__(self, addr, n):
+                self.__cuda_array_interface__ = {'shape': (n,), 'typestr': '<f8', 'data': (addr, False), 'version': 2}
+        dev = torch.device('cuda', self.device)
+        return (torch.as_tensor(_Dev(a.value, self.n_chains), device=dev),
+                torch.as_tensor(_Dev(b.value, self.n_chains), device=dev))
 
     def move_log_q(self, chain, kind, zone, site_new=-1, site_removed=-1, p_grow_connected=0.85):
         lq, lqb = C.c_double(), C.c_double()

@@ -63,6 +63,29 @@ class ChainShard:
         pr = np.concatenate([out[r, 1, :self.counts[r]] for r in range(self.world)])
         return ll, pr
 
+    def all_gather_device(self, ll_dev, prior_dev, out_row, scratch):
+        """The same exchange without a host hop: `ll_dev` / `prior_dev` are device tensors (the context's own running
+        arrays, `Engine.device_scalars`), `scratch` a persistent (2 * max_local) device buffer and `out_row` a persistent
+        (world * 2 * max_local) device buffer -- two tiny device copies and ONE all-gather on the current stream;
+        `unpack_gathered` turns rows read back later into per-chain arrays."""
+        m = max(self.counts)
+        scratch[:self.n_local].copy_(ll_dev)
+        scratch[m:m + self.n_local].copy_(prior_dev)
+        dist = _dist()
+        if dist is None or self.world == 1:
+            out_row.copy_(scratch)
+        else:
+            dist.all_gather_into_tensor(out_row, scratch)
+
+    def unpack_gathered(self, rows):
+        """rows: (..., world * 2 * max_local) host array -> (ll, prior) of shape (..., n_chains)."""
+        rows = np.asarray(rows)
+        m = max(self.counts)
+        r = rows.reshape(rows.shape[:-1] + (self.world, 2, m))
+        ll = np.concatenate([r[..., k, 0, :self.counts[k]] for k in range(self.world)], axis=-1)
+        pr = np.concatenate([r[..., k, 1, :self.counts[k]] for k in range(self.world)], axis=-1)
+        return ll, pr
+
     def all_gather_events(self, ll_local, prior_local, device=None):
         """The batched form: (n_events, n_local) arrays of every rank -> (n_events, n_chains), ONE collective for all
         the events of a persistent launch (16 B per chain and event)."""

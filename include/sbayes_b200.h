@@ -174,6 +174,9 @@ int sb_source_posterior(sb_ctx* ctx, int chain, double* post /* (N,F,C) */);
  * cnt_fam  (Fam,F,S)  :389-400                     cnt_src_zone (F,C) :239-240,256-257
  * cnt_src_fam (F,C)   :283-284
  * recount != 0 recomputes from the resident source state; 0 returns the incrementally maintained tables. */
+/* launch-only full recount (kernel K4) of chains [chain_begin, chain_begin + n_chains) for timing with device-resident
+ * inputs (no D2H, no synchronisation) */
+int sb_recount_async(sb_ctx* ctx, int chain_begin, int n_chains);
 int sb_counts(sb_ctx* ctx, int chain, int recount, int32_t* cnt_glob, int32_t* cnt_zone, int32_t* cnt_fam,
               int32_t* cnt_src_zone, int32_t* cnt_src_fam);
 
@@ -208,6 +211,9 @@ int sb_read_event_scalars(sb_ctx* ctx, int n_events, double* ll, double* prior);
 int sb_read_snapshot(sb_ctx* ctx, int slot, int chain, uint8_t* zones, double* weights, double* p_global,
                      double* p_zones, double* p_families /* any may be NULL */);
 int sb_read_chain_scalars(sb_ctx* ctx, double* ll, double* prior);              /* (n_chains) each; SB_E_NUMERIC if flagged */
+/* DEVICE addresses of the running (ll, prior) arrays, n_chains doubles each, valid until sb_destroy: the MC3 exchange
+ * (mcmc_generative.py:242-280) all-gathers them with NCCL on the context's stream without a host hop */
+int sb_device_scalars(sb_ctx* ctx, void** ll, void** prior);
 int sb_chain_errors(sb_ctx* ctx, int32_t* flags);                                /* (n_chains) SB_ERR_* bits, sticky until sb_set_state */
 int sb_read_op_stats(sb_ctx* ctx, int64_t* accepted, int64_t* rejected);        /* (n_chains, SB_N_OPS) each */
 int sb_step_counter(sb_ctx* ctx, int64_t* steps_done);                          /* per context      */
