@@ -43,6 +43,7 @@ struct sb_ctx {
     double* lt_partial = nullptr;    // [n_chains][lt.n_tiles * lt.n_chunks]
     unsigned* lt_ticket = nullptr;   // [n_chains]
     long lt_want = 148L * 14;        // CTA target of one K1 launch (SB_K1_CTAS overrides, for tuning)
+    long lt_want_compact = 148L * 7; // the same for shapes with one site per code byte (SB_K1_CTAS_COMPACT; 444..2072 measured)
     std::vector<int> h_gclass;       // host copy of lt.group_class (class span of a group range)
     int geo_cap = 0;                 // capacity (members) of the Prim scratch
     int64_t launches = 0;
@@ -147,6 +148,7 @@ int sb_create(sb_ctx** out, int device, const sb_dims* dims) {
     ctx->device = device;
     ctx->dims = *dims;
     if (const char* e = getenv("SB_K1_CTAS")) ctx->lt_want = std::max(1L, atol(e));
+    if (const char* e = getenv("SB_K1_CTAS_COMPACT")) ctx->lt_want_compact = std::max(1L, atol(e));
     *out = ctx;   // returned even on failure so that the caller can read sb_last_error, then sb_destroy
     CK(cudaSetDevice(device));
     CK(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
@@ -778,7 +780,9 @@ static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source
         // correction, reduction); measured best on B200 (scripts/gpu_k1_sweep.sh) at about two waves of
         // 148 SMs x 7 resident CTAs, each walking all groups of its split for its feature chunk
         const int n_tiles = (t.n_groups + LT_THREADS - 1) / LT_THREADS;
-        const long want = ctx->lt_want;
+        // compact rows (one site per code byte): every CTA rebuilds the rows of ALL family classes of its feature chunk,
+        // so fewer, fatter chunks win (shape D: 17 chunks of 12 features, 77 us, against 34 chunks of 6 with 256-byte rows, 96 us)
+        const long want = t.cpb == 1 ? std::min(ctx->lt_want, ctx->lt_want_compact) : ctx->lt_want;
         const int fc_min = std::min(d.F, 4);
         int chunks = (int)std::min<long>((d.F + fc_min - 1) / fc_min, std::max<long>(1, (want + n - 1) / n));
         t.n_splits = (int)std::min<long>(n_tiles, std::max<long>(1, (want + (long)chunks * n - 1) / ((long)chunks * n)));
@@ -790,12 +794,12 @@ static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source
             t.max_cls = std::max(t.max_cls, ctx->h_gclass[g1 - 1] - ctx->h_gclass[g0] + 1);
         }
         t.fc = std::max(1, (d.F + chunks - 1) / chunks);
-        while (t.fc > 1 && lt_smem_bytes(t.fc, t.max_cls, d.S) > 46 * 1024) --t.fc;
+        while (t.fc > 1 && lt_smem_bytes(t.fc, t.max_cls, d.S, t.cpb == 1) > 46 * 1024) --t.fc;
         // (hundreds of family classes in one split: even one feature's rows do not fit -> tile-per-site kernel below)
-        const bool tables_fit = lt_smem_bytes(t.fc, t.max_cls, d.S) <= 46 * 1024;
+        const bool tables_fit = lt_smem_bytes(t.fc, t.max_cls, d.S, t.cpb == 1) <= 46 * 1024;
         if (tables_fit) {
         t.n_chunks = (d.F + t.fc - 1) / t.fc;
-        t.smem = std::max(lt_smem_bytes(t.fc, t.max_cls, d.S), (size_t)std::min(d.F, LT_CORR_FB) * 12 * sizeof(double));
+        t.smem = std::max(lt_smem_bytes(t.fc, t.max_cls, d.S, t.cpb == 1), (size_t)std::min(d.F, LT_CORR_FB) * 12 * sizeof(double));
         // blockIdx.z < n_corr: correction CTAs (zone members), scheduled first, concurrent with the streaming CTAs
         // (one is enough once the streaming pass dominates: 96.7 vs 99.1 us at N = 20000)
         const int n_corr = d.Z > 0 ? (d.N >= 16384 ? 1 : std::max(1, LT_CORR_CTAS / t.n_splits)) : 0;
@@ -910,7 +914,7 @@ int sb_eval_likelihood_noalloc(sb_ctx* ctx, int chain_begin, int n, double* ll_o
     // launch geometry of the table-driven K1, as in launch_likelihood
     LhTab t = ctx->lt;
     const int n_tiles = (t.n_groups + LT_THREADS - 1) / LT_THREADS;
-    const long want = ctx->lt_want;
+    const long want = t.cpb == 1 ? std::min(ctx->lt_want, ctx->lt_want_compact) : ctx->lt_want;
     const int fc_min = std::min(d.F, 4);
     const int chunks = (int)std::min<long>((d.F + fc_min - 1) / fc_min, std::max<long>(1, (want + n - 1) / n));
     t.n_splits = (int)std::min<long>(n_tiles, std::max<long>(1, (want + (long)chunks * n - 1) / ((long)chunks * n)));
@@ -922,11 +926,11 @@ int sb_eval_likelihood_noalloc(sb_ctx* ctx, int chain_begin, int n, double* ll_o
         t.max_cls = std::max(t.max_cls, ctx->h_gclass[g1 - 1] - ctx->h_gclass[g0] + 1);
     }
     t.fc = std::max(1, (d.F + chunks - 1) / chunks);
-    while (t.fc > 1 && lt_smem_bytes(t.fc, t.max_cls, d.S) > 46 * 1024) --t.fc;
-    if (lt_smem_bytes(t.fc, t.max_cls, d.S) > 46 * 1024)
+    while (t.fc > 1 && lt_smem_bytes(t.fc, t.max_cls, d.S, t.cpb == 1) > 46 * 1024) --t.fc;
+    if (lt_smem_bytes(t.fc, t.max_cls, d.S, t.cpb == 1) > 46 * 1024)
         FAIL(SB_E_ARG, "sb_eval_likelihood_noalloc: the family-class tables of one feature exceed shared memory");
     t.n_chunks = (d.F + t.fc - 1) / t.fc;
-    t.smem = std::max(lt_smem_bytes(t.fc, t.max_cls, d.S), (size_t)std::min(d.F, LT_CORR_FB) * 12 * sizeof(double));
+    t.smem = std::max(lt_smem_bytes(t.fc, t.max_cls, d.S, t.cpb == 1), (size_t)std::min(d.F, LT_CORR_FB) * 12 * sizeof(double));
     const int n_corr = d.Z > 0 ? (d.N >= 16384 ? 1 : std::max(1, LT_CORR_CTAS / t.n_splits)) : 0;
     if (t.n_chunks + n_corr > 65535) FAIL(SB_E_ARG, "sb_eval_likelihood_noalloc: more than 65535 feature chunks");
     const size_t parts = (size_t)t.n_splits * (t.n_chunks + n_corr);
@@ -1172,7 +1176,11 @@ static int configure_step(sb_ctx* ctx, int cap) {
     }
     if (d.sample_source && !sp.work_counts) team = 1;     // the global-atomics source sweep is single-CTA
     if (team > 8) CK(cudaFuncSetAttribute(mcmc_step_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-    while (team > 1) {      // the hardware must be able to co-schedule the cluster
+    // every chain's cluster must be resident at once: clusters live inside one GPC (~18 SMs on B200), so e.g. 16 teams of
+    // 8 do NOT fit although 128 <= 148 SMs -- a second wave doubles the launch time (measured: 16 chains, team 8 -> 3.2 us
+    // per step against 1.8 us for team 4).  An explicit SBAYES_B200_TEAM keeps its value as long as ONE cluster fits.
+    const int need_clusters = getenv("SBAYES_B200_TEAM") ? 1 : nc;
+    while (team > 1) {
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned)(nc * team), 1, 1);
         cfg.blockDim = dim3(STEP_THREADS, 1, 1);
@@ -1182,7 +1190,8 @@ static int configure_step(sb_ctx* ctx, int cap) {
         attr[0].val.clusterDim.x = (unsigned)team; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr; cfg.numAttrs = 1;
         int n_clusters = 0;
-        if (cudaOccupancyMaxActiveClusters(&n_clusters, mcmc_step_kernel, &cfg) == cudaSuccess && n_clusters >= 1) break;
+        if (cudaOccupancyMaxActiveClusters(&n_clusters, mcmc_step_kernel, &cfg) == cudaSuccess &&
+            n_clusters >= std::min(need_clusters, sms / team)) break;
         cudaGetLastError();
         team >>= 1;
     }

@@ -46,11 +46,14 @@ __host__ __device__ __forceinline__ size_t lt_off_val(int fc) { return ((size_t)
 __host__ __device__ __forceinline__ size_t lt_off_tab(int fc, int max_cls, int S) {
     return (lt_off_val(fc) + (size_t)max_cls * fc * (S + 1) * 8 + 255) & ~(size_t)255;
 }
-__host__ __device__ __forceinline__ size_t lt_off_slow(int fc, int max_cls, int S) {
-    return lt_off_tab(fc, max_cls, S) + (size_t)max_cls * fc * 2 * LT_ROW * 4;
+// One site per code byte (S + 1 > 5, `compact`): the value array IS the table -- rows of S + 1 doubles read with one
+// LDS.64 -- so the 32-entry hi / lo rows (256 B for S + 1 used entries) are not allocated: 3.5x less shared memory per
+// row at S = 8, i.e. 3.5x more features per CTA and 3.5x fewer CTAs that rebuild the rows of every family class.
+__host__ __device__ __forceinline__ size_t lt_off_slow(int fc, int max_cls, int S, bool compact = false) {
+    return lt_off_tab(fc, max_cls, S) + (compact ? 0 : (size_t)max_cls * fc * 2 * LT_ROW * 4);
 }
-__host__ __device__ __forceinline__ size_t lt_smem_bytes(int fc, int max_cls, int S) {
-    return lt_off_slow(fc, max_cls, S) + (((size_t)max_cls * fc + 15) & ~(size_t)15);
+__host__ __device__ __forceinline__ size_t lt_smem_bytes(int fc, int max_cls, int S, bool compact = false) {
+    return lt_off_slow(fc, max_cls, S, compact) + (((size_t)max_cls * fc + 15) & ~(size_t)15);
 }
 
 __device__ __forceinline__ double lt_free_value(const DevData& d, const double* __restrict__ wn12,
@@ -88,6 +91,25 @@ __device__ __forceinline__ void lt_unit(const uint4 xv, uint32_t row, double& m,
         }
     }
     m = m0;
+}
+
+// the same for one site per code byte and rows of S + 1 doubles (the code byte holds 4 * digit)
+__device__ __forceinline__ void lt_unit_compact(const uint4 xv, uint32_t row, double& m, int& e) {
+    const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+    double m0 = m, m1 = 1.0;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        const uint32_t byte = __byte_perm(xw[j >> 2], 0u, 0x4440 + (j & 3));
+        double tv;
+        asm("ld.shared.f64 %0, [%1];" : "=d"(tv) : "r"(row + 2u * byte));
+        if (j & 1) m1 *= tv; else m0 *= tv;
+    }
+    // 8 factors >= 2^-60 per partial product on top of a mantissa in [1, 4): no underflow before the merge
+    const int h0 = __double2hiint(m0), h1 = __double2hiint(m1);
+    e += ((h0 >> 20) & 0x7ff) + ((h1 >> 20) & 0x7ff) - 2046;
+    m0 = __hiloint2double((h0 & 0x800fffff) | 0x3ff00000, __double2loint(m0));
+    m1 = __hiloint2double((h1 & 0x800fffff) | 0x3ff00000, __double2loint(m1));
+    m = m0 * m1;
 }
 
 // Correction CTA: zone members, + log prod mix_zone - log prod v_free over the member's non-NA cells.  CTA `idx` of
@@ -229,8 +251,12 @@ lh_table_kernel(DevData d, ChainArrays st, LhTab t, int chain_begin, double* __r
     double* wn = reinterpret_cast<double*>(lt_smem);
     double* val = reinterpret_cast<double*>(lt_smem + lt_off_val(t.fc));
     uint32_t* tab = reinterpret_cast<uint32_t*>(lt_smem + lt_off_tab(t.fc, t.max_cls, S));
-    unsigned char* slow = lt_smem + lt_off_slow(t.fc, t.max_cls, S);
-    const uint32_t tab_s = (uint32_t)__cvta_generic_to_shared(tab);
+    constexpr bool COMPACT = CPB == 1;
+    unsigned char* slow = lt_smem + lt_off_slow(t.fc, t.max_cls, S, COMPACT);
+    // compact: rows of S + 1 doubles inside `val`, laid out [class][nf]; else 256-byte hi / lo rows laid out [class][fc]
+    const uint32_t tab_s = (uint32_t)__cvta_generic_to_shared(COMPACT ? (void*)val : (void*)tab);
+    const uint32_t row_b = COMPACT ? (uint32_t)S1 * 8u : 2u * LT_ROW * 4u;
+    const uint32_t cls_rows = COMPACT ? (uint32_t)nf : (uint32_t)t.fc;
 
     const double* __restrict__ w = st.weights + chain * st.s_weights;
     const double* __restrict__ pg = st.p_global + chain * st.s_p_global;
@@ -253,6 +279,7 @@ lh_table_kernel(DevData d, ChainArrays st, LhTab t, int chain_begin, double* __r
         val[i] = v;
     }
     const int any_slow = __syncthreads_or(tiny);
+    if (!COMPACT)
     for (int i = threadIdx.x; i < ncls * nf * LT_ROW; i += LT_THREADS) {
         const int r = i / LT_ROW, code = i - r * LT_ROW, ci = r / nf, fi = r - ci * nf;
         if (code >= t.row_entries) continue;
@@ -279,7 +306,7 @@ lh_table_kernel(DevData d, ChainArrays st, LhTab t, int chain_begin, double* __r
     for (int g = g0 + threadIdx.x; g < g1; g += LT_THREADS) {
         const int ci = t.group_class[g] - c_lo;
         const uint8_t* __restrict__ xp = t.xcode + (size_t)g * 16 + (size_t)f0 * xstride;
-        uint32_t row = tab_s + (uint32_t)(ci * t.fc) * (2 * LT_ROW * 4);
+        uint32_t row = tab_s + (uint32_t)ci * cls_rows * row_b;
         if (!any_slow) {
             uint4 buf[PF];
 #pragma unroll
@@ -296,8 +323,9 @@ lh_table_kernel(DevData d, ChainArrays st, LhTab t, int chain_begin, double* __r
                         const uint4 xv = buf[k];
                         if (fb + k + PF < nf) buf[k] = __ldg(reinterpret_cast<const uint4*>(xp));
                         xp += xstride;
-                        lt_unit<CPB>(xv, row, m, e);
-                        row += 2 * LT_ROW * 4;
+                        if (COMPACT) lt_unit_compact(xv, row, m, e);
+                        else lt_unit<CPB>(xv, row, m, e);
+                        row += row_b;
                     }
                 }
             }
@@ -306,9 +334,11 @@ lh_table_kernel(DevData d, ChainArrays st, LhTab t, int chain_begin, double* __r
             continue;
         }
         // general path (some row of this CTA holds a tiny / zero value)
-        for (int fi = 0; fi < nf; ++fi, row += 2 * LT_ROW * 4) {
+        for (int fi = 0; fi < nf; ++fi, row += row_b) {
             if (!slow[ci * nf + fi]) {
-                lt_unit<CPB>(__ldg(reinterpret_cast<const uint4*>(xp + (size_t)fi * xstride)), row, acc.m, acc.e);
+                const uint4 xv = __ldg(reinterpret_cast<const uint4*>(xp + (size_t)fi * xstride));
+                if (COMPACT) lt_unit_compact(xv, row, acc.m, acc.e);
+                else lt_unit<CPB>(xv, row, acc.m, acc.e);
                 continue;
             }
             for (int q = 0; q < t.G; ++q) {
