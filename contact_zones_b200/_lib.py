@@ -28,7 +28,7 @@ SB_ERR_NONFINITE, SB_ERR_GEO_CAP, SB_ERR_NAPP = 1, 2, 4
 # every symbol include/sbayes_b200.h declares (tests/test_abi_symbols.py checks the .so exports them all)
 SYMBOLS = [
     'sb_version', 'sb_device_count', 'sb_create', 'sb_destroy', 'sb_last_error', 'sb_set_stream', 'sb_sync',
-    'sb_upload_data', 'sb_set_priors', 'sb_set_state', 'sb_set_states', 'sb_get_state', 'sb_copy_state',
+    'sb_upload_data', 'sb_upload_locations', 'sb_set_priors', 'sb_set_state', 'sb_set_states', 'sb_get_state', 'sb_copy_state',
     'sb_eval', 'sb_eval_likelihood_async', 'sb_read_ll', 'sb_eval_likelihood_noalloc', 'sb_eval_components', 'sb_source_posterior',
     'sb_counts', 'sb_recount_async', 'sb_device_scalars', 'sb_move_log_q', 'sb_pair_log_q', 'sb_set_operators', 'sb_run', 'sb_set_sample_from_prior',
     'sb_run_events', 'sb_read_event_scalars', 'sb_read_snapshot', 'sb_read_chain_scalars', 'sb_chain_errors',
@@ -79,6 +79,7 @@ def load():
         'sb_destroy': ([vp], i32), 'sb_last_error': ([vp], C.c_char_p),
         'sb_set_stream': ([vp, vp], i32), 'sb_sync': ([vp], i32),
         'sb_upload_data': ([vp] + [vp] * 6, i32),
+        'sb_upload_locations': ([vp, vp], i32),
         'sb_set_priors': ([vp, C.POINTER(SbPriorCfg)] + [vp] * 4, i32),
         'sb_set_state': ([vp, i32] + [vp] * 6, i32),
         'sb_set_states': ([vp, i32, i32] + [vp] * 6, i32),

@@ -9,7 +9,7 @@ from .mcmc_setup import MCMC
 
 
 def run_experiment(experiment, data, run):
-    mcmc = MCMC(data=data, experiment=experiment)
+    mcmc = MCMC(data=data, experiment=experiment, run=run)
     mcmc.log_setup()
     mcmc.warm_up()
     mcmc.sample()

@@ -371,6 +371,19 @@ int sb_upload_data(sb_ctx* ctx, const uint8_t* x, const uint8_t* applicable, con
     return SB_OK;
 }
 
+int sb_upload_locations(sb_ctx* ctx, const double* xy) {
+    if (!ctx || !xy) return SB_E_ARG;
+    CK(cudaSetDevice(ctx->device));
+    if (!ctx->has_data) FAIL(SB_E_STATE, "sb_upload_data must precede sb_upload_locations");
+    for (int i = 0; i < 2 * ctx->d.N; ++i)
+        if (!std::isfinite(xy[i])) FAIL(SB_E_ARG, "non-finite site coordinate");
+    double* dloc;
+    DA(dloc, (size_t)2 * ctx->d.N);
+    H2D(dloc, xy, (size_t)2 * ctx->d.N);
+    ctx->d.loc = dloc;
+    return SB_OK;
+}
+
 int sb_set_priors(sb_ctx* ctx, const sb_prior_cfg* cfg, const double* gibbs_g, const double* alpha_g,
                   const double* gibbs_f, const double* alpha_f) {
     if (!ctx || !cfg) return SB_E_ARG;
@@ -380,7 +393,8 @@ int sb_set_priors(sb_ctx* ctx, const sb_prior_cfg* cfg, const double* gibbs_g, c
     if (cfg->size_type < 0 || cfg->size_type > 2 || cfg->geo_type < 0 || cfg->geo_type > 1 ||
         cfg->p_global_type < 0 || cfg->p_global_type > 1 || cfg->p_families_type < 0 || cfg->p_families_type > 1)
         FAIL(SB_E_ARG, "unknown prior type");
-    if (cfg->geo_type == SB_GEO_COST_BASED && !d.cost) FAIL(SB_E_ARG, "cost_based geo prior needs a cost matrix");
+    if (cfg->geo_type == SB_GEO_COST_BASED && !d.cost && !d.loc)
+        FAIL(SB_E_ARG, "cost_based geo prior needs a cost matrix (sb_upload_data) or site locations (sb_upload_locations)");
     if (cfg->geo_type == SB_GEO_COST_BASED && !(cfg->geo_scale > 0)) FAIL(SB_E_ARG, "geo scale must be > 0");
     if (cfg->p_global_type == SB_DIR_COUNTS && !alpha_g) FAIL(SB_E_ARG, "alpha_global required");
     if (d.inheritance && cfg->p_families_type == SB_DIR_COUNTS && !alpha_f) FAIL(SB_E_ARG, "alpha_fam required");

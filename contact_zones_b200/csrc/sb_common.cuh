@@ -37,6 +37,7 @@ struct DevData {
     const int* adj_ptr;
     const int* adj_idx;
     const double* cost;         // may be null
+    const double* loc;          // [N][2] site coordinates: implicit Euclidean cost when `cost` is null (may be null)
     // priors
     int size_type, geo_type, pg_type, pf_type;
     double geo_scale;

@@ -209,7 +209,16 @@ __device__ __forceinline__ double dirichlet_row(const double* __restrict__ p, co
 // CTA.  Returns (sum of non-zero MST edge costs, their number) -- scipy's sparse MST result drops zero-weight
 // edges (model.py:1125-1131), infinite entries are non-edges (csgraph_from_dense(null_value=inf)).
 // key/intree: shared scratch for M entries.
-__device__ void prim_mst(const double* __restrict__ cost, int N, const int* __restrict__ members, int M,
+// Cost of the edge (a, b).  Dense form: the symmetric minimum of the two matrix entries.  Implicit form (no N x N
+// matrix, f3): the Euclidean distance of the site coordinates -- what the reference's `dist_mat` holds when the cost
+// matrix is the network's distance matrix (simulation.py:155-156, preprocessing.py:101-174 without a CRS); the
+// multiplications and the sum are rounded separately (no FMA contraction), like scipy's cdist.
+__device__ __forceinline__ double geo_cost(const double* __restrict__ cost, const double* __restrict__ loc, int N, int a, int b) {
+    if (cost) return fmin(cost[(size_t)a * N + b], cost[(size_t)b * N + a]);
+    const double dx = loc[2 * a] - loc[2 * b], dy = loc[2 * a + 1] - loc[2 * b + 1];
+    return sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+}
+__device__ void prim_mst(const double* __restrict__ cost, const double* __restrict__ loc, int N, const int* __restrict__ members, int M,
                          double* key, unsigned char* intree, double* red, int* redi,
                          double* out_sum, int* out_cnt) {
     for (int j = threadIdx.x; j < M; j += blockDim.x) { key[j] = INFINITY; intree[j] = 0; }
@@ -226,8 +235,7 @@ __device__ void prim_mst(const double* __restrict__ cost, int N, const int* __re
         int besti = -1;
         for (int j = threadIdx.x; j < M; j += blockDim.x) {
             if (intree[j]) continue;
-            const double a = cost[(size_t)mc * N + members[j]], b = cost[(size_t)members[j] * N + mc];
-            const double cst = fmin(a, b);
+            const double cst = geo_cost(cost, loc, N, mc, members[j]);
             double k = key[j];
             if (cst < k) { k = cst; key[j] = k; }
             if (besti < 0 || k < best) { best = k; besti = j; }
@@ -309,7 +317,7 @@ prior_kernel(DevData d, ChainArrays st, int chain_begin, int geo_cap) {
         double* key = reinterpret_cast<double*>(smem_raw);
         unsigned char* intree = smem_raw + (size_t)geo_cap * sizeof(double);
         double sum; int cnt;
-        prim_mst(d.cost, d.N, st.zone_members + chain * st.s_zone_members + (size_t)z * d.N, M,
+        prim_mst(d.cost, d.loc, d.N, st.zone_members + chain * st.s_zone_members + (size_t)z * d.N, M,
                  key, intree, red, redi, &sum, &cnt);
         // mean_e expon.logpdf(cost_e, scale) = -log(scale) - mean(cost_e)/scale ; none -> -log(scale)
         geo = cnt > 0 ? (-(double)cnt * log(d.geo_scale) - sum / d.geo_scale) / (double)cnt : -log(d.geo_scale);

@@ -631,7 +631,7 @@ __device__ __forceinline__ double size_prior_of(const DevData& d, const int* zsi
 __device__ double geo_prior_of(const DevData& d, const int* members, int M, double* key, unsigned char* intree,
                                StepShared& sh) {
     double sum; int cnt;
-    prim_mst(d.cost, d.N, members, M, key, intree, sh.red, sh.redi, &sum, &cnt);
+    prim_mst(d.cost, d.loc, d.N, members, M, key, intree, sh.red, sh.redi, &sum, &cnt);
     return cnt > 0 ? (-(double)cnt * log(d.geo_scale) - sum / d.geo_scale) / (double)cnt : -log(d.geo_scale);
 }
 

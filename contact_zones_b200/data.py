@@ -101,7 +101,11 @@ def compute_delaunay(locations):
 class compute_network:
     """`preprocessing.compute_network` (:101-174): a dict-like network with the keys the sampler reads."""
 
-    def __init__(self, sites, subset=None, crs=None):
+    # above this number of sites the dense N x N distance matrix (8 N^2 bytes: 3.2 GB at N = 20000) is not built unless
+    # asked for; the geo prior then works on the site coordinates (implicit Euclidean cost, `sb_upload_locations`)
+    DENSE_LIMIT = 8192
+
+    def __init__(self, sites, subset=None, crs=None, dense_distances=None):
         if crs is not None:
             raise ImportError("Using a coordinate reference system (crs) requires the cartopy / pyproj libraries, "
                               "which are not available in this build")
@@ -120,7 +124,11 @@ class compute_network:
         self.n = len(vertices)
         self.m = self.edges.shape[0]
         loc = np.asarray(sites['locations'])
-        self.dist_mat = np.linalg.norm(loc[:, None] - loc, axis=-1)
+        if dense_distances is None:
+            dense_distances = len(loc) <= self.DENSE_LIMIT
+        # (row by row: the broadcast form needs a second N x N x 2 temporary)
+        self.dist_mat = (np.stack([np.sqrt(((loc - p) ** 2).sum(axis=1)) for p in loc]) if dense_distances and len(loc)
+                         else None)
 
     def __getitem__(self, key):
         return getattr(self, key)
@@ -236,7 +244,7 @@ class Data:
          self.family_names, self.log_load_features, self.features_idx) = read_features_from_csv(
             file=self.config['data']['FEATURES'], feature_states_file=self.config['data']['FEATURE_STATES'],
             return_index=True)
-        self.network = compute_network(self.sites, crs=self.crs)
+        self.network = compute_network(self.sites, crs=self.crs, dense_distances=self.config['data'].get('DENSE_DISTANCES'))
 
     def load_universal_counts(self):
         cfg = self.config['model']['PRIOR']['universal']
@@ -264,6 +272,11 @@ class Data:
             return
         if 'file' not in geo:
             cost = self.network['dist_mat']
+            if cost is None:
+                # no dense matrix (data.DENSE_DISTANCES = false, or more than compute_network.DENSE_LIMIT sites): the
+                # device derives the same Euclidean costs from the coordinates
+                self.geo_prior = {'cost_matrix': None, 'locations': np.asarray(self.network['locations'], float)}
+                return
         else:
             cost, self.log_load_geo_cost_matrix = read_geo_cost_matrix(site_names=self.site_names, file=geo['file'])
         self.geo_prior = {'cost_matrix': cost}

@@ -32,8 +32,14 @@ def engine_for(data, n_zones, inheritance, sample_source, n_chains=1, with_cost=
     if pooled and key in _POOL:
         return _POOL[key][0]
     cost = cost_matrix_of(data) if with_cost else None
+    locations = None
     if with_cost and cost is None:
-        raise KeyError('cost_matrix')        # the reference fails the same way at model.py:1009
+        # no dense matrix: the implicit Euclidean cost over the site coordinates, if the data object carries them
+        # (`Data.load_geo_cost_matrix` with DENSE_DISTANCES = false)
+        gp = getattr(data, 'geo_prior', None)
+        locations = gp.get('locations') if isinstance(gp, dict) else None
+        if locations is None:
+            raise KeyError('cost_matrix')        # the reference fails the same way at model.py:1009
     network = getattr(data, 'network', None)
     adj = network['adj_mat'] if network else None
     states = getattr(data, 'states', None)       # test/test_model.py:76-80 passes a stub with features + families only
@@ -44,7 +50,7 @@ def engine_for(data, n_zones, inheritance, sample_source, n_chains=1, with_cost=
         feats = data.features
     eng = Engine(feats, states, data.families if inheritance else None, adj, cost,
                  n_zones=n_zones, n_chains=n_chains, inheritance=inheritance, sample_source=sample_source, warmup=warmup,
-                 device=device, chain_offset=chain_offset)
+                 device=device, chain_offset=chain_offset, locations=locations)
     eng.prior_token = None
     if pooled:
         _POOL[key] = (eng, data)             # keeping `data` alive pins id(data)

@@ -24,14 +24,13 @@ def state_index(features):
 
 
 def family_index(families, n_sites):
-    """bool (Fam,N) -> int16 (N) family id, -1 = none.  A site in two families is rejected (the reference lets
-    the later family overwrite, `model.py:427-431`)."""
+    """bool (Fam,N) -> int16 (N) family id, -1 = none.  A site listed in several (nested) families belongs to the
+    LAST of them, as in the reference: `compute_family_likelihood` writes `lh_families[families[fam]]` family by
+    family, so the later one overwrites (`model.py:427-431`)."""
     fid = np.full(n_sites, -1, dtype=np.int16)
     if families is None:
         return fid
     fam = np.asarray(families, dtype=bool)
-    if fam.size and fam.sum(axis=0).max() > 1:
-        raise ValueError('a site belongs to more than one family')
     for k in range(fam.shape[0]):
         fid[fam[k]] = k
     return fid
@@ -48,7 +47,7 @@ def pack_source(source, n_components):
 
 class Engine:
     def __init__(self, features, states, families=None, adj_mat=None, cost_matrix=None, *, n_zones, n_chains=1,
-                 inheritance=False, sample_source=False, warmup=False, device=0, chain_offset=0):
+                 inheritance=False, sample_source=False, warmup=False, device=0, chain_offset=0, locations=None):
         self.lib = _lib.load()
         self._ctx = C.c_void_p()
         x = state_index(features)
@@ -87,7 +86,11 @@ class Engine:
         cost = as_c(cost_matrix, np.float64)
         xs, st = as_c(x, np.uint8), as_c(states, np.uint8)
         self._check(self.lib.sb_upload_data(self._ctx, ptr(xs), ptr(st), ptr(fid), ptr(indptr), ptr(indices), ptr(cost)))
-        self.has_cost = cost is not None
+        if cost is None and locations is not None:
+            # implicit Euclidean cost matrix of the geo prior: N x 2 coordinates instead of N x N doubles
+            loc = as_c(np.asarray(locations, dtype=np.float64).reshape(self.N, 2), np.float64)
+            self._check(self.lib.sb_upload_locations(self._ctx, ptr(loc)))
+        self.has_cost = cost is not None or locations is not None
         self.set_priors()
 
     # -- plumbing ---------------------------------------------------------------------------------

@@ -12,8 +12,9 @@ from .sampling import Sample, ZoneMCMC, ZoneMCMCWarmup
 class MCMC:
     """mcmc_setup.py:18-234.  `experiment` needs `.config`, `.path_results` (pathlib.Path) and `.logger`."""
 
-    def __init__(self, data, experiment):
+    def __init__(self, data, experiment, run=0):
         self.data = data
+        self.run = int(run)             # index of the run (cli.py: `for run in range(N_RUNS)`): part of the sub-seeds
         self.config = experiment.config
         self.path_log = experiment.path_results / 'experiment.log'
         self.path_results = experiment.path_results
@@ -61,13 +62,22 @@ class MCMC:
                     f'{kind}_p_zones': steps['contact'], f'{kind}_p_families': steps['inheritance']})
         self.ops = ops
 
-    def _sampler_kwargs(self):
+    def _sampler_kwargs(self, phase):
+        """`phase` 0 = warm-up, 1 = sampling.  The config's SEED (an extension over the reference, which seeds nothing)
+        is not handed to the samplers as it is: the device RNG is Philox keyed by (seed, chain) with a step counter that
+        restarts at 0 in every sampler, so warm-up and sampling -- and every run of N_RUNS, every value of N_AREAS --
+        would replay the same streams.  Each sampler instance gets its own sub-seed instead."""
         c = self.config['mcmc']
         kw = dict(data=self.data, model=self.model, operators=self.ops, var_proposal=c['PROPOSAL_PRECISION'],
                   p_grow_connected=c['P_GROW_CONNECTED'], initial_size=c['M_INITIAL'], logger=self.logger)
         if c.get('SEED') is not None:
-            kw['seed'] = c['SEED']
+            kw['seed'] = self.sub_seed(c['SEED'], self.run, self.config['model']['N_AREAS'], phase)
         return kw
+
+    @staticmethod
+    def sub_seed(seed, run, n_areas, phase):
+        ss = np.random.SeedSequence([int(seed), int(run), int(n_areas), int(phase)])
+        return int(ss.generate_state(1, dtype=np.uint64)[0] >> np.uint64(1))
 
     def sample(self, lh_per_area=True, initial_sample=None):
         c = self.config['mcmc']
@@ -76,7 +86,7 @@ class MCMC:
         mc3 = c.get('MC3') or {}
         self.sampler = ZoneMCMC(n_chains=c.get('N_CHAINS', 1), initial_sample=initial_sample,
                                 mc3=bool(mc3.get('ACTIVATE', False)), swap_period=mc3.get('SWAP_PERIOD'),
-                                chain_swaps=mc3.get('N_SWAPS'), **self._sampler_kwargs())
+                                chain_swaps=mc3.get('N_SWAPS'), **self._sampler_kwargs(phase=1))
         self.sampler.generate_samples(c['N_STEPS'], c['N_SAMPLES'])
         if lh_per_area:
             contribution_per_area(self.sampler)
@@ -111,7 +121,7 @@ class MCMC:
 
     def warm_up(self):
         c = self.config['mcmc']
-        warmup = ZoneMCMCWarmup(n_chains=c['WARM_UP']['N_WARM_UP_CHAINS'], **self._sampler_kwargs())
+        warmup = ZoneMCMCWarmup(n_chains=c['WARM_UP']['N_WARM_UP_CHAINS'], **self._sampler_kwargs(phase=0))
         self.sample_from_warm_up = warmup.generate_samples(n_steps=0, n_samples=0, warm_up=True,
                                                            warm_up_steps=c['WARM_UP']['N_WARM_UP_STEPS'])
         warmup.close()

@@ -469,7 +469,7 @@ class GeoPrior(object):
             self.prior_type = self.TYPES.UNIFORM
         elif config['type'] == 'cost_based':
             self.prior_type = self.TYPES.COST_BASED
-            self.cost_matrix = self.data.geo_prior['cost_matrix']
+            self.cost_matrix = self.data.geo_prior['cost_matrix']         # None: implicit (site coordinates), f3
             self.scale = config['scale']
         else:
             raise ValueError('Geo prior not supported')

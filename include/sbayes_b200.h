@@ -121,6 +121,11 @@ int sb_upload_data(sb_ctx* ctx,
                    const int32_t* adj_indptr,   /* (N+1)  network['adj_mat'] CSR (util.py:139-155)     */
                    const int32_t* adj_indices,  /* (nnz)                                               */
                    const double* cost);         /* (N,N)  geo_prior['cost_matrix'] or NULL             */
+/* Site coordinates (N,2) for the IMPLICIT cost matrix of the cost_based geo prior: cost(i, j) = Euclidean distance of
+ * the sites -- exactly the `dist_mat` the reference uses as cost matrix when no cost file is given
+ * (simulation.py:155-156, load_data.py:116-132 -> preprocessing.py:101-174), without its O(N^2) memory (3.2 GB at
+ * N = 20000).  Used when sb_upload_data got no dense cost matrix. */
+int sb_upload_locations(sb_ctx* ctx, const double* xy);
 int sb_set_priors(sb_ctx* ctx, const sb_prior_cfg* cfg,
                   const double* gibbs_counts_global,  /* (F,S)     prior_p_global.counts   (model.py:577,585)  or NULL = 1 */
                   const double* alpha_global,         /* (F,S)     Dirichlet density alpha (util.py:589-623)   or NULL     */

@@ -134,3 +134,16 @@ def test_loader_matches_reference_on_balkan():
     io_, _ = D.read_inheritance_counts(ours[7], ours[3], ours[4], files, 'counts_file', fs)
     it, _ = rp.read_inheritance_counts(theirs[7], theirs[3], theirs[4], files, 'counts_file', fs)
     assert np.array_equal(io_, it)
+
+
+def test_network_without_dense_distances():
+    """compute_network(dense_distances=False): no N x N matrix; `Data.load_geo_cost_matrix` then hands the site
+    coordinates to the geo prior (implicit Euclidean cost)."""
+    from contact_zones_b200.data import compute_network
+    rng = np.random.default_rng(1)
+    loc = rng.random((40, 2)) * 100
+    sites = {'id': list(range(40)), 'locations': loc, 'names': [f's{i}' for i in range(40)]}
+    dense = compute_network(sites)
+    lean = compute_network(sites, dense_distances=False)
+    assert lean['dist_mat'] is None and (lean['adj_mat'] != dense['adj_mat']).nnz == 0
+    assert np.array_equal(dense['dist_mat'], np.linalg.norm(loc[:, None] - loc, axis=-1))

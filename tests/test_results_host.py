@@ -86,3 +86,22 @@ def test_max_size_list_matches_reference_formula():
     got = get_max_size_list(start=(5 + 50) / 4, end=50, n_total=15, k_groups=4)
     assert got == [13] * 4 + [22] * 4 + [31] * 4 + [40] * 3
     assert len(get_max_size_list(10, 30, 3, 4)) == 3
+
+
+def test_sub_seeds_differ_per_sampler_instance():
+    """The config's SEED is expanded into one sub-seed per (run, N_AREAS, phase): warm-up and sampling, the runs of
+    N_RUNS and the values of an N_AREAS list never replay each other's device streams."""
+    from contact_zones_b200.mcmc_setup import MCMC
+    seen = {MCMC.sub_seed(7, run, z, phase) for run in range(4) for z in range(1, 5) for phase in (0, 1)}
+    assert len(seen) == 32 and all(0 <= v < 2 ** 63 for v in seen)
+    assert MCMC.sub_seed(7, 1, 3, 1) == MCMC.sub_seed(7, 1, 3, 1) != MCMC.sub_seed(8, 1, 3, 1)
+
+
+def test_overlapping_families_last_one_wins():
+    """A site listed in two (nested) families belongs to the later one, like the reference's
+    compute_family_likelihood (model.py:427-431), instead of being rejected."""
+    from contact_zones_b200.engine import family_index
+    fam = np.zeros((3, 6), bool)
+    fam[0, :4] = True
+    fam[1, 2:5] = True
+    assert list(family_index(fam, 6)) == [0, 0, 1, 1, 1, -1]

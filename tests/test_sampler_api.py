@@ -102,6 +102,28 @@ def test_mcmc_facade_writes_reference_files(built_lib, tmp_path):
     assert z.shape == (c['Z'], c['N']) and int(row['size_a0']) == z[0].sum()
 
 
+def test_seed_is_expanded_per_run_and_phase(built_lib, tmp_path):
+    """Same SEED: the same run index reproduces the files byte for byte, another run index gives another chain, and
+    the sampling phase does not replay the warm-up's streams (sub-seeds per sampler instance)."""
+    from contact_zones_b200.mcmc_setup import MCMC
+    c = load_case('B_balkan_like')
+    data = case_data(c)
+    outs = []
+    for tag, run in (('a', 0), ('b', 0), ('c', 1)):
+        cfg = {'model': case_model_config(c), 'mcmc': _mcmc_config(600, 6), 'results': {'FILE_INFO': 'n'}}
+        d = tmp_path / tag
+        d.mkdir()
+        mc = MCMC(data, SimpleNamespace(config=cfg, path_results=pathlib.Path(d), logger=logging.getLogger('t')), run=run)
+        mc.warm_up()
+        mc.sample()
+        mc.save_samples(run=run)
+        mc.sampler.close()
+        fi = f"n{c['Z']}"
+        outs.append((d / fi / f'stats_{fi}_{run}.txt').read_bytes())
+        assert mc._sampler_kwargs(0)['seed'] != mc._sampler_kwargs(1)['seed']
+    assert outs[0] == outs[1] and outs[0] != outs[2]
+
+
 def test_cli_end_to_end(built_lib, tmp_path):
     """`python -m contact_zones_b200 config.json` on a CSV dataset: counts priors, cost-based geo prior from a cost
     file, inheritance, warm-up, sampling, result files (sbayes/cli.py:30-84)."""

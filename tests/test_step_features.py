@@ -192,3 +192,66 @@ def test_error_flags_reach_the_caller(built_lib):
     eng.set_state(0, st['zones'], st['weights'], pg, pz)              # a new state clears the chain's flags
     assert list(eng.chain_errors()) == [0, SB_ERR_NAPP]
     eng.close()
+
+
+def test_implicit_cost_matrix_equals_dense(built_lib):
+    """the cost_based geo prior without the dense N x N matrix.  With the site coordinates
+    (`sb_upload_locations`) the device derives the Euclidean costs itself: same prior values as with the dense
+    `dist_mat` the reference uses (simulation.py:155-156), same sampler trajectory."""
+    from contact_zones_b200 import synthetic
+    from contact_zones_b200.engine import Engine
+    data = synthetic.make_data(300, 20, 4, n_families=3, seed=9, with_dist=True, planted_zones=2, planted_size=10)
+    loc, dense = data.network['locations'], data.geo_prior['cost_matrix']
+    engs = [Engine(data.features, data.states, data.families, data.network['adj_mat'], dense, n_zones=2, n_chains=4,
+                   inheritance=True, sample_source=True),
+            Engine(data.features, data.states, data.families, data.network['adj_mat'], None, n_zones=2, n_chains=4,
+                   inheritance=True, sample_source=True, locations=loc)]
+    ops = {'shrink_zone': .15, 'grow_zone': .15, 'swap_zone': .1, 'gibbs_sample_weights': .2, 'gibbs_sample_p_global': .1,
+           'gibbs_sample_p_zones': .2, 'gibbs_sample_p_families': .1}
+    out = []
+    for eng in engs:
+        eng.set_priors(size_type='uniform', geo_type='cost_based', geo_scale=80.0)
+        for c in range(4):
+            st = synthetic.random_state(data, 2, 8, True, True, seed=40 + c)
+            eng.set_state(c, st['zones'], st['weights'], st['p_global'], st['p_zones'], st['p_families'], st['source'])
+        ll, pr, geo = eng.eval()
+        eng.set_operators(ops, PRECISION, min_size=3, max_size=25, p_grow_connected=0.85, seed=5)
+        eng.run(4000)
+        ll1, pr1 = eng.chain_scalars()
+        ll2, pr2, geo2 = eng.eval()
+        assert np.allclose(pr1, pr2, rtol=1e-9, atol=1e-9) and np.allclose(ll1, ll2, rtol=1e-9)
+        out.append((pr, geo, pr1, geo2, [eng.get_state(c, fields=('zones',))['zones'] for c in range(4)]))
+        eng.close()
+    (pr_a, geo_a, pr1_a, geo2_a, z_a), (pr_b, geo_b, pr1_b, geo2_b, z_b) = out
+    assert np.all(geo_a < 0) and np.allclose(geo_a, geo_b, rtol=1e-12, atol=0) and np.allclose(pr_a, pr_b, rtol=1e-12)
+    assert all(np.array_equal(a, b) for a, b in zip(z_a, z_b))              # the same moves were accepted
+    assert np.allclose(geo2_a, geo2_b, rtol=1e-12, atol=0)
+    assert any(not np.array_equal(z, synthetic.random_state(data, 2, 8, True, True, seed=40 + c)['zones'])
+               for c, z in enumerate(z_a))                                   # ... and zones did move
+
+
+def test_cost_based_geo_prior_at_20000_sites(built_lib):
+    """The dense cost matrix of 20000 sites would be 3.2 GB per GPU (and as much on the host); the implicit form needs
+    320 KB.  Checked against scipy's MST over the last zone's members (oracle, model.py:1096-1139)."""
+    import sbayes_oracle as orc
+    from scipy.spatial.distance import cdist
+    from contact_zones_b200 import synthetic
+    from contact_zones_b200.engine import Engine
+    data = synthetic.make_data(20000, 6, 3, n_families=0, seed=2, with_dist=False)
+    loc = data.network['locations']
+    eng = Engine(data.features, data.states, None, data.network['adj_mat'], None, n_zones=3, n_chains=2,
+                 inheritance=False, sample_source=True, locations=loc)
+    eng.set_priors(geo_type='cost_based', geo_scale=30.0)
+    for c in range(2):
+        st = synthetic.random_state(data, 3, 40, False, True, seed=70 + c)
+        eng.set_state(c, st['zones'], st['weights'], st['p_global'], st['p_zones'], None, st['source'])
+    ops = {'shrink_zone': .2, 'grow_zone': .2, 'swap_zone': .2, 'gibbs_sample_weights': .2, 'gibbs_sample_p_zones': .2}
+    eng.eval()
+    eng.set_operators(ops, PRECISION, min_size=3, max_size=120, p_grow_connected=0.85, seed=9)
+    eng.run(600)
+    _, pr, geo = eng.eval()
+    for c in range(2):
+        m = np.flatnonzero(eng.get_state(c, fields=('zones',))['zones'][-1])
+        ref = orc.geo_prior_cost_based(np.ones((1, len(m)), bool), cdist(loc[m], loc[m]), 30.0)
+        assert abs(geo[c] - ref) <= 1e-9 * abs(ref), (geo[c], ref)
+    eng.close()
