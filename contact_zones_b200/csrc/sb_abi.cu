@@ -456,7 +456,7 @@ static int recount_chains(sb_ctx* ctx, int chain, int n) {
     ChainArrays& st = ctx->st;
     const size_t nn = (size_t)n;
     const size_t cb_smem = count_block_smem(d.S, d.Z, d.Fam);
-    if (d.sample_source && cb_smem <= 200 * 1024 && blocked_kernels_allowed()) {
+    if (d.sample_source && cb_smem <= 200 * 1024 && n <= 65535 && blocked_kernels_allowed()) {
         // blocked recount: shared-memory counters per (16-feature block, chain), every table entry written once
         if (cb_smem > 48 * 1024)
             CK(cudaFuncSetAttribute(count_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem));
@@ -832,20 +832,21 @@ static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source
         return SB_OK;
         }
     }
-    dim3 gw((d.F + 127) / 128, n);
-    wnorm_kernel<<<gw, 128, 0, ctx->stream>>>(d, ctx->st, chain_begin);
     const size_t lb_smem = lh_source_block_smem(d.S, d.Z, d.Fam);
-    if (use_source && lb_smem <= 200 * 1024 && blocked_kernels_allowed()) {
-        // blocked form: parameter tables of a 16-feature block staged in shared memory
+    if (use_source && lb_smem <= 200 * 1024 && n <= 65535 && blocked_kernels_allowed()) {
+        // blocked form, ONE launch: parameter tables of a 16-feature block staged in shared memory (w~ rows included),
+        // the chain's last CTA reduces the per-block partial sums
         const int nb = d.ldx >> 4;
         if (lb_smem > 48 * 1024)
             CK(cudaFuncSetAttribute(lh_source_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lb_smem));
-        lh_source_block_kernel<<<dim3(nb, n), LH_THREADS, lb_smem, ctx->stream>>>(d, ctx->st, chain_begin, ctx->partial, nb);
-        lh_reduce_kernel<<<n, 32, 0, ctx->stream>>>(ctx->partial, nb, ctx->st.ll, chain_begin);
-        ctx->launches += 3;
+        lh_source_block_kernel<<<dim3(nb, n), LH_THREADS, lb_smem, ctx->stream>>>(
+            d, ctx->st, chain_begin, ctx->partial + (size_t)chain_begin * nb, nb, ctx->lt_ticket + chain_begin);
+        ++ctx->launches;
         CK(cudaGetLastError());
         return SB_OK;
     }
+    dim3 gw((d.F + 127) / 128, n);
+    wnorm_kernel<<<gw, 128, 0, ctx->stream>>>(d, ctx->st, chain_begin);
     // fallbacks (with source: tables of a feature block exceed shared memory; source-free: S = 32 or too many family
     // classes for K1's tables): one CTA per (site tile, chain), global gathers
     dim3 grid(ctx->n_tiles, n);

@@ -113,6 +113,44 @@ __device__ __forceinline__ double lp_value(LogProd& a) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// Rotated column strips (K4, K1s).  A thread holds the 16-byte strip (16 features) of one site; at unrolled step j lane
+// l works on feature (l + j) & 15 of ITS site and on table column (l + j) & 31, so the 32 lanes of a warp always touch
+// 32 different columns.  Tables laid out [row][32 columns] of 32-bit counters (column c and c + 16 both belong to
+// feature c & 15 and are added up at the end) or [row][16 features] of 64-bit values are then updated / read without a
+// bank conflict whatever the rows are.  The strip is rotated once per site (12 instructions) so that step j extracts
+// the STATIC byte j.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 rot_strip(const uint4 v, const int rot) {
+    uint32_t a0 = v.x, a1 = v.y, a2 = v.z, a3 = v.w, t;
+    if (rot & 4) { t = a0; a0 = a1; a1 = a2; a2 = a3; a3 = t; }
+    if (rot & 8) { t = a0; a0 = a2; a2 = t; t = a1; a1 = a3; a3 = t; }
+    const int br = (rot & 3) * 8;
+    return make_uint4(__funnelshift_r(a0, a1, br), __funnelshift_r(a1, a2, br), __funnelshift_r(a2, a3, br),
+                      __funnelshift_r(a3, a0, br));
+}
+__device__ __forceinline__ uint32_t strip_byte(const uint4& v, const int j) {      // j is a compile-time constant
+    const uint32_t w = (j >> 2) == 0 ? v.x : ((j >> 2) == 1 ? v.y : ((j >> 2) == 2 ? v.z : v.w));
+    return (w >> ((j & 3) * 8)) & 0xffu;
+}
+// state index (6 bits; NA / padding -> 63 / 62) and source component (2 bits) of the 16 cells in one strip
+__device__ __forceinline__ uint4 strip_merge(const uint4 x, const uint4 s) {
+    return make_uint4((x.x & 0x3f3f3f3fu) | ((s.x << 6) & 0xc0c0c0c0u), (x.y & 0x3f3f3f3fu) | ((s.y << 6) & 0xc0c0c0c0u),
+                      (x.z & 0x3f3f3f3fu) | ((s.z << 6) & 0xc0c0c0c0u), (x.w & 0x3f3f3f3fu) | ((s.w << 6) & 0xc0c0c0c0u));
+}
+// first row of the table a cell's source selects, as a 16-bit field picked by PRMT: [0] global (row 0), [1] the site's
+// zone, [2] the site's family, [3] the scrap table (a source the site has no table for)
+struct RowSel { uint32_t lo, hi; };
+__device__ __forceinline__ RowSel row_sel(int zid, int fam, int Z, int n_tab, int rows_per_tab) {
+    RowSel r;
+    r.lo = (uint32_t)((zid >= 0 ? 1 + zid : n_tab) * rows_per_tab) << 16;
+    r.hi = (uint32_t)((fam >= 0 ? 1 + Z + fam : n_tab) * rows_per_tab) | ((uint32_t)(n_tab * rows_per_tab) << 16);
+    return r;
+}
+__device__ __forceinline__ uint32_t row_of(const RowSel& r, uint32_t sc) {         // sc in 0..3
+    return __byte_perm(r.lo, r.hi, sc * 0x22u + 0x10u);
+}
+
+// ---------------------------------------------------------------------------------------------
 // deterministic block reductions (fixed shuffle tree + fixed warp order)
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ double warp_sum(double v) {

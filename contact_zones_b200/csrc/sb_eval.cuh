@@ -113,68 +113,156 @@ lh_full_kernel(DevData d, ChainArrays st, int chain_begin, int sites_per_tile, d
     if (threadIdx.x == 0) partial[(size_t)blockIdx.y * n_tiles + tile] = v;
 }
 
-// K1 with source (SRC = 1), blocked form: one CTA = one (16-feature block, chain); the block's parameter tables
-// (w~ [16][12], p_* [1 + Z + Fam][16][S + 1], the extra column = 1 for NA cells) are staged in shared memory, so the
-// cell body is two shared-memory look-ups and one fp64 multiply into the running product.  Same result as
-// lh_full_kernel<1> (which remains the fallback when the tables do not fit); partial[chain][block] is reduced in
-// fixed order by lh_reduce_kernel.
+// K1 with source (SRC = 1), blocked form: one CTA = one (16-feature block, chain); the block's parameter tables are
+// staged in shared memory feature-fastest -- P[table][state column][16] (tables: global, Z zones, Fam families, a scrap
+// table of ones; the extra state column = 1 for NA / padding cells) and W[cfg][4][16] (w~ of the chosen source) -- and
+// read through rotated strips (see above): two conflict-free LDS.64 and two fp64 multiplies per cell, 8 factors per
+// partial product, one exponent fold per site.  A site with a factor below 2^-120 (incl. a zero weight:
+// model.py:177-184, log 0) is redone cell by cell on the exact path.  Same result as lh_full_kernel<1> (which remains
+// the fallback when the tables do not fit); partial[chain][block] is reduced in fixed order by the chain's last CTA.
 __host__ __device__ __forceinline__ size_t lh_source_block_smem(int S, int Z, int Fam) {
-    return ((size_t)16 * (S + 1) * (1 + Z + Fam) + 192) * sizeof(double);
+    return ((size_t)(2 + Z + Fam) * (S + 1) * 16 + 256) * sizeof(double);
 }
 __global__ void __launch_bounds__(LH_THREADS)
-lh_source_block_kernel(DevData d, ChainArrays st, int chain_begin, double* __restrict__ partial, int n_blocks) {
-    extern __shared__ double lb_tab[];
+lh_source_block_kernel(DevData d, ChainArrays st, int chain_begin, double* __restrict__ partial, int n_blocks,
+                       unsigned* __restrict__ ticket) {
+    extern __shared__ __align__(128) double lb_tab[];
     __shared__ double red[33];
+    __shared__ int is_last;
     const int chain = chain_begin + blockIdx.y;
     const int f0 = blockIdx.x << 4;
     const int S = d.S, S1 = S + 1, F = d.F, N = d.N;
-    const int nf = min(16, F - f0);
-    const int bP = 16 * S1, n_rows = 16 * (1 + d.Z + d.Fam);
+    const int nf = min(16, F - f0), nfS = nf * S;
+    const int n_tab = 1 + d.Z + d.Fam, n_val = (n_tab + 1) * S1 * 16;
     const size_t FS = (size_t)F * S;
-    double* W = lb_tab + n_rows * S1;
+    double* W = lb_tab + n_val;
     const int8_t* __restrict__ zone_id = st.zone_id + chain * st.s_zone_id;
     const uint8_t* __restrict__ src = st.source + chain * st.s_source;
-    const double* __restrict__ wn = st.wnorm + chain * st.s_wnorm;
-    for (int i = threadIdx.x; i < 192; i += blockDim.x) W[i] = i < nf * 12 ? wn[(size_t)f0 * 12 + i] : 1.0;
-    for (int r = threadIdx.x; r < n_rows; r += blockDim.x) {
-        const int t = r >> 4, j = r & 15;
-        const double* srow = (t == 0 ? st.p_global + chain * st.s_p_global
-                                     : (t <= d.Z ? st.p_zones + chain * st.s_p_zones + (size_t)(t - 1) * FS
-                                                 : st.p_fam + chain * st.s_p_fam + (size_t)(t - 1 - d.Z) * FS))
-                             + (size_t)(f0 + j) * S;
-        double* dst = lb_tab + r * S1;
-        for (int sx = 0; sx < S; ++sx) dst[sx] = j < nf ? srow[sx] : 1.0;
-        dst[S] = 1.0;
-    }
+    for (int i = threadIdx.x; i < ((n_val + 256) >> 1); i += blockDim.x)
+        reinterpret_cast<double2*>(lb_tab)[i] = make_double2(1.0, 1.0);
     __syncthreads();
-    LogProd acc;
-    lp_init(acc);
-    bool zero_weight = false;
-    for (int n = threadIdx.x; n < N; n += blockDim.x) {
-        const uint4 xv = __ldg(reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + f0));
-        const uint4 sv = *reinterpret_cast<const uint4*>(src + (size_t)n * d.ldx + f0);
-        const int zid = zone_id[n];
-        const int fam = d.inheritance ? d.fam_id[n] : -1;
-        const int cfg = (zid >= 0 ? 1 : 0) + (fam >= 0 ? 2 : 0);
-        const int bz = (1 + max(zid, 0)) * bP, bf = (1 + d.Z + max(fam, 0)) * bP;
-        const double* wr = W + cfg * 3;
-        const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
-        const uint32_t sw[4] = {sv.x, sv.y, sv.z, sv.w};
+    if (threadIdx.x < nf) {                                       // w~ rows of the block (also refreshes the chain's table)
+        double row[12];
+        wnorm_row(st.weights + chain * st.s_weights + (size_t)(f0 + threadIdx.x) * 3, row, d.C);
+        double* g = st.wnorm + chain * st.s_wnorm + (size_t)(f0 + threadIdx.x) * 12;
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            if (j >= nf) break;                                             // CTA-uniform (padding columns)
-            const int xs = (xw[j >> 2] >> ((j & 3) * 8)) & 0xff;
-            const int sc = (sw[j >> 2] >> ((j & 3) * 8)) & 0xff;
-            const double ws = wr[j * 12 + sc];
-            if (ws == 0.0) { zero_weight = true; continue; }                // model.py:177-184: log 0
-            const int e = j * S1 + min(xs, S);                              // NA -> the column of ones
-            lp_mul(acc, ws * lb_tab[(sc == 0 ? 0 : (sc == 1 ? bz : bf)) + e]);
+        for (int i = 0; i < 12; ++i) {
+            W[((i / 3) * 4 + i % 3) * 16 + threadIdx.x] = row[i];
+            g[i] = row[i];
         }
     }
-    double v = lp_value(acc);
+    {   // thread -> (group, entry i = j * S + sx of the block's contiguous [nf][S] slice); groups split the tables
+        const int groups = max(1, (int)blockDim.x / nfS);
+        for (int i0 = threadIdx.x; i0 < groups * nfS; i0 += blockDim.x) {
+            const int g = i0 / nfS, i = i0 - g * nfS;
+            const int j = i / S, sx = i - j * S;
+            double* dst = lb_tab + sx * 16 + j;
+            const size_t o = (size_t)f0 * S + i;
+            // eight table entries in flight per thread (the loads are L2 round trips)
+            for (int t0 = g; t0 < n_tab; t0 += 8 * groups) {
+                double v4[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int t = t0 + u * groups;
+                    const double* srow = t == 0 ? st.p_global + chain * st.s_p_global
+                                                : (t <= d.Z ? st.p_zones + chain * st.s_p_zones + (size_t)(t - 1) * FS
+                                                            : st.p_fam + chain * st.s_p_fam + (size_t)(t - 1 - d.Z) * FS);
+                    v4[u] = t < n_tab ? srow[o] : 1.0;
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int t = t0 + u * groups;
+                    if (t < n_tab) dst[(size_t)t * S1 * 16] = v4[u];
+                }
+            }
+        }
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const uint32_t p_s = (uint32_t)__cvta_generic_to_shared(lb_tab), w_s = (uint32_t)__cvta_generic_to_shared(W);
+    double am = 1.0, side = 0.0;                                   // running product: mantissa in [1, 4), exact logs
+    int ae = 0;
+    bool zero_weight = false;
+    int n = threadIdx.x;
+    uint4 xv = make_uint4(0, 0, 0, 0), sv = xv;
+    int zid = -1, fam = -1;
+    if (n < N) {
+        xv = __ldg(reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + f0));
+        sv = *reinterpret_cast<const uint4*>(src + (size_t)n * d.ldx + f0);
+        zid = zone_id[n];
+        fam = d.inheritance ? d.fam_id[n] : -1;
+    }
+    while (n < N) {
+        const uint4 cr = rot_strip(strip_merge(xv, sv), lane & 15);
+        const RowSel rs = row_sel(zid, fam, d.Z, n_tab, S1);
+        const uint32_t wrow = w_s + (uint32_t)((zid >= 0 ? 1 : 0) + (fam >= 0 ? 2 : 0)) * 512u;        // W[cfg][..][..]
+        n += blockDim.x;
+        if (n < N) {                                                                   // next site's loads in flight
+            xv = __ldg(reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + f0));
+            sv = *reinterpret_cast<const uint4*>(src + (size_t)n * d.ldx + f0);
+            zid = zone_id[n];
+            fam = d.inheritance ? d.fam_id[n] : -1;
+        }
+        double m0 = am, m1 = 1.0;
+        int lo_hi = 0x7fffffff;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const uint32_t col = (uint32_t)((lane + j) & 15) * 8u;                     // loop-invariant per (thread, j)
+            const uint32_t c = strip_byte(cr, j);
+            const uint32_t xs = min(c & 63u, (uint32_t)S), sc = c >> 6;                // NA / padding -> the column of ones
+            double ws, pv;
+            asm("ld.shared.f64 %0, [%1];" : "=d"(ws) : "r"((wrow + sc * 128u) | col));
+            asm("ld.shared.f64 %0, [%1];" : "=d"(pv) : "r"((p_s + (row_of(rs, sc) + xs) * 128u) | col));
+            const double v = ws * pv;
+            lo_hi = min(lo_hi, __double2hiint(v));
+            if (j & 1) m1 *= v; else m0 *= v;
+        }
+        if (lo_hi >= 0x38700000) {
+            // 8 factors >= 2^-120 per partial product on top of a mantissa in [1, 4): no underflow before the fold
+            const int h0 = __double2hiint(m0), h1 = __double2hiint(m1);
+            ae += ((h0 >> 20) & 0x7ff) + ((h1 >> 20) & 0x7ff) - 2046;
+            am = __hiloint2double((h0 & 0x800fffff) | 0x3ff00000, __double2loint(m0))
+                 * __hiloint2double((h1 & 0x800fffff) | 0x3ff00000, __double2loint(m1));
+            continue;
+        }
+        // exact path: a tiny / zero factor somewhere in this site's strip
+#pragma unroll 1
+        for (int j = 0; j < 16; ++j) {
+            const uint32_t col = (uint32_t)((lane + j) & 15) * 8u;
+            const uint32_t w4 = j < 4 ? cr.x : (j < 8 ? cr.y : (j < 12 ? cr.z : cr.w));
+            const uint32_t c = (w4 >> ((j & 3) * 8)) & 0xffu;
+            const uint32_t xs = min(c & 63u, (uint32_t)S), sc = c >> 6;
+            double ws, pv;
+            asm("ld.shared.f64 %0, [%1];" : "=d"(ws) : "r"((wrow + sc * 128u) | col));
+            asm("ld.shared.f64 %0, [%1];" : "=d"(pv) : "r"((p_s + (row_of(rs, sc) + xs) * 128u) | col));
+            if (ws == 0.0) { zero_weight = true; continue; }
+            const double v = ws * pv;
+            if (__double2hiint(v) < 0x38700000) { side += sb_log(v); continue; }
+            am *= v;
+            const int h = __double2hiint(am);
+            ae += ((h >> 20) & 0x7ff) - 1023;
+            am = __hiloint2double((h & 0x800fffff) | 0x3ff00000, __double2loint(am));
+        }
+    }
+    double v = log(am) + (double)ae * SB_LN2 + side;
     if (zero_weight) v = -INFINITY;
     v = block_sum(v, red);
-    if (threadIdx.x == 0) partial[(size_t)blockIdx.y * n_blocks + blockIdx.x] = v;
+    if (threadIdx.x == 0) {
+        partial[(size_t)blockIdx.y * n_blocks + blockIdx.x] = v;
+        __threadfence();
+        is_last = atomicAdd(&ticket[blockIdx.y], 1u) == (unsigned)(n_blocks - 1);
+    }
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        double t = 0.0;
+        for (int i = threadIdx.x; i < n_blocks; i += blockDim.x) t += __ldcg(&partial[(size_t)blockIdx.y * n_blocks + i]);
+        t = block_sum(t, red);
+        if (threadIdx.x == 0) {
+            st.ll[chain] = t;
+            ticket[blockIdx.y] = 0u;
+        }
+    }
 }
 
 __global__ void lh_reduce_kernel(const double* __restrict__ partial, int n_tiles, double* __restrict__ ll,
@@ -377,62 +465,138 @@ count_kernel(DevData d, ChainArrays st, int chain_begin, int sites_per_tile) {
     }
 }
 
-// K4 (full recount), blocked form: one CTA = one (16-feature block, chain).  The block's counters -- [1 + Z + Fam]
-// tables of [16][S] and the source table [16][12] -- live in shared memory, are filled with shared-memory atomics
-// while the CTA streams its 16-byte column strip of x and source over all sites, and are flushed with plain stores:
-// no global atomics and no zeroing pass (every entry of the block's rows is written).  Same semantics as
-// count_kernel, which remains the fallback when the tables of a block do not fit in shared memory.
+// K4 (full recount), blocked form: one CTA = one (16-feature block, chain).  The block's counters live in shared
+// memory as cnt[table][state column][32] (32-bit; tables: the global table once per site configuration cfg = has_zone +
+// 2 has_family, Z zones, Fam families, one scrap table for cells whose source has no table; the extra state column
+// takes NA / padding cells) and are filled with ONE conflict-free shared-memory atomic per cell (rotated strips,
+// sb_common.cuh) while the CTA streams its 16-byte column strip of x and source over all sites.  Shared-memory atomics
+// retire ~4 lanes per clock whatever their addresses (ncu: mio_throttle, 10 clocks per warp-wide ATOMS), which is
+// what bounds this kernel, so the source table cnt_src[f][cfg][s] is not counted but DERIVED: a site of configuration
+// cfg only has the sources its configuration allows, hence  src[cfg][0] = sum_x global_cfg[x],
+// src[1][1] = n_sites(cfg 1) - src[1][0],  src[2][2] = n_sites(cfg 2) - src[2][0],  src[3][1] = sum_z,x zone_z[x] - src[1][1],
+// src[3][2] = sum_k,x family_k[x] - src[2][2].  The flush writes every entry of the block's rows with plain coalesced
+// stores: no global atomics and no zeroing pass.  Same result as count_kernel on every state whose sources are valid
+// (count_kernel remains the fallback when the tables of a block do not fit in shared memory).
 __host__ __device__ __forceinline__ size_t count_block_smem(int S, int Z, int Fam) {
-    return ((size_t)16 * S * (1 + Z + Fam) + 192) * sizeof(int);
+    return ((size_t)(5 + Z + Fam) * (S + 1) * 32 + 128) * sizeof(int);
 }
 __global__ void __launch_bounds__(256)
 count_block_kernel(DevData d, ChainArrays st, int chain_begin) {
-    extern __shared__ int cb_tab[];
+    extern __shared__ __align__(128) int cb_tab[];
     const int chain = chain_begin + blockIdx.y;
     const int f0 = blockIdx.x << 4;
-    const int S = d.S, F = d.F, N = d.N;
+    const int S = d.S, S1 = S + 1, F = d.F, N = d.N;
     const int nf = min(16, F - f0);
-    const int bS = 16 * S, n_rows = 16 * (1 + d.Z + d.Fam);
-    int* tcs = cb_tab + n_rows * S;
-    const int T = n_rows * S + 192;
+    const int n_tab = 4 + d.Z + d.Fam, TS = S1 * 32;                    // tables (without the scrap table), ints per table
+    int* aux = cb_tab + (n_tab + 1) * TS;                               // [0..3] sites per cfg, [16 + 6 j ..] sums of feature j
+    const int T = (n_tab + 1) * TS + 128;
     const int8_t* __restrict__ zone_id = st.zone_id + chain * st.s_zone_id;
     const uint8_t* __restrict__ src = st.source + chain * st.s_source;
-    for (int i = threadIdx.x; i < T; i += blockDim.x) cb_tab[i] = 0;
+    for (int i = threadIdx.x; i < (T >> 2); i += blockDim.x) reinterpret_cast<int4*>(cb_tab)[i] = make_int4(0, 0, 0, 0);
     __syncthreads();
-    for (int n = threadIdx.x; n < N; n += blockDim.x) {
-        const uint4 xv = __ldg(reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + f0));
-        const uint4 sv = *reinterpret_cast<const uint4*>(src + (size_t)n * d.ldx + f0);
-        const int zid = zone_id[n];
-        const int fam = d.inheritance ? d.fam_id[n] : -1;
+    const int lane = threadIdx.x & 31;
+    const uint32_t cnt_s = (uint32_t)__cvta_generic_to_shared(cb_tab);
+    int n = threadIdx.x;
+    uint4 xv = make_uint4(0, 0, 0, 0), sv = xv;
+    int zid = -1, fam = -1;
+    if (n < N) {
+        xv = __ldg(reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + f0));
+        sv = *reinterpret_cast<const uint4*>(src + (size_t)n * d.ldx + f0);
+        zid = zone_id[n];
+        fam = d.inheritance ? d.fam_id[n] : -1;
+    }
+    uint32_t n_cfg = 0;                                                 // four 8-bit tallies (<= N / blockDim sites each)
+    while (n < N) {
+        const uint4 cr = rot_strip(strip_merge(xv, sv), lane & 15);
         const int cfg = (zid >= 0 ? 1 : 0) + (fam >= 0 ? 2 : 0);
-        const int bz = (1 + max(zid, 0)) * bS, bf = (1 + d.Z + max(fam, 0)) * bS;
-        const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
-        const uint32_t sw[4] = {sv.x, sv.y, sv.z, sv.w};
+        // first row of the table a cell's source selects: [0] global table of the site's cfg, [1] its zone, [2] its
+        // family, [3] scrap
+        RowSel rs;
+        rs.lo = (uint32_t)(cfg * S1) | ((uint32_t)((zid >= 0 ? 4 + zid : n_tab) * S1) << 16);
+        rs.hi = (uint32_t)((fam >= 0 ? 4 + d.Z + fam : n_tab) * S1) | ((uint32_t)(n_tab * S1) << 16);
+        n_cfg += 1u << (8 * cfg);
+        if ((n_cfg & 0x80808080u) != 0u) {                              // (only with > 32768 sites per chain)
+            for (int c = 0; c < 4; ++c) atomicAdd(aux + c, (int)((n_cfg >> (8 * c)) & 0xffu));
+            n_cfg = 0;
+        }
+        n += blockDim.x;
+        if (n < N) {                                                                   // next site's loads in flight
+            xv = __ldg(reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + f0));
+            sv = *reinterpret_cast<const uint4*>(src + (size_t)n * d.ldx + f0);
+            zid = zone_id[n];
+            fam = d.inheritance ? d.fam_id[n] : -1;
+        }
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
-            if (j >= nf) break;                                             // CTA-uniform (padding columns)
-            const int xs = (xw[j >> 2] >> ((j & 3) * 8)) & 0xff;
-            const int s = (sw[j >> 2] >> ((j & 3) * 8)) & 0xff;
-            atomicAdd(tcs + j * 12 + cfg * 3 + s, 1);
-            if (xs == SB_NA) continue;
-            if (s == 0) atomicAdd(cb_tab + j * S + xs, 1);
-            else if (s == 1) { if (zid >= 0) atomicAdd(cb_tab + bz + j * S + xs, 1); }
-            else if (fam >= 0) atomicAdd(cb_tab + bf + j * S + xs, 1);
+            const uint32_t col = (uint32_t)((lane + j) & 31) * 4u;                     // loop-invariant per (thread, j)
+            const uint32_t c = strip_byte(cr, j);
+            const uint32_t xs = min(c & 63u, (uint32_t)S), sc = c >> 6;                // NA / padding -> the extra column
+            const uint32_t a_cnt = (cnt_s + ((row_of(rs, sc) & 0xffffu) + xs) * 128u) | col;
+            asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(a_cnt), "r"(1u) : "memory");
+        }
+    }
+    for (int c = 0; c < 4; ++c)
+        if ((n_cfg >> (8 * c)) & 0xffu) atomicAdd(aux + c, (int)((n_cfg >> (8 * c)) & 0xffu));
+    __syncthreads();
+    const size_t FS = (size_t)F * S;
+    // flush: thread -> (group, entry i = j * S + sx of the block's contiguous [nf][S] slice); group 0 also adds the four
+    // global tables up, the groups split the zone / family tables.  On the way every thread collects its share of the
+    // per-feature sums of the derived source table: aux[16 + 6 j + q], q = 0..3 global table of cfg q, 4 zones, 5 families
+    {
+        const int nfS = nf * S, groups = max(1, (int)blockDim.x / nfS);
+        for (int i0 = threadIdx.x; i0 < groups * nfS; i0 += blockDim.x) {
+            const int g = i0 / nfS, i = i0 - g * nfS;
+            const int j = i / S, sx = i - j * S;
+            const int* c = cb_tab + sx * 32 + j;
+            const size_t o = (size_t)f0 * S + i;
+            int* sums = aux + 16 + 6 * j;
+            if (g == 0) {
+                int tot = 0;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int v = c[q * TS] + c[q * TS + 16];
+                    if (v) atomicAdd(sums + q, v);
+                    tot += v;
+                }
+                st.cnt_glob[chain * st.s_cnt_glob + o] = tot;
+            }
+            int sz = 0, sf = 0;
+            for (int z = g; z < d.Z; z += groups) {
+                const int v = c[(4 + z) * TS] + c[(4 + z) * TS + 16];
+                st.cnt_zone[chain * st.s_cnt_zone + (size_t)z * FS + o] = v;
+                sz += v;
+            }
+            for (int k = g; k < d.Fam; k += groups) {
+                const int v = c[(4 + d.Z + k) * TS] + c[(4 + d.Z + k) * TS + 16];
+                st.cnt_fam[chain * st.s_cnt_fam + (size_t)k * FS + o] = v;
+                sf += v;
+            }
+            if (sz) atomicAdd(sums + 4, sz);
+            if (sf) atomicAdd(sums + 5, sf);
+        }
+        // the NA column of every table also counts towards the source sums: (feature, table slice) per thread
+        for (int i = threadIdx.x; i < 16 * 8; i += blockDim.x) {
+            const int j = i & 15;
+            if (j >= nf) continue;
+            const int* c = cb_tab + S * 32 + j;
+            int acc[6] = {0, 0, 0, 0, 0, 0};
+            for (int t = i >> 4; t < n_tab; t += 8) acc[t < 4 ? t : (t < 4 + d.Z ? 4 : 5)] += c[t * TS] + c[t * TS + 16];
+#pragma unroll
+            for (int q = 0; q < 6; ++q)
+                if (acc[q]) atomicAdd(aux + 16 + 6 * j + q, acc[q]);
         }
     }
     __syncthreads();
-    const size_t FS = (size_t)F * S;
-    for (int r = threadIdx.x; r < n_rows; r += blockDim.x) {
-        const int t = r >> 4, j = r & 15;
-        if (j >= nf) continue;
-        int* dst = (t == 0 ? st.cnt_glob + chain * st.s_cnt_glob
-                           : (t <= d.Z ? st.cnt_zone + chain * st.s_cnt_zone + (size_t)(t - 1) * FS
-                                       : st.cnt_fam + chain * st.s_cnt_fam + (size_t)(t - 1 - d.Z) * FS))
-                   + (size_t)(f0 + j) * S;
-        for (int sx = 0; sx < S; ++sx) dst[sx] = cb_tab[r * S + sx];
-    }
     int* cs = st.cnt_src + chain * st.s_cnt_src + (size_t)f0 * 12;
-    for (int i = threadIdx.x; i < nf * 12; i += blockDim.x) cs[i] = tcs[i];
+    if (threadIdx.x < nf) {
+        const int* a = aux + 16 + 6 * threadIdx.x;
+        int* o = cs + threadIdx.x * 12;
+        const int s11 = aux[1] - a[1], s22 = aux[2] - a[2];
+        o[0] = a[0]; o[1] = 0;           o[2] = 0;
+        o[3] = a[1]; o[4] = s11;         o[5] = 0;
+        o[6] = a[2]; o[7] = 0;           o[8] = s22;
+        o[9] = a[3]; o[10] = a[4] - s11; o[11] = a[5] - s22;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
