@@ -43,6 +43,8 @@ struct sb_ctx {
     double* lt_partial = nullptr;    // [n_chains][lt.n_tiles * lt.n_chunks]
     unsigned* lt_ticket = nullptr;   // [n_chains]
     long lt_want = 148L * 14;        // CTA target of one K1 launch (SB_K1_CTAS overrides, for tuning)
+    int k1b_threads = LH_THREADS, k1s_threads = LH_THREADS;   // CTA sizes of the blocked likelihood kernels (SB_K1B_THREADS, SB_K1S_THREADS)
+    int k1_block_max_n = 0;          // source-free launches over at most this many sites take the blocked kernel (SB_K1_BLOCK_MAX_N)
     long lt_want_compact = 148L * 7; // the same for shapes with one site per code byte (SB_K1_CTAS_COMPACT; 444..2072 measured)
     std::vector<int> h_gclass;       // host copy of lt.group_class (class span of a group range)
     int geo_cap = 0;                 // capacity (members) of the Prim scratch
@@ -149,6 +151,9 @@ int sb_create(sb_ctx** out, int device, const sb_dims* dims) {
     ctx->dims = *dims;
     if (const char* e = getenv("SB_K1_CTAS")) ctx->lt_want = std::max(1L, atol(e));
     if (const char* e = getenv("SB_K1_CTAS_COMPACT")) ctx->lt_want_compact = std::max(1L, atol(e));
+    if (const char* e = getenv("SB_K1_BLOCK_MAX_N")) ctx->k1_block_max_n = atoi(e);
+    if (const char* e = getenv("SB_K1B_THREADS")) ctx->k1b_threads = std::min(LH_THREADS, std::max(32, atoi(e) & ~31));
+    if (const char* e = getenv("SB_K1S_THREADS")) ctx->k1s_threads = std::min(LH_THREADS, std::max(32, atoi(e) & ~31));
     *out = ctx;   // returned even on failure so that the caller can read sb_last_error, then sb_destroy
     CK(cudaSetDevice(device));
     CK(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
@@ -788,6 +793,20 @@ static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source
     const DevData& d = ctx->d;
     // table-driven K1: one launch (weights normalisation and the per-chain reduction are fused).  Its table rows hold
     // 32 codes, i.e. S + 1 <= 32 digits: S = 32 (SB_MAX_S) takes the tile-per-site kernel below
+    // blocked form (one CTA per 16-feature block and chain, sb_eval.cuh): shapes with one site per code byte (S + 1 > 5),
+    // S = 32, and launches over few sites, where the table kernel's per-chain prologue dominates (SB_K1_BLOCK_MAX_N)
+    const size_t fb_smem = lh_free_block_smem(d.S, d.Z, d.Fam);
+    if (!use_source && fb_smem <= 200 * 1024 && n <= 65535 && blocked_kernels_allowed() &&
+        (ctx->lt.cpb == 1 || d.S + 1 > LT_ROW || d.N <= ctx->k1_block_max_n)) {
+        const int nb = d.ldx >> 4;
+        if (fb_smem > 48 * 1024)
+            CK(cudaFuncSetAttribute(lh_free_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fb_smem));
+        lh_free_block_kernel<<<dim3(nb, n), ctx->k1b_threads, fb_smem, ctx->stream>>>(
+            d, ctx->st, chain_begin, ctx->partial + (size_t)chain_begin * nb, nb, ctx->lt_ticket + chain_begin);
+        ++ctx->launches;
+        CK(cudaGetLastError());
+        return SB_OK;
+    }
     if (!use_source && d.S + 1 <= LT_ROW) {
         LhTab t = ctx->lt;
         // grid = (group splits, feature chunks, chains).  Every CTA pays a fixed latency chain (tables, zone-member
@@ -839,7 +858,7 @@ static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source
         const int nb = d.ldx >> 4;
         if (lb_smem > 48 * 1024)
             CK(cudaFuncSetAttribute(lh_source_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lb_smem));
-        lh_source_block_kernel<<<dim3(nb, n), LH_THREADS, lb_smem, ctx->stream>>>(
+        lh_source_block_kernel<<<dim3(nb, n), ctx->k1s_threads, lb_smem, ctx->stream>>>(
             d, ctx->st, chain_begin, ctx->partial + (size_t)chain_begin * nb, nb, ctx->lt_ticket + chain_begin);
         ++ctx->launches;
         CK(cudaGetLastError());

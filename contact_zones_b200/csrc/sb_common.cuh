@@ -163,6 +163,18 @@ __device__ __forceinline__ int warp_sum_i(int v) {
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
 }
+// log of the product of the 32 lanes' running products (mantissa in [1, 4), binary exponent, exact side logs): the
+// mantissas are multiplied across the warp (< 4^32) so that ONE log per warp is taken; lane 0 holds the value, the
+// other lanes 0, i.e. the result is ready for block_sum.
+__device__ __forceinline__ double lp_warp_value(double m, int e, double side) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m *= __shfl_xor_sync(0xffffffffu, m, o);
+        e += __shfl_xor_sync(0xffffffffu, e, o);
+        side += __shfl_xor_sync(0xffffffffu, side, o);
+    }
+    return (threadIdx.x & 31) == 0 ? log(m) + (double)e * SB_LN2 + side : 0.0;
+}
 // Result valid in every thread. `red` = shared scratch of >= 33 doubles.
 __device__ __forceinline__ double block_sum(double v, double* red) {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;

@@ -244,8 +244,209 @@ lh_source_block_kernel(DevData d, ChainArrays st, int chain_begin, double* __res
             am = __hiloint2double((h & 0x800fffff) | 0x3ff00000, __double2loint(am));
         }
     }
-    double v = log(am) + (double)ae * SB_LN2 + side;
+    double v = lp_warp_value(am, ae, side);
     if (zero_weight) v = -INFINITY;
+    v = block_sum(v, red);
+    if (threadIdx.x == 0) {
+        partial[(size_t)blockIdx.y * n_blocks + blockIdx.x] = v;
+        __threadfence();
+        is_last = atomicAdd(&ticket[blockIdx.y], 1u) == (unsigned)(n_blocks - 1);
+    }
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        double t = 0.0;
+        for (int i = threadIdx.x; i < n_blocks; i += blockDim.x) t += __ldcg(&partial[(size_t)blockIdx.y * n_blocks + i]);
+        t = block_sum(t, red);
+        if (threadIdx.x == 0) {
+            st.ll[chain] = t;
+            ticket[blockIdx.y] = 0u;
+        }
+    }
+}
+
+// K1 source-free, blocked form (shapes whose zone-free table does not pay: one site per code byte, or few sites): one
+// CTA = one (16-feature block, chain).  For a site in no zone the mixture value of a cell depends only on
+// (f, x, family), so the CTA builds V[class][state column][16] = w~[f][cfg][0] p_global + w~[f][cfg][2] p_family
+// (classes: Fam families, "no family", and a class of ones that zone members read; the extra state column = 1 for
+// NA / padding cells) straight from the chain's global tables and streams its 16-byte column strip of x over all sites
+// through rotated strips (sb_common.cuh): ONE conflict-free LDS.64 and one fp64 multiply per cell, 8 factors per
+// partial product, one exponent fold per site.  The <= Z * MAX_M zone members then get their exact value in a second,
+// dense pass over the member lists:  mix = rho_f V[class][x] + w~[f][cfg][1] p_zone[z][x],  rho_f = the weight mass
+// of the zone-free components (1 - w~[f][cfg][1] up to rounding; for an NA cell V = p_zone = 1).  A site with a
+// factor below 2^-120 is redone cell by cell on the exact path (log 0 = -inf as in model.py:174-176).
+// partial[chain][block] is reduced in fixed order by the chain's last CTA.
+__host__ __device__ __forceinline__ size_t lh_free_block_smem(int S, int Z, int Fam) {
+    return ((size_t)(2 + Fam + Z) * (S + 1) * 16 + 64) * sizeof(double);
+}
+// the 16 cells of one site folded into (am, ae, side): v_j = rho_j * V[vrow + x_j] + om_j * PZ[zrow + x_j] with ZONE,
+// else V[vrow + x_j]
+template <bool ZONE>
+__device__ __forceinline__ void lh_free_site(const uint4 xr, const int lane, const int S, const uint32_t vrow,
+                                             const uint32_t zrow, const uint32_t coef, double& am, int& ae, double& side) {
+    double m0 = am, m1 = 1.0;
+    int lo_hi = 0x7fffffff;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        const uint32_t col = (uint32_t)((lane + j) & 15) * 8u;                         // loop-invariant per (thread, j)
+        const uint32_t xs = min(strip_byte(xr, j), (uint32_t)S);                       // NA / padding -> the column of ones
+        double v;
+        asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"((vrow + xs * 128u) | col));
+        if (ZONE) {
+            double pz, rho, om;
+            asm("ld.shared.f64 %0, [%1];" : "=d"(pz) : "r"((zrow + xs * 128u) | col));
+            asm("ld.shared.f64 %0, [%1];" : "=d"(rho) : "r"(coef | col));
+            asm("ld.shared.f64 %0, [%1];" : "=d"(om) : "r"((coef + 128u) | col));
+            v = rho * v + om * pz;
+        }
+        lo_hi = min(lo_hi, __double2hiint(v));
+        if (j & 1) m1 *= v; else m0 *= v;
+    }
+    if (lo_hi >= 0x38700000) {
+        // 8 factors >= 2^-120 per partial product on top of a mantissa in [1, 4): no underflow before the fold
+        const int h0 = __double2hiint(m0), h1 = __double2hiint(m1);
+        ae += ((h0 >> 20) & 0x7ff) + ((h1 >> 20) & 0x7ff) - 2046;
+        am = __hiloint2double((h0 & 0x800fffff) | 0x3ff00000, __double2loint(m0))
+             * __hiloint2double((h1 & 0x800fffff) | 0x3ff00000, __double2loint(m1));
+        return;
+    }
+    // exact path: a tiny / zero factor somewhere in this site's strip
+#pragma unroll 1
+    for (int j = 0; j < 16; ++j) {
+        const uint32_t col = (uint32_t)((lane + j) & 15) * 8u;
+        const uint32_t w4 = j < 4 ? xr.x : (j < 8 ? xr.y : (j < 12 ? xr.z : xr.w));
+        const uint32_t xs = min((w4 >> ((j & 3) * 8)) & 0xffu, (uint32_t)S);
+        double v;
+        asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"((vrow + xs * 128u) | col));
+        if (ZONE) {
+            double pz, rho, om;
+            asm("ld.shared.f64 %0, [%1];" : "=d"(pz) : "r"((zrow + xs * 128u) | col));
+            asm("ld.shared.f64 %0, [%1];" : "=d"(rho) : "r"(coef | col));
+            asm("ld.shared.f64 %0, [%1];" : "=d"(om) : "r"((coef + 128u) | col));
+            v = rho * v + om * pz;
+        }
+        if (__double2hiint(v) < 0x38700000) { side += sb_log(v); continue; }
+        am *= v;
+        const int h = __double2hiint(am);
+        ae += ((h >> 20) & 0x7ff) - 1023;
+        am = __hiloint2double((h & 0x800fffff) | 0x3ff00000, __double2loint(am));
+    }
+}
+__global__ void __launch_bounds__(LH_THREADS)
+lh_free_block_kernel(DevData d, ChainArrays st, int chain_begin, double* __restrict__ partial, int n_blocks,
+                     unsigned* __restrict__ ticket) {
+    extern __shared__ __align__(128) double fb_tab[];
+    __shared__ double red[33];
+    __shared__ int is_last;
+    __shared__ int zoff[SB_MAX_Z + 1];
+    const int chain = chain_begin + blockIdx.y;
+    const int f0 = blockIdx.x << 4;
+    const int S = d.S, S1 = S + 1, F = d.F, N = d.N, Fam = d.Fam;
+    const int nf = min(16, F - f0), nfS = nf * S;
+    const size_t FS = (size_t)F * S;
+    // V: classes 0 .. Fam-1 families, Fam "no family", Fam+1 ones | PZ: Z zones | coef: [cfg 1 | cfg 3][rho, omega][16]
+    const int n_v = (Fam + 2) * S1 * 16, n_pz = d.Z * S1 * 16;
+    double* PZ = fb_tab + n_v;
+    double* CO = PZ + n_pz;
+    const int8_t* __restrict__ zone_id = st.zone_id + chain * st.s_zone_id;
+    // the first site of every thread is requested before the tables are built
+    int n = threadIdx.x;
+    uint4 xv = make_uint4(0, 0, 0, 0);
+    int cls = Fam + 1;
+    if (n < N) {
+        xv = __ldg(reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + f0));
+        const int fam = d.inheritance ? d.fam_id[n] : -1;
+        cls = zone_id[n] >= 0 ? Fam + 1 : (fam >= 0 ? fam : Fam);
+    }
+    for (int i = threadIdx.x; i < ((n_v + n_pz + 64) >> 1); i += blockDim.x)
+        reinterpret_cast<double2*>(fb_tab)[i] = make_double2(1.0, 1.0);
+    if (threadIdx.x == 0) {
+        int o = 0;
+        for (int z = 0; z < d.Z; ++z) { zoff[z] = o; o += st.zone_size[chain * st.s_zone_size + z]; }
+        zoff[d.Z] = o;
+    }
+    __syncthreads();
+    if (threadIdx.x >= nf && threadIdx.x < 16) CO[16 + threadIdx.x] = CO[48 + threadIdx.x] = 0.0;   // padding columns: 1 V + 0 pz
+    {   // thread -> (group, entry i = j * S + sx of the block's contiguous [nf][S] slice); the groups split the classes
+        const int groups = max(1, (int)blockDim.x / nfS);
+        const double* __restrict__ w = st.weights + chain * st.s_weights;
+        for (int i0 = threadIdx.x; i0 < groups * nfS; i0 += blockDim.x) {
+            const int g = i0 / nfS, i = i0 - g * nfS;
+            const int j = i / S, sx = i - j * S;
+            const size_t o = (size_t)f0 * S + i;
+            // the entries of w~ this thread needs, with wnorm_row's arithmetic: a_c / ((a_0 + a_1) + a_2)
+            const double a0 = w[(size_t)(f0 + j) * 3], a1 = w[(size_t)(f0 + j) * 3 + 1];
+            const double a2 = d.C == 3 ? w[(size_t)(f0 + j) * 3 + 2] : 0.0;
+            const double pg = st.p_global[chain * st.s_p_global + o];
+            const double s2 = (a0 + 0.0) + a2;
+            const double row6 = a0 / s2, row8 = a2 / s2;                               // cfg 2: family, no zone
+            double* dst = fb_tab + sx * 16 + j;
+            if (g == 0) {
+                dst[(size_t)Fam * S1 * 16] = (a0 / ((a0 + 0.0) + 0.0)) * pg;           // no family: cfg 0
+                if (sx == 0) {
+                    // zone members: cfg 1 -> w~[1][0] V + w~[1][1] pz;  cfg 3 -> (1 - w~[3][1]) V + w~[3][1] pz with
+                    // V = (w~[3][0] pg + w~[3][2] pf) / (w~[3][0] + w~[3][2]) = the cfg-2 value
+                    const double s1 = (a0 + a1) + 0.0, s3 = (a0 + a1) + a2;
+                    CO[j] = a0 / s1;
+                    CO[16 + j] = a1 / s1;
+                    CO[32 + j] = a0 / s3 + a2 / s3;
+                    CO[48 + j] = a1 / s3;
+                }
+            }
+            // the zone and family tables of this entry, eight loads in flight (they are L2 round trips)
+            for (int e0 = g; e0 < d.Z + Fam; e0 += 8 * groups) {
+                double p8[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int e = e0 + u * groups;
+                    const double* src = e < d.Z ? st.p_zones + chain * st.s_p_zones + (size_t)e * FS
+                                                : st.p_fam + chain * st.s_p_fam + (size_t)(e - d.Z) * FS;
+                    p8[u] = e < d.Z + Fam ? src[o] : 0.0;
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int e = e0 + u * groups;
+                    if (e < d.Z) PZ[(size_t)e * S1 * 16 + sx * 16 + j] = p8[u];
+                    else if (e < d.Z + Fam) dst[(size_t)(e - d.Z) * S1 * 16] = row6 * pg + row8 * p8[u];
+                }
+            }
+        }
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const uint32_t v_s = (uint32_t)__cvta_generic_to_shared(fb_tab), pz_s = (uint32_t)__cvta_generic_to_shared(PZ);
+    const uint32_t co_s = (uint32_t)__cvta_generic_to_shared(CO);
+    double am = 1.0, side = 0.0;                                   // running product: mantissa in [1, 4), exact logs
+    int ae = 0;
+    // ---- every site as if it were in no zone (zone members read the class of ones) ----
+    {
+        while (n < N) {
+            const uint4 xr = rot_strip(xv, lane & 15);
+            const uint32_t vrow = v_s + (uint32_t)(cls * S1) * 128u;
+            n += blockDim.x;
+            if (n < N) {                                                               // next site's loads in flight
+                xv = __ldg(reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + f0));
+                const int fam = d.inheritance ? d.fam_id[n] : -1;
+                cls = zone_id[n] >= 0 ? Fam + 1 : (fam >= 0 ? fam : Fam);
+            }
+            lh_free_site<false>(xr, lane, S, vrow, 0u, 0u, am, ae, side);
+        }
+    }
+    // ---- zone members, exact ----
+    {
+        const int* __restrict__ members = st.zone_members + chain * st.s_zone_members;
+        const int n_mem = zoff[d.Z];
+        for (int m = threadIdx.x; m < n_mem; m += blockDim.x) {
+            int z = 0;
+            while (m >= zoff[z + 1]) ++z;
+            const int n = members[(size_t)z * N + (m - zoff[z])];
+            const int fam = d.inheritance ? d.fam_id[n] : -1;
+            const uint4 xr = rot_strip(__ldg(reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + f0)), lane & 15);
+            lh_free_site<true>(xr, lane, S, v_s + (uint32_t)((fam >= 0 ? fam : Fam) * S1) * 128u,
+                               pz_s + (uint32_t)(z * S1) * 128u, co_s + (fam >= 0 ? 256u : 0u), am, ae, side);
+        }
+    }
+    double v = lp_warp_value(am, ae, side);
     v = block_sum(v, red);
     if (threadIdx.x == 0) {
         partial[(size_t)blockIdx.y * n_blocks + blockIdx.x] = v;
