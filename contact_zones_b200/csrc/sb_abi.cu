@@ -44,7 +44,9 @@ struct sb_ctx {
     unsigned* lt_ticket = nullptr;   // [n_chains]
     long lt_want = 148L * 14;        // CTA target of one K1 launch (SB_K1_CTAS overrides, for tuning)
     int k1b_threads = LH_THREADS, k1s_threads = LH_THREADS;   // CTA sizes of the blocked likelihood kernels (SB_K1B_THREADS, SB_K1S_THREADS)
-    int k1_block_max_n = 0;          // source-free launches over at most this many sites take the blocked kernel (SB_K1_BLOCK_MAX_N)
+    int n_sms = 148;                 // cudaDevAttrMultiProcessorCount of the context's device
+    int k1b_parts = 0;               // CTAs per chain of the blocked source-free kernel (0 = chosen per launch; SB_K1B_PARTS)
+    int k1_block_max_n = 1024;       // source-free launches over at most this many sites take the blocked kernel (SB_K1_BLOCK_MAX_N)
     long lt_want_compact = 148L * 7; // the same for shapes with one site per code byte (SB_K1_CTAS_COMPACT; 444..2072 measured)
     std::vector<int> h_gclass;       // host copy of lt.group_class (class span of a group range)
     int geo_cap = 0;                 // capacity (members) of the Prim scratch
@@ -149,9 +151,11 @@ int sb_create(sb_ctx** out, int device, const sb_dims* dims) {
     sb_ctx* ctx = new sb_ctx();
     ctx->device = device;
     ctx->dims = *dims;
+    if (cudaDeviceGetAttribute(&ctx->n_sms, cudaDevAttrMultiProcessorCount, ctx->device) != cudaSuccess || ctx->n_sms < 1) ctx->n_sms = 148;
     if (const char* e = getenv("SB_K1_CTAS")) ctx->lt_want = std::max(1L, atol(e));
     if (const char* e = getenv("SB_K1_CTAS_COMPACT")) ctx->lt_want_compact = std::max(1L, atol(e));
     if (const char* e = getenv("SB_K1_BLOCK_MAX_N")) ctx->k1_block_max_n = atoi(e);
+    if (const char* e = getenv("SB_K1B_PARTS")) ctx->k1b_parts = atoi(e);
     if (const char* e = getenv("SB_K1B_THREADS")) ctx->k1b_threads = std::min(LH_THREADS, std::max(32, atoi(e) & ~31));
     if (const char* e = getenv("SB_K1S_THREADS")) ctx->k1s_threads = std::min(LH_THREADS, std::max(32, atoi(e) & ~31));
     *out = ctx;   // returned even on failure so that the caller can read sb_last_error, then sb_destroy
@@ -795,14 +799,22 @@ static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source
     // 32 codes, i.e. S + 1 <= 32 digits: S = 32 (SB_MAX_S) takes the tile-per-site kernel below
     // blocked form (one CTA per 16-feature block and chain, sb_eval.cuh): shapes with one site per code byte (S + 1 > 5),
     // S = 32, and launches over few sites, where the table kernel's per-chain prologue dominates (SB_K1_BLOCK_MAX_N)
-    const size_t fb_smem = lh_free_block_smem(d.S, d.Z, d.Fam);
-    if (!use_source && fb_smem <= 200 * 1024 && n <= 65535 && blocked_kernels_allowed() &&
+    const size_t fb_one = lh_free_block_smem(d.S, d.Z, d.Fam);
+    if (!use_source && fb_one <= 200 * 1024 && n <= 65535 && blocked_kernels_allowed() &&
         (ctx->lt.cpb == 1 || d.S + 1 > LT_ROW || d.N <= ctx->k1_block_max_n)) {
+        // CTAs per chain: enough for two CTAs per SM over the launch (a CTA's prologue and epilogue are dependent
+        // memory round trips, so few fat CTAs win: 256 chains x 500 x 100 x 4 take 29 / 34 / 36 / 50 us with 1 / 2 /
+        // 3 / 7 CTAs per chain), every CTA's tables within 48 KB (wide tables: one block per CTA).  SB_K1B_PARTS overrides.
         const int nb = d.ldx >> 4;
+        int parts = std::min(nb, std::max(1, 2 * ctx->n_sms / n));
+        while (parts < nb && lh_free_block_smem(d.S, d.Z, d.Fam, (nb + parts - 1) / parts) > 48 * 1024) ++parts;
+        if (ctx->k1b_parts > 0) parts = std::min(nb, ctx->k1b_parts);
+        const size_t fb_smem = lh_free_block_smem(d.S, d.Z, d.Fam, (nb + parts - 1) / parts);
+        if (fb_smem > 200 * 1024) FAIL(SB_E_ARG, "SB_K1B_PARTS: the tables of a CTA exceed shared memory");
         if (fb_smem > 48 * 1024)
             CK(cudaFuncSetAttribute(lh_free_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fb_smem));
-        lh_free_block_kernel<<<dim3(nb, n), ctx->k1b_threads, fb_smem, ctx->stream>>>(
-            d, ctx->st, chain_begin, ctx->partial + (size_t)chain_begin * nb, nb, ctx->lt_ticket + chain_begin);
+        lh_free_block_kernel<<<dim3(parts, n), ctx->k1b_threads, fb_smem, ctx->stream>>>(
+            d, ctx->st, chain_begin, ctx->partial + (size_t)chain_begin * nb, ctx->lt_ticket + chain_begin);
         ++ctx->launches;
         CK(cudaGetLastError());
         return SB_OK;

@@ -276,8 +276,8 @@ lh_source_block_kernel(DevData d, ChainArrays st, int chain_begin, double* __res
 // of the zone-free components (1 - w~[f][cfg][1] up to rounding; for an NA cell V = p_zone = 1).  A site with a
 // factor below 2^-120 is redone cell by cell on the exact path (log 0 = -inf as in model.py:174-176).
 // partial[chain][block] is reduced in fixed order by the chain's last CTA.
-__host__ __device__ __forceinline__ size_t lh_free_block_smem(int S, int Z, int Fam) {
-    return ((size_t)(2 + Fam + Z) * (S + 1) * 16 + 64) * sizeof(double);
+__host__ __device__ __forceinline__ size_t lh_free_block_smem(int S, int Z, int Fam, int blocks_per_cta = 1) {
+    return (size_t)blocks_per_cta * ((size_t)(2 + Fam + Z) * (S + 1) * 16 + 64) * sizeof(double);
 }
 // the 16 cells of one site folded into (am, ae, side): v_j = rho_j * V[vrow + x_j] + om_j * PZ[zrow + x_j] with ZONE,
 // else V[vrow + x_j]
@@ -332,33 +332,37 @@ __device__ __forceinline__ void lh_free_site(const uint4 xr, const int lane, con
         am = __hiloint2double((h & 0x800fffff) | 0x3ff00000, __double2loint(am));
     }
 }
+// grid = (parts per chain, chains): CTA `part` owns the feature blocks [part nb / parts, (part + 1) nb / parts) of its
+// chain (one block per CTA on wide tables; several on small ones, where a launch would otherwise be waves of CTAs that
+// are all prologue).
 __global__ void __launch_bounds__(LH_THREADS)
-lh_free_block_kernel(DevData d, ChainArrays st, int chain_begin, double* __restrict__ partial, int n_blocks,
-                     unsigned* __restrict__ ticket) {
+lh_free_block_kernel(DevData d, ChainArrays st, int chain_begin, double* __restrict__ partial, unsigned* __restrict__ ticket) {
     extern __shared__ __align__(128) double fb_tab[];
     __shared__ double red[33];
     __shared__ int is_last;
     __shared__ int zoff[SB_MAX_Z + 1];
     const int chain = chain_begin + blockIdx.y;
-    const int f0 = blockIdx.x << 4;
+    const int parts = gridDim.x, nb = d.ldx >> 4;
+    const int b0 = (int)((long)blockIdx.x * nb / parts), b1 = (int)((long)(blockIdx.x + 1) * nb / parts), nbl = b1 - b0;
     const int S = d.S, S1 = S + 1, F = d.F, N = d.N, Fam = d.Fam;
-    const int nf = min(16, F - f0), nfS = nf * S;
+    const int f_begin = b0 << 4, f_end = min(F, b1 << 4), nFS = (f_end - f_begin) * S;
     const size_t FS = (size_t)F * S;
-    // V: classes 0 .. Fam-1 families, Fam "no family", Fam+1 ones | PZ: Z zones | coef: [cfg 1 | cfg 3][rho, omega][16]
-    const int n_v = (Fam + 2) * S1 * 16, n_pz = d.Z * S1 * 16;
-    double* PZ = fb_tab + n_v;
-    double* CO = PZ + n_pz;
+    // per local block: V (classes 0 .. Fam-1 families, Fam "no family", Fam+1 ones) | PZ (Z zones) | coef [cfg 1 | cfg 3][rho, omega][16]
+    const int n_v = (Fam + 2) * S1 * 16, n_pz = d.Z * S1 * 16, blk = n_v + n_pz + 64;
     const int8_t* __restrict__ zone_id = st.zone_id + chain * st.s_zone_id;
-    // the first site of every thread is requested before the tables are built
-    int n = threadIdx.x;
+    // the first strip of every thread is requested before the tables are built; a thread walks the strips
+    // threadIdx.x + k blockDim.x of the flattened (block, site) range.  (Two and four strips in flight per thread were
+    // measured: no faster on few sites, slower at shape D -- 94 / 104 registers.)
+    int n = threadIdx.x, lb = 0;
+    while (n >= N && lb < nbl) { n -= N; ++lb; }
     uint4 xv = make_uint4(0, 0, 0, 0);
     int cls = Fam + 1;
-    if (n < N) {
-        xv = __ldg(reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + f0));
+    if (lb < nbl) {
+        xv = __ldg(reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + ((b0 + lb) << 4)));
         const int fam = d.inheritance ? d.fam_id[n] : -1;
         cls = zone_id[n] >= 0 ? Fam + 1 : (fam >= 0 ? fam : Fam);
     }
-    for (int i = threadIdx.x; i < ((n_v + n_pz + 64) >> 1); i += blockDim.x)
+    for (int i = threadIdx.x; i < (nbl * blk) >> 1; i += blockDim.x)
         reinterpret_cast<double2*>(fb_tab)[i] = make_double2(1.0, 1.0);
     if (threadIdx.x == 0) {
         int o = 0;
@@ -366,31 +370,36 @@ lh_free_block_kernel(DevData d, ChainArrays st, int chain_begin, double* __restr
         zoff[d.Z] = o;
     }
     __syncthreads();
-    if (threadIdx.x >= nf && threadIdx.x < 16) CO[16 + threadIdx.x] = CO[48 + threadIdx.x] = 0.0;   // padding columns: 1 V + 0 pz
-    {   // thread -> (group, entry i = j * S + sx of the block's contiguous [nf][S] slice); the groups split the classes
-        const int groups = max(1, (int)blockDim.x / nfS);
+    if (b1 == nb && threadIdx.x < 16 && threadIdx.x >= F - ((nb - 1) << 4)) {       // padding columns: 1 V + 0 pz
+        double* co = fb_tab + (size_t)(nbl - 1) * blk + n_v + n_pz;
+        co[16 + threadIdx.x] = co[48 + threadIdx.x] = 0.0;
+    }
+    {   // thread -> (group, entry i of the CTA's contiguous [features][S] slice); the groups split the classes
+        const int groups = max(1, (int)blockDim.x / nFS);
         const double* __restrict__ w = st.weights + chain * st.s_weights;
-        for (int i0 = threadIdx.x; i0 < groups * nfS; i0 += blockDim.x) {
-            const int g = i0 / nfS, i = i0 - g * nfS;
-            const int j = i / S, sx = i - j * S;
-            const size_t o = (size_t)f0 * S + i;
+        for (int i0 = threadIdx.x; i0 < groups * nFS; i0 += blockDim.x) {
+            const int g = i0 / nFS, i = i0 - g * nFS;
+            const int fi = i / S, sx = i - fi * S, f = f_begin + fi, j = f & 15;
+            const size_t o = (size_t)f_begin * S + i;
+            double* tab = fb_tab + (size_t)((f >> 4) - b0) * blk;
             // the entries of w~ this thread needs, with wnorm_row's arithmetic: a_c / ((a_0 + a_1) + a_2)
-            const double a0 = w[(size_t)(f0 + j) * 3], a1 = w[(size_t)(f0 + j) * 3 + 1];
-            const double a2 = d.C == 3 ? w[(size_t)(f0 + j) * 3 + 2] : 0.0;
+            const double a0 = w[(size_t)f * 3], a1 = w[(size_t)f * 3 + 1];
+            const double a2 = d.C == 3 ? w[(size_t)f * 3 + 2] : 0.0;
             const double pg = st.p_global[chain * st.s_p_global + o];
             const double s2 = (a0 + 0.0) + a2;
             const double row6 = a0 / s2, row8 = a2 / s2;                               // cfg 2: family, no zone
-            double* dst = fb_tab + sx * 16 + j;
+            double* dst = tab + sx * 16 + j;
             if (g == 0) {
                 dst[(size_t)Fam * S1 * 16] = (a0 / ((a0 + 0.0) + 0.0)) * pg;           // no family: cfg 0
                 if (sx == 0) {
                     // zone members: cfg 1 -> w~[1][0] V + w~[1][1] pz;  cfg 3 -> (1 - w~[3][1]) V + w~[3][1] pz with
                     // V = (w~[3][0] pg + w~[3][2] pf) / (w~[3][0] + w~[3][2]) = the cfg-2 value
                     const double s1 = (a0 + a1) + 0.0, s3 = (a0 + a1) + a2;
-                    CO[j] = a0 / s1;
-                    CO[16 + j] = a1 / s1;
-                    CO[32 + j] = a0 / s3 + a2 / s3;
-                    CO[48 + j] = a1 / s3;
+                    double* co = tab + n_v + n_pz;
+                    co[j] = a0 / s1;
+                    co[16 + j] = a1 / s1;
+                    co[32 + j] = a0 / s3 + a2 / s3;
+                    co[48 + j] = a1 / s3;
                 }
             }
             // the zone and family tables of this entry, eight loads in flight (they are L2 round trips)
@@ -406,7 +415,7 @@ lh_free_block_kernel(DevData d, ChainArrays st, int chain_begin, double* __restr
 #pragma unroll
                 for (int u = 0; u < 8; ++u) {
                     const int e = e0 + u * groups;
-                    if (e < d.Z) PZ[(size_t)e * S1 * 16 + sx * 16 + j] = p8[u];
+                    if (e < d.Z) tab[n_v + (size_t)e * S1 * 16 + sx * 16 + j] = p8[u];
                     else if (e < d.Z + Fam) dst[(size_t)(e - d.Z) * S1 * 16] = row6 * pg + row8 * p8[u];
                 }
             }
@@ -414,50 +423,55 @@ lh_free_block_kernel(DevData d, ChainArrays st, int chain_begin, double* __restr
     }
     __syncthreads();
     const int lane = threadIdx.x & 31;
-    const uint32_t v_s = (uint32_t)__cvta_generic_to_shared(fb_tab), pz_s = (uint32_t)__cvta_generic_to_shared(PZ);
-    const uint32_t co_s = (uint32_t)__cvta_generic_to_shared(CO);
+    const uint32_t tab_s = (uint32_t)__cvta_generic_to_shared(fb_tab), blk_b = (uint32_t)blk * 8u;
+    const uint32_t pz_o = (uint32_t)n_v * 8u, co_o = (uint32_t)(n_v + n_pz) * 8u;
     double am = 1.0, side = 0.0;                                   // running product: mantissa in [1, 4), exact logs
     int ae = 0;
-    // ---- every site as if it were in no zone (zone members read the class of ones) ----
-    {
-        while (n < N) {
-            const uint4 xr = rot_strip(xv, lane & 15);
-            const uint32_t vrow = v_s + (uint32_t)(cls * S1) * 128u;
-            n += blockDim.x;
-            if (n < N) {                                                               // next site's loads in flight
-                xv = __ldg(reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + f0));
-                const int fam = d.inheritance ? d.fam_id[n] : -1;
-                cls = zone_id[n] >= 0 ? Fam + 1 : (fam >= 0 ? fam : Fam);
-            }
-            lh_free_site<false>(xr, lane, S, vrow, 0u, 0u, am, ae, side);
+    // ---- every (site, block) strip as if the site were in no zone (zone members read the class of ones) ----
+    while (lb < nbl) {
+        const uint4 xr = rot_strip(xv, lane & 15);
+        const uint32_t vrow = tab_s + (uint32_t)lb * blk_b + (uint32_t)(cls * S1) * 128u;
+        n += blockDim.x;
+        while (n >= N && lb < nbl) { n -= N; ++lb; }
+        if (lb < nbl) {                                                                // next strip's loads in flight
+            xv = __ldg(reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + ((b0 + lb) << 4)));
+            const int fam = d.inheritance ? d.fam_id[n] : -1;
+            cls = zone_id[n] >= 0 ? Fam + 1 : (fam >= 0 ? fam : Fam);
         }
+        lh_free_site<false>(xr, lane, S, vrow, 0u, 0u, am, ae, side);
     }
     // ---- zone members, exact ----
     {
         const int* __restrict__ members = st.zone_members + chain * st.s_zone_members;
         const int n_mem = zoff[d.Z];
-        for (int m = threadIdx.x; m < n_mem; m += blockDim.x) {
+        for (int idx = threadIdx.x; idx < n_mem * nbl; idx += blockDim.x) {
+            const int l = idx / n_mem, m = idx - l * n_mem;
             int z = 0;
             while (m >= zoff[z + 1]) ++z;
-            const int n = members[(size_t)z * N + (m - zoff[z])];
-            const int fam = d.inheritance ? d.fam_id[n] : -1;
-            const uint4 xr = rot_strip(__ldg(reinterpret_cast<const uint4*>(d.x + (size_t)n * d.ldx + f0)), lane & 15);
-            lh_free_site<true>(xr, lane, S, v_s + (uint32_t)((fam >= 0 ? fam : Fam) * S1) * 128u,
-                               pz_s + (uint32_t)(z * S1) * 128u, co_s + (fam >= 0 ? 256u : 0u), am, ae, side);
+            const int ns = members[(size_t)z * N + (m - zoff[z])];
+            const int fam = d.inheritance ? d.fam_id[ns] : -1;
+            const uint4 xr = rot_strip(__ldg(reinterpret_cast<const uint4*>(d.x + (size_t)ns * d.ldx + ((b0 + l) << 4))), lane & 15);
+            const uint32_t base = tab_s + (uint32_t)l * blk_b;
+            lh_free_site<true>(xr, lane, S, base + (uint32_t)((fam >= 0 ? fam : Fam) * S1) * 128u,
+                               base + pz_o + (uint32_t)(z * S1) * 128u, base + co_o + (fam >= 0 ? 256u : 0u), am, ae, side);
         }
     }
     double v = lp_warp_value(am, ae, side);
     v = block_sum(v, red);
+    if (parts == 1) {
+        if (threadIdx.x == 0) st.ll[chain] = v;
+        return;
+    }
     if (threadIdx.x == 0) {
-        partial[(size_t)blockIdx.y * n_blocks + blockIdx.x] = v;
+        partial[(size_t)blockIdx.y * parts + blockIdx.x] = v;
         __threadfence();
-        is_last = atomicAdd(&ticket[blockIdx.y], 1u) == (unsigned)(n_blocks - 1);
+        is_last = atomicAdd(&ticket[blockIdx.y], 1u) == (unsigned)(parts - 1);
     }
     __syncthreads();
     if (is_last) {
         __threadfence();
         double t = 0.0;
-        for (int i = threadIdx.x; i < n_blocks; i += blockDim.x) t += __ldcg(&partial[(size_t)blockIdx.y * n_blocks + i]);
+        for (int i = threadIdx.x; i < parts; i += blockDim.x) t += __ldcg(&partial[(size_t)blockIdx.y * parts + i]);
         t = block_sum(t, red);
         if (threadIdx.x == 0) {
             st.ll[chain] = t;

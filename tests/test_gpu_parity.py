@@ -263,6 +263,27 @@ def test_fallback_evaluation_kernels(name, built_lib, monkeypatch):
             assert np.array_equal(fast[k], slow[k]), k
 
 
+@pytest.mark.parametrize('max_n', ['0', '1000000'])
+@pytest.mark.parametrize('name', golden_cases())
+def test_both_source_free_kernels_on_the_goldens(name, max_n, built_lib, monkeypatch):
+    """The source-free likelihood has two kernels: the table kernel (packed state codes, sb_lhtab.cuh) and the blocked
+    kernel (one CTA per range of 16-feature blocks, sb_eval.cuh), chosen by shape.  SB_K1_BLOCK_MAX_N = 0 keeps every
+    shape with two or more sites per code byte on the table kernel, 1000000 sends every shape to the blocked one (with
+    1 .. all blocks per CTA, SB_K1B_PARTS): both reproduce the reference's value."""
+    c = load_case(name)
+    g = c['g']
+    monkeypatch.setenv('SB_K1_BLOCK_MAX_N', max_n)
+    for parts in (['0'] if max_n == '0' else ['0', '1', '2', '1000']):
+        monkeypatch.setenv('SB_K1B_PARTS', parts)
+        eng = make_engine(c, n_chains=3, sample_source=False)
+        for ch in range(3):
+            set_golden_state(eng, c, ch, with_source=False)
+        ll = eng.eval()[0]
+        assert rel_err(ll, g['ref_ll_nosrc']) < RTOL, (parts, ll)
+        assert ll[0] == ll[1] == ll[2]
+        eng.close()
+
+
 @pytest.mark.parametrize('seed', range(int(__import__('os').environ.get('SB_FUZZ_SEEDS_K1', '10'))))
 def test_likelihood_kernels_on_random_large_shapes(seed, built_lib):
     """K1 (table-driven, source-free), K1 with source and the K4 recount on seeded random shapes up to 20000 sites,
