@@ -327,3 +327,41 @@ def test_likelihood_kernels_on_random_large_shapes(seed, built_lib):
     for k in range(z):
         assert np.array_equal(cnt['cnt_zone'][k], orc.state_counts_zone(data.features, st['source'], st['zones'][k]))
     eng.close()
+
+
+@pytest.mark.parametrize('shape', [(40000, 5, 3, 2, 3), (300, 20, 32, 3, 5), (500, 17, 8, 2, 150), (1500, 33, 8, 4, 0)])
+def test_blocked_kernels_at_the_edges_of_their_shapes(shape, built_lib):
+    """The blocked evaluation kernels (K1b, K1s, K4) where their layout changes: more than 32768 sites per chain (K4's
+    per-thread site tallies are flushed early), S = 32 (33 state columns, no table kernel), 150 families (the tables
+    of a block exceed shared memory: tile-per-site fallbacks), no families at S = 8."""
+    from contact_zones_b200 import synthetic
+    from contact_zones_b200.engine import Engine, state_index
+    n, f, s_, z, fam = shape
+    inh = fam > 0
+    data = synthetic.make_data(n, f, s_, n_families=fam, seed=n + f, with_dist=False, na_frac=0.05)
+    sts = [synthetic.random_state(data, z, 12, inh, True, seed=50 + i) for i in range(2)]
+    eng = Engine(state_index(data.features), data.states, data.families if inh else None, data.network['adj_mat'], None,
+                 n_zones=z, n_chains=3, inheritance=inh, sample_source=True)
+    for ch in range(3):
+        st = sts[ch % 2]
+        eng.set_state(ch, st['zones'], st['weights'], st['p_global'], st['p_zones'], st['p_families'] if inh else None,
+                      np.argmax(st['source'], -1))
+    ll_free, ll_src = eng.eval(use_source=False)[0], eng.eval(use_source=True)[0]
+    fam_b = np.asarray(data.families, bool)
+    for ch in (0, 1):
+        st = sts[ch]
+        args = (data.features, fam_b, inh, st['zones'], st['weights'], st['p_global'], st['p_zones'],
+                st['p_families'] if inh else None)
+        assert rel_err(ll_free[ch], orc.log_likelihood(*args, source=None)) < RTOL
+        assert rel_err(ll_src[ch], orc.log_likelihood(*args, source=st['source'])) < RTOL
+    assert ll_free[2] == ll_free[0] and ll_src[2] == ll_src[0]
+    st = sts[1]
+    cnt = eng.counts(1, recount=True)
+    assert np.array_equal(cnt['cnt_glob'], orc.state_counts_global(data.features, st['source']))
+    for k in range(z):
+        assert np.array_equal(cnt['cnt_zone'][k], orc.state_counts_zone(data.features, st['source'], st['zones'][k]))
+    # the source tables of gibbs_sample_weights (derived inside K4 from the per-configuration global tables)
+    assert np.array_equal(cnt['cnt_src_zone'], orc.source_counts(st['source'], st['zones'].any(0)))
+    if inh:
+        assert np.array_equal(cnt['cnt_src_fam'], orc.source_counts(st['source'], fam_b.any(0)))
+    eng.close()
