@@ -370,7 +370,7 @@ def make_sampler(data, n_chains, seed, mcmc_steps, model_cfg=None, ops=None):
                     seed=seed)
 
 
-def sampler_leg(torch, args, data, n_chains, seed, stream, barrier, flush, timed_steps, warm_steps):
+def sampler_leg(torch, args, data, n_chains, seed, stream, barrier, flush, timed_steps, warm_steps, keep_states=False):
     """Device-resident leg for one seed: chains initialised and sharded by the product (`ZoneMCMC`), warmed, then
     `timed_steps` bench steps of `--mcmc-steps` proposals per chain, each followed by the MC3 exchange -- an NCCL
     all-gather straight from the contexts' device (ll, prior) arrays into a persistent device buffer
@@ -425,7 +425,8 @@ def sampler_leg(torch, args, data, n_chains, seed, stream, barrier, flush, timed
     assert np.allclose(ll_all[-1][shard.offset:shard.offset + shard.n_local], ll_run, rtol=0, atol=0)
     acc1, rej1 = eng.op_stats()
     acc, rej = (acc1 - acc0).sum(axis=0), (rej1 - rej0).sum(axis=0)
-    out = {'seed': seed, 'step_ms': step_ms, 'kernel_ms': kernel_ms, 'exchange_ms': exch_ms, 'launches': int(launches),
+    states = [eng.get_state(c, one_hot_source=False) for c in range(shard.n_local)] if keep_states else None
+    out = {'seed': seed, 'states': states, 'step_ms': step_ms, 'kernel_ms': kernel_ms, 'exchange_ms': exch_ms, 'launches': int(launches),
            'drift': drift, 'acc': acc, 'rej': rej, 'swaps': stats, 't0': t0, 't1': t1, 'n_local': shard.n_local,
            'team': int(os.environ.get('SBAYES_B200_TEAM', 0)) or None,
            'zone_size_mean': float(np.mean([eng.get_state(c, fields=('zones',))['zones'].sum() for c in range(min(4, shard.n_local))]))}
@@ -433,28 +434,26 @@ def sampler_leg(torch, args, data, n_chains, seed, stream, barrier, flush, timed
     return out
 
 
-def host_states(data, n, first_chain, seed):
-    """`n` initial chain states as stacked, pinned host arrays (the e2e leg's inputs): the product's own
-    generate_initial_sample path for global chains first_chain .. first_chain + n - 1."""
+def host_states(states):
+    """The rank's chain states as stacked, pinned host arrays (the e2e leg's inputs): the states the device-resident leg
+    left its chains in (`Engine.get_state` of every local chain after the timed steps), so that both legs time the same
+    workload -- warmed chains -- and differ only in where the data lives."""
     import torch
-    smp = make_sampler(data, first_chain + n, seed, 1000)
-    smp.shard.world, smp.shard.rank = 1, 0                     # host-side generation only, no collective
-    samples = [smp._initial_sample_host(first_chain + c) for c in range(n)]
-    rng = np.random.default_rng([seed, 77])
-    src = rng.integers(0, 1, size=(n, D_SHAPE['N'], D_SHAPE['F']), dtype=np.uint8)      # component 0 is always valid
-    arrs = dict(zones=np.stack([s.zones for s in samples]).astype(np.uint8), weights=np.stack([s.weights for s in samples]),
-                p_global=np.stack([s.p_global[0] for s in samples]), p_zones=np.stack([s.p_zones for s in samples]),
-                p_families=np.stack([s.p_families for s in samples]), source=src)
+    arrs = dict(zones=np.stack([s['zones'] for s in states]).astype(np.uint8), weights=np.stack([s['weights'] for s in states]),
+                p_global=np.stack([s['p_global'][0] for s in states]), p_zones=np.stack([s['p_zones'] for s in states]),
+                p_families=np.stack([s['p_families'] for s in states]),
+                source=np.stack([s['source'] for s in states]).astype(np.uint8))
     return {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for k, v in arrs.items()}
 
 
-def e2e_leg(torch, args, data, nc, chain_offset, device, seed, barrier, n_steps):
+def e2e_leg(torch, args, data, nc, chain_offset, device, seed, barrier, n_steps, states):
     """The same bench step through the C ABI with HOST buffers: every step uploads all chain states of the rank from
     pinned host memory (sb_set_states), runs the launch and reads the logged chain's state and every chain's
     (ll, prior) back.  Two contexts alternate, so the upload of step k+1 (copy engine + host packing) overlaps the
     launch of step k; every step's H2D and D2H are inside the timed region."""
     from contact_zones_b200.engine import Engine
-    host = host_states(data, nc, chain_offset, seed)
+    host = host_states(states)
+    assert host['zones'].shape[0] == nc
     h2d = sum(t.numel() * t.element_size() for t in host.values())
     engs = []
     for i in range(2):
@@ -498,10 +497,17 @@ def e2e_leg(torch, args, data, nc, chain_offset, device, seed, barrier, n_steps)
         upload(e)
     e.sync()
     up_s = (time.perf_counter() - t0) / 3
+    # ... and the whole step on ONE context (upload -> launch -> read back, nothing overlapped)
+    t0 = time.perf_counter()
+    for k in range(3):
+        upload(e)
+        e.run(args.mcmc_steps)
+        read(e)
+    serial_s = (time.perf_counter() - t0) / 3
     for e in engs:
         e.close()
     return {'s_per_step': dt, 'h2d': int(h2d), 'd2h': int(d2h), 'launches': int(launches), 'upload_ms': 1e3 * up_s,
-            'upload_gbs': h2d / up_s / 1e9}
+            'upload_gbs': h2d / up_s / 1e9, 'serial_s_per_step': serial_s}
 
 
 def api_leg(torch, data, n_chains, n_steps, n_samples, seed, model_cfg=None, ops=None):
@@ -621,7 +627,8 @@ def run_gpu_arm(args, rank, world, local_rank):
     clocks = ClockSampler(local_rank) if rank == 0 else None
     legs = []
     for seed in args.seeds:
-        leg = sampler_leg(torch, args, data, chains_total, seed, stream, barrier, flush, args.steps, args.warmup)
+        leg = sampler_leg(torch, args, data, chains_total, seed, stream, barrier, flush, args.steps, args.warmup,
+                          keep_states=seed == args.seeds[0])
         leg['step_ms'], leg['kernel_ms'] = rank_max(leg['step_ms'], leg['kernel_ms'])
         legs.append(leg)
     order = sorted(range(len(legs)), key=lambda i: legs[i]['step_ms'])
@@ -652,8 +659,9 @@ def run_gpu_arm(args, rank, world, local_rank):
 
     # ---- e2e leg: host buffers in, host results out, every step ----------------------------------------------------
     nc_local = chains_total // world
-    e2e = e2e_leg(torch, args, data, nc_local, rank * nc_local, local_rank, args.seeds[0], barrier, args.e2e_steps)
-    (e2e_s,) = rank_max(e2e['s_per_step'])
+    e2e = e2e_leg(torch, args, data, nc_local, rank * nc_local, local_rank, args.seeds[0], barrier, args.e2e_steps,
+                  legs[0].pop('states'))
+    e2e_s, e2e_serial_s = rank_max(e2e['s_per_step'], e2e['serial_s_per_step'])
     e2e_value = proposals / e2e_s
 
     # ---- the drop-in API end to end (sharded ZoneMCMC.generate_samples, 1000 steps per logged sample) --------------
@@ -707,7 +715,12 @@ def run_gpu_arm(args, rank, world, local_rank):
         'e2e': {'value': e2e_value, 'unit': 'proposals/s', 'h2d_bytes_per_step': e2e['h2d'],
                 'd2h_bytes_per_step': e2e['d2h'], 'steps': args.e2e_steps, 'upload_ms': e2e['upload_ms'],
                 'upload_gbs': e2e['upload_gbs'],
-                'pipeline': 'two contexts alternate: the upload of step k+1 overlaps the launch of step k'},
+                'serial_value': proposals / e2e_serial_s,
+                'pipeline': 'two contexts alternate: the upload of step k+1 overlaps the launch of step k, and the launch '
+                            'of step k+1 starts on the SMs that the finished chains of step k free (a launch lasts as long as '
+                            'its slowest chain), which is why e2e can exceed the one-stream device rate `value`; '
+                            'serial_value = upload -> launch -> read back on one context, nothing overlapped; inputs = '
+                            'the warmed chain states of the device leg, re-uploaded from pinned host memory every step'},
         'gpu_launches': int(sum(l['launches'] for l in legs)),
         'kernel_ms_per_step': med['kernel_ms'], 'exchange_ms_per_step': med['exchange_ms'],
         'us_per_proposal_per_chain': 1e3 * med['kernel_ms'] / args.mcmc_steps,
@@ -739,7 +752,7 @@ def main():
     ap.add_argument('--api-steps', type=int, default=100000, help='N_STEPS of the ZoneMCMC.generate_samples leg')
     ap.add_argument('--no-weak', action='store_true')
     ap.add_argument('--no-api-leg', action='store_true')
-    ap.add_argument('--e2e-steps', type=int, default=5)
+    ap.add_argument('--e2e-steps', type=int, default=12)
     ap.add_argument('--cpu-proposals', type=int, default=400, help='proposals per host process in the CPU sample')
     ap.add_argument('--seed', type=int, default=1)
     ap.add_argument('--no-cpu-baseline', action='store_true')
