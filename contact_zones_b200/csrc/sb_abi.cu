@@ -30,6 +30,12 @@ struct sb_ctx {
     DevData d{};
     ChainArrays st{};
     cudaStream_t own_stream = nullptr, stream = nullptr;
+    // snapshot read-back next to a launch in flight: sb_read_snapshot copies on its own stream, after the event of the
+    // launch that wrote the slot (two events, by launch parity: waiting for a later launch of the same parity is safe)
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t run_done[2] = {nullptr, nullptr};
+    long long n_event_launches = 0;
+    std::vector<long long> slot_launch;          // per ring slot: the sb_run_events launch that wrote it last (0 = never)
     std::string err;
     bool has_data = false, has_priors = false, has_ops = false;
     std::vector<void*> allocs;
@@ -225,6 +231,9 @@ int sb_destroy(sb_ctx* ctx) {
         if (sg.buf) cudaFreeHost(sg.buf);
     }
     if (ctx->direct_done) cudaEventDestroy(ctx->direct_done);
+    if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
+    for (cudaEvent_t e : ctx->run_done)
+        if (e) cudaEventDestroy(e);
     if (ctx->src_scratch) cudaFree(ctx->src_scratch);
     if (ctx->d_events) cudaFree(ctx->d_events);
     if (ctx->d_ev_scalars) cudaFree(ctx->d_ev_scalars);
@@ -1398,10 +1407,16 @@ int sb_run_events(sb_ctx* ctx, int64_t n_steps, int n_events, const int32_t* eve
         ctx->ring_rec = ring_record_bytes(ctx->st);
         const size_t need = (size_t)n_slots * nc * ctx->ring_rec;
         if (need > ctx->ring_cap) {
+            // (the slots of an earlier launch may not have been read yet: the ring keeps its content when it grows)
             CK(cudaStreamSynchronize(ctx->stream));
-            if (ctx->d_ring) CK(cudaFree(ctx->d_ring));
-            ctx->d_ring = nullptr;
-            CK(cudaMalloc((void**)&ctx->d_ring, need));
+            if (ctx->copy_stream) CK(cudaStreamSynchronize(ctx->copy_stream));
+            unsigned char* grown = nullptr;
+            CK(cudaMalloc((void**)&grown, need));
+            if (ctx->d_ring) {
+                CK(cudaMemcpy(grown, ctx->d_ring, ctx->ring_cap, cudaMemcpyDeviceToDevice));
+                CK(cudaFree(ctx->d_ring));
+            }
+            ctx->d_ring = grown;
             ctx->ring_cap = need;
         }
         // the events travel through the pinned staging buffer (the call returns without a synchronisation)
@@ -1415,10 +1430,16 @@ int sb_run_events(sb_ctx* ctx, int64_t n_steps, int n_events, const int32_t* eve
     }
     sp.events = ctx->d_events; sp.n_events = n_events; sp.ev_scalars = ctx->d_ev_scalars;
     sp.ring = ctx->d_ring; sp.ring_rec = ctx->ring_rec; sp.ring_chain = ring_chain;
-    ctx->ring_slots = n_slots;
+    ctx->ring_slots = std::max(ctx->ring_slots, n_slots);
     int r = launch_steps(ctx, sp, (long long)n_steps);
     if (r != SB_OK) return r;
     ctx->steps_done += n_steps;
+    const long long id = ++ctx->n_event_launches;
+    if (!ctx->run_done[id & 1]) CK(cudaEventCreateWithFlags(&ctx->run_done[id & 1], cudaEventDisableTiming));
+    CK(cudaEventRecord(ctx->run_done[id & 1], ctx->stream));
+    if ((int)ctx->slot_launch.size() < ctx->ring_slots) ctx->slot_launch.resize((size_t)ctx->ring_slots, 0);
+    for (int k = 0; k < n_events; ++k)
+        if (event_slots[k] >= 0) ctx->slot_launch[(size_t)event_slots[k]] = id;
     return SB_OK;
 }
 
@@ -1462,7 +1483,8 @@ int sb_read_snapshot(sb_ctx* ctx, int slot, int chain, uint8_t* zones, double* w
     CK(cudaSetDevice(ctx->device));
     int r = check_chain(ctx, chain);
     if (r != SB_OK) return r;
-    if (slot < 0 || slot >= ctx->ring_slots) FAIL(SB_E_ARG, "snapshot slot out of range");
+    if (slot < 0 || slot >= (int)ctx->slot_launch.size() || ctx->slot_launch[(size_t)slot] == 0)
+        FAIL(SB_E_ARG, "snapshot slot out of range (no launch has written it)");
     const DevData& d = ctx->d;
     const ChainArrays& st = ctx->st;
     const int N = d.N, F = d.F, S = d.S, Z = d.Z, C = d.C, Fam = d.Fam;
@@ -1472,8 +1494,12 @@ int sb_read_snapshot(sb_ctx* ctx, int slot, int chain, uint8_t* zones, double* w
     if (r != SB_OK) return r;
     unsigned char* b = sg->buf;
     const unsigned char* rec = ctx->d_ring + ((size_t)slot * ctx->dims.n_chains + chain) * ctx->ring_rec;
-    CK(cudaMemcpyAsync(b, rec, ctx->ring_rec, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
+    // on the copy stream, behind the launch that wrote the slot: a later launch in flight (which writes other slots) is
+    // not waited for
+    if (!ctx->copy_stream) CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->run_done[ctx->slot_launch[(size_t)slot] & 1], 0));
+    CK(cudaMemcpyAsync(b, rec, ctx->ring_rec, cudaMemcpyDeviceToHost, ctx->copy_stream));
+    CK(cudaStreamSynchronize(ctx->copy_stream));
     size_t off = 0;
     if (zones && Z > 0) {
         const int8_t* zid = reinterpret_cast<const int8_t*>(b);

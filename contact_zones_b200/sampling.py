@@ -9,6 +9,7 @@ comes from one seeded numpy Generator instead of the reference's two global gene
 """
 import logging
 import math
+import os
 import time
 from collections import defaultdict
 
@@ -349,22 +350,26 @@ class ZoneMCMC(object):
     # events per persistent launch / bytes of snapshot ring per launch (the ring holds one record per logged sample
     # and resident chain under MC3, one per logged sample otherwise)
     MAX_EVENTS_PER_LAUNCH = 4096
-    RING_BYTES_PER_LAUNCH = 256 << 20
+    RING_BYTES_PER_LAUNCH = 256 << 20     # (x 2: consecutive launches alternate between two halves of the ring; 1 / 4 GB
+                                          # were measured: no faster, and multi-GB allocations stall now and then)
 
-    def _snapshot_sample(self, slot, chain):
-        """The logged `Sample` of GLOBAL chain `chain` from snapshot `slot` of its owner's ring, on every rank."""
+    def _snapshot_samples(self, requests):
+        """The logged `Sample`s of a launch: `requests` = [(snapshot slot, GLOBAL chain)], each read from the ring of the
+        chain's owner; every rank gets all of them in one collective (`ChainShard.gather_states`)."""
         eng = self._engine
-        owner, local = self.shard.owner(chain)
 
-        def local_arrays():
-            st = eng.read_snapshot(slot, local)
+        def local_arrays(key):
+            slot, chain = key
+            st = eng.read_snapshot(slot, self.shard.owner(chain)[1])
             d = {'zones': st['zones'], 'weights': st['weights'], 'p_global': st['p_global'], 'p_zones': st['p_zones']}
             if self.inheritance:
                 d['p_families'] = st['p_families']
             return d
 
-        a = self.shard.broadcast_state(chain, local_arrays, self._template(False), self._dist_device)
-        return Sample(a['zones'], a['weights'], a['p_global'], a['p_zones'], a.get('p_families'), source=None, chain=chain)
+        got = self.shard.gather_states([(chain, (slot, chain)) for slot, chain in requests], local_arrays,
+                                       self._template(False), self._dist_device)
+        return [Sample(a['zones'], a['weights'], a['p_global'], a['p_zones'], a.get('p_families'), source=None, chain=chain)
+                for a, (_, chain) in zip(got, requests)]
 
     # evaluation API of the reference sampler (mcmc_generative.py:86-126)
     def prior(self, sample, chain):
@@ -450,8 +455,8 @@ class ZoneMCMC(object):
         if not self.mc3:
             owner, local = self.shard.owner(self.chain_idx[0])
             ring_chain = local if owner == self.shard.rank else None
-        done = 0
-        i = 0
+        # the launches of the run: consecutive stops, as many logging points each as the ring holds
+        launches, i = [], 0
         while i < len(stops):
             batch, n_logs = [], 0
             while i < len(stops) and len(batch) < self.MAX_EVENTS_PER_LAUNCH:
@@ -461,30 +466,61 @@ class ZoneMCMC(object):
                 batch.append(t)
                 n_logs += t in log_at
                 i += 1
-            slots, k = [], 0
+            launches.append(batch)
+
+        def enqueue(b):
+            # consecutive launches write alternating halves of the ring, so that launch b + 1 can run while the host
+            # reads the snapshots of launch b
+            batch, first = launches[b], (launches[b - 1][-1] if b else 0)
+            slots, k = [], (b & 1) * max_logs
             for t in batch:
                 if t in log_at and ring_chain is not None:
                     slots.append(k)
                     k += 1
                 else:
                     slots.append(-1)
-            eng.run_events(batch[-1] - done, [t - done for t in batch], slots, -1 if ring_chain is None else ring_chain)
-            ll_ev, pr_ev = eng.event_scalars(len(batch))
+            eng.run_events(batch[-1] - first, [t - first for t in batch], slots, -1 if ring_chain is None else ring_chain)
+
+        trace = {} if os.environ.get('SBAYES_B200_TRACE') else None          # seconds per host phase of the run
+
+        def lap(name, t0):
+            if trace is not None:
+                trace[name] = trace.get(name, 0.0) + time.time() - t0
+            return time.time()
+
+        if launches:
+            enqueue(0)
+        for b, batch in enumerate(launches):
+            t0 = time.time()
+            ll_ev, pr_ev = eng.event_scalars(len(batch))                   # waits for launch b
+            t0 = lap('wait for the launch', t0)
+            if b + 1 < len(launches):
+                enqueue(b + 1)                                             # ... which runs under the host work below
+            t0 = lap('enqueue', t0)
             if self.sample_from_prior:
                 ll_ev = np.zeros_like(ll_ev)
             ll_ev, pr_ev = self.shard.all_gather_events(ll_ev, pr_ev, self._dist_device)
-            k = 0
+            t0 = lap('all-gather of the event scalars', t0)
+            # replay of the launch's events in order: the swaps move the labels, so the chain that carries label 0 at
+            # every logging point is known only now; its snapshots are then fetched together (one collective per launch)
+            k, logged = (b & 1) * max_logs, []
             for j, t in enumerate(batch):
                 self._ll, self._prior = ll_ev[j], pr_ev[j]                 # (ll, prior) of every chain after t steps
                 if t in log_at:
-                    c0 = self.chain_idx[0]
-                    self.log_sample_statistics(self._snapshot_sample(k, c0), c=c0, sample_id=log_at[t])
+                    logged.append((j, t, k, self.chain_idx[0]))
                     k += 1
                 if t in swap_at:
                     self.swap_chains(None)
                 if t in screen_at:
                     self.print_screen_log(t, None)
-            done = batch[-1]
+            t0 = lap('replay of swaps', t0)
+            for (j, t, _, c0), sample in zip(logged, self._snapshot_samples([(k_, c0) for _, _, k_, c0 in logged])):
+                self._ll, self._prior = ll_ev[j], pr_ev[j]
+                self.log_sample_statistics(sample, c=c0, sample_id=log_at[t])
+            self._ll, self._prior = ll_ev[-1], pr_ev[-1]
+            lap('snapshots', t0)
+        if trace is not None:
+            print('generate_samples host phases [s]:', {k: round(v, 4) for k, v in trace.items()}, 'launches', len(launches))
         if n_steps > 1:
             self.log_last_sample(self._fetch_sample(self.chain_idx[0], with_source=True))
         eng.sync()

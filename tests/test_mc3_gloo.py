@@ -47,8 +47,18 @@ def _worker(rank, world, port, out):
         return {'zones': np.arange(12).reshape(3, 4) % 2 == (c % 2), 'weights': np.full((2, 3), float(c))}
 
     snap = shard.broadcast_state(chain_idx[0], local_arrays, {'zones': ((3, 4), bool), 'weights': ((2, 3), float)})
+    # the per-launch form: several (chain, key) requests in one collective, every owner evaluated only for its own
+    asked = []
+
+    def arrays_of(key):
+        asked.append(key)
+        return {'zones': np.arange(12).reshape(3, 4) % 3 == (key % 3), 'weights': np.full((2, 3), -0.5 * key)}
+
+    reqs = [(c, 10 * c + i) for i, c in enumerate([0, 6, 3, 4, 6])]
+    many = shard.gather_states(reqs, arrays_of, {'zones': ((3, 4), bool), 'weights': ((2, 3), float)})
     out[rank] = dict(counts=shard.counts, offset=shard.offset, ll=g_ll, pr=g_pr, idx=chain_idx, stats=stats,
-                     owner=shard.owner(chain_idx[0])[0], calls=calls, w=snap['weights'], z=snap['zones'])
+                     owner=shard.owner(chain_idx[0])[0], calls=calls, w=snap['weights'], z=snap['zones'],
+                     asked=asked, many=[(m['zones'], m['weights']) for m in many], reqs=reqs)
     dist.destroy_process_group()
 
 
@@ -76,6 +86,12 @@ def test_mc3_exchange_world2():
     s = ChainShard(N_CHAINS, rank=0, world=1)
     assert s.n_local == N_CHAINS and s.owner(5) == (0, 5)
 
+    # gather_states: identical results on both ranks, each request evaluated on its owner only (chains 0-3 -> rank 0)
+    assert r0['asked'] == [k for c, k in r0['reqs'] if c < 4] and r1['asked'] == [k for c, k in r0['reqs'] if c >= 4]
+    for (c, key), (z0, w0), (z1, w1) in zip(r0['reqs'], r0['many'], r1['many']):
+        assert np.array_equal(z0, np.arange(12).reshape(3, 4) % 3 == (key % 3)) and z0.dtype == bool
+        assert np.array_equal(w0, np.full((2, 3), -0.5 * key))
+        assert np.array_equal(z0, z1) and np.array_equal(w0, w1)
 
 def test_swap_accepts_better_chain():
     """mcmc_generative.py:263-274: label 0 moves to a chain whose posterior is higher with probability 1."""
