@@ -209,7 +209,11 @@ int sb_set_sample_from_prior(sb_ctx* ctx, int on);
  * mcmc_generative.py:205-231) instead of one launch per event: after event_steps[k] completed steps of this launch
  * (ascending, 1 <= step <= n_steps) every chain records (ll, prior); if event_slots[k] >= 0 the state of chain
  * `ring_chain` (-1 = of every chain: under MC3 the logged label moves between chains) is copied into snapshot slot
- * event_slots[k] of a device ring.  Asynchronous; read with sb_read_event_scalars / sb_read_snapshot. */
+ * event_slots[k] of a device ring.  Asynchronous; read with sb_read_event_scalars / sb_read_snapshot.
+ * The ring grows to the largest slot ever named and keeps its content, and sb_read_snapshot(slot) waits only for the
+ * launch that wrote that slot (it copies on a stream of its own): a caller that alternates between two ranges of slots
+ * can enqueue launch b + 1 right after sb_read_event_scalars of launch b and read b's snapshots while b + 1 runs
+ * (contact_zones_b200/sampling.py:generate_samples does). */
 int sb_run_events(sb_ctx* ctx, int64_t n_steps, int n_events, const int32_t* event_steps, const int32_t* event_slots,
                   int ring_chain);
 int sb_read_event_scalars(sb_ctx* ctx, int n_events, double* ll, double* prior);   /* (n_events, n_chains) each */
