@@ -140,9 +140,10 @@ class ChainShard:
 
     def gather_states(self, requests, arrays_local, template, device=None):
         """Every rank gets the state arrays of a LIST of (global chain, key) requests, each from the chain's owner, in ONE
-        collective: every rank packs the requests it owns into its rows of an (n_requests, n) matrix (zeros elsewhere) and
-        the matrices are all-gathered.  This is the per-launch form of `broadcast_state`: the logged snapshots of a whole
-        launch move in one collective instead of one broadcast per logged sample.
+        collective: every rank packs the requests it owns into a matrix of (most requests of one owner, n) rows, the
+        matrices are all-gathered (the collective the swap exchange uses anyway), and request r is row (position of r
+        among its owner's requests) of its owner's matrix.  This is the per-launch form of `broadcast_state`: the logged
+        snapshots of a whole launch move in one collective instead of one broadcast per logged sample.
         `arrays_local(key)`: evaluated on the owner only, returns {name: array}; `template` as in `broadcast_state`."""
         dist = _dist()
         if dist is None or self.world == 1:
@@ -152,39 +153,28 @@ class ChainShard:
         import torch
         keys = sorted(template)
         n = int(sum(int(np.prod(template[k][0])) for k in keys))
-        cuda = device is not None and torch.device(device).type == 'cuda'
-        cache = self.__dict__.setdefault('_gather_buf', {})                # pinned staging, kept between launches
-        mat = cache.get((len(requests), n))
-        if mat is None:
-            mat = torch.zeros(len(requests), n, dtype=torch.float64)
-            if cuda:
-                mat = mat.pin_memory()
-            cache.clear()
-            cache[(len(requests), n)] = mat
-        else:
-            mat.zero_()
-        rows = mat.numpy()
+        owners = [self.owner(chain)[0] for chain, _ in requests]
+        pos, per_owner = [], [0] * self.world
+        for o in owners:
+            pos.append(per_owner[o])
+            per_owner[o] += 1
+        m = max(per_owner)
+        rows = np.zeros((m, n))
         for r, (chain, key) in enumerate(requests):
-            if self.owner(chain)[0] == self.rank:
+            if owners[r] == self.rank:
                 arrs = arrays_local(key)
                 o = 0
                 for k in keys:
                     sz = int(np.prod(template[k][0]))
-                    rows[r, o:o + sz] = np.asarray(arrs[k], dtype=np.float64).ravel()
+                    rows[pos[r], o:o + sz] = np.asarray(arrs[k], dtype=np.float64).ravel()
                     o += sz
-        # one all-gather of the ranks' matrices (the collective the swap exchange uses anyway: no new NCCL channels), then
-        # every request's row is taken from its owner's matrix on the device and ONE copy brings the (n_requests, n)
-        # result to the host
-        t = mat.to(device, non_blocking=True) if device is not None else mat
-        allm = torch.empty(self.world * len(requests) * n, dtype=torch.float64, device=t.device)
+        t = torch.from_numpy(rows)
+        if device is not None:
+            t = t.to(device)
+        allm = torch.empty(self.world * m * n, dtype=torch.float64, device=t.device)
         dist.all_gather_into_tensor(allm, t.reshape(-1))
-        owners = torch.tensor([self.owner(chain)[0] for chain, _ in requests], device=t.device)
-        sel = allm.view(self.world, len(requests), n)[owners, torch.arange(len(requests), device=t.device)]
-        if cuda:
-            mat.copy_(sel)                                                  # pinned destination
-            flat = rows
-        else:
-            flat = sel.numpy()
+        index = torch.tensor([o * m + p for o, p in zip(owners, pos)], device=t.device)
+        flat = allm.view(self.world * m, n).index_select(0, index).cpu().numpy()
         out = []
         for r in range(len(requests)):
             d, o = {}, 0
