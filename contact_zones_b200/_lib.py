@@ -31,7 +31,7 @@ SYMBOLS = [
     'sb_upload_data', 'sb_upload_locations', 'sb_set_priors', 'sb_set_state', 'sb_set_states', 'sb_get_state', 'sb_copy_state',
     'sb_eval', 'sb_eval_likelihood_async', 'sb_read_ll', 'sb_eval_likelihood_noalloc', 'sb_eval_components', 'sb_source_posterior',
     'sb_counts', 'sb_recount_async', 'sb_device_scalars', 'sb_move_log_q', 'sb_pair_log_q', 'sb_set_operators', 'sb_run', 'sb_set_sample_from_prior',
-    'sb_run_events', 'sb_read_event_scalars', 'sb_read_snapshot', 'sb_read_chain_scalars', 'sb_chain_errors',
+    'sb_run_events', 'sb_read_event_scalars', 'sb_read_snapshot', 'sb_snapshot_ring', 'sb_read_chain_scalars', 'sb_chain_errors',
     'sb_read_op_stats', 'sb_step_counter', 'sb_kernel_launches', 'sb_rng_sample',
 ]
 
@@ -100,6 +100,7 @@ def load():
         'sb_run_events': ([vp, i64, i32, vp, vp, i32], i32),
         'sb_read_event_scalars': ([vp, i32, vp, vp], i32),
         'sb_read_snapshot': ([vp, i32, i32] + [vp] * 5, i32),
+        'sb_snapshot_ring': ([vp, C.POINTER(vp), C.POINTER(i64), C.POINTER(i64), vp, vp], i32),
         'sb_chain_errors': ([vp, vp], i32),
         'sb_recount_async': ([vp, i32, i32], i32),
         'sb_device_scalars': ([vp, C.POINTER(vp), C.POINTER(vp)], i32),

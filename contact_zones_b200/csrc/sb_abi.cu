@@ -1522,6 +1522,22 @@ int sb_read_snapshot(sb_ctx* ctx, int slot, int chain, uint8_t* zones, double* w
     return SB_OK;
 }
 
+int sb_snapshot_ring(sb_ctx* ctx, void** ring, int64_t* record_bytes, int64_t* n_records, int64_t* offsets, int64_t* lengths) {
+    if (!ctx || !ring || !record_bytes || !n_records) return SB_E_ARG;
+    const ChainArrays& st = ctx->st;
+    const size_t len[5] = {st.s_zone_id, st.s_weights * 8, st.s_p_global * 8, st.s_p_zones * 8, st.s_p_fam * 8};
+    size_t off = 0;
+    for (int a = 0; a < 5; ++a) {
+        if (offsets) offsets[a] = (int64_t)off;
+        if (lengths) lengths[a] = (int64_t)len[a];
+        off += ring_align(len[a]);
+    }
+    *ring = ctx->d_ring;
+    *record_bytes = (int64_t)off;
+    *n_records = ctx->d_ring ? (int64_t)(ctx->ring_cap / off) : 0;
+    return SB_OK;
+}
+
 int sb_read_chain_scalars(sb_ctx* ctx, double* ll, double* prior) {
     if (!ctx) return SB_E_ARG;
     CK(cudaSetDevice(ctx->device));

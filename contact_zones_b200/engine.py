@@ -331,6 +331,35 @@ class Engine:
         return {'zones': zones.astype(bool), 'weights': w, 'p_global': pg, 'p_zones': pz, 'p_families': pf,
                 'source': None}
 
+    def snapshot_ring(self):
+        """The device snapshot ring as a zero-copy torch view (n_records, record_bytes) of uint8 -- record (slot, chain)
+        is row slot * n_chains + chain -- or None before the first `run_events` with a snapshot slot."""
+        import torch
+        a, rec, n = C.c_void_p(), C.c_int64(), C.c_int64()
+        off, ln = np.zeros(5, np.int64), np.zeros(5, np.int64)
+        self._check(self.lib.sb_snapshot_ring(self._ctx, C.byref(a), C.byref(rec), C.byref(n), ptr(off), ptr(ln)))
+        self._ring_layout, self.ring_record_size = (off, ln), int(rec.value)
+        if not a.value or n.value == 0:
+            return None
+
+        class _Dev:
+            def __init__(self, addr, shape):
+                self.__cuda_array_interface__ = {'shape': shape, 'typestr': '|u1', 'data': (addr, False), 'version': 2}
+        return torch.as_tensor(_Dev(a.value, (int(n.value), int(rec.value))), device=torch.device('cuda', self.device))
+
+    def unpack_record(self, rec):
+        """One snapshot record (uint8 array, `snapshot_ring` row) -> the arrays `read_snapshot` returns."""
+        off, ln = self._ring_layout
+        zid = rec[off[0]:off[0] + self.N].view(np.int8)
+        zones = zid[None, :] == np.arange(self.Z, dtype=np.int8)[:, None]
+
+        def f64(a, shape):
+            return rec[off[a]:off[a] + int(np.prod(shape)) * 8].view(np.float64).reshape(shape).copy()
+        fs = (self.F, self.S)
+        return {'zones': zones, 'weights': f64(1, (self.F, 3))[:, :self.C].copy(), 'p_global': f64(2, (1,) + fs),
+                'p_zones': f64(3, (self.Z,) + fs), 'p_families': f64(4, (self.Fam,) + fs) if self.inheritance else None,
+                'source': None}
+
     def chain_errors(self):
         e = np.zeros(self.n_chains, np.int32)
         self._check(self.lib.sb_chain_errors(self._ctx, ptr(e)))

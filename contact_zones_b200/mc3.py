@@ -187,6 +187,35 @@ class ChainShard:
         return out
 
 
+    def gather_records(self, requests, ring):
+        """The device form of `gather_states`: `requests` = [(global chain, record index in the OWNER's ring)], `ring` =
+        this rank's snapshot ring as a (n_records, record_bytes) uint8 device tensor (Engine.snapshot_ring).  Every rank
+        selects the records it owns on the device, the ranks' (most records of one owner, record_bytes) blocks are
+        all-gathered and ONE device-to-host copy returns the (n_requests, record_bytes) records in request order: no host
+        hop on the owner, no per-sample transfer."""
+        import torch
+        dist = _dist()
+        if not requests:
+            return np.zeros((0, 0), np.uint8)
+        owners = [self.owner(chain)[0] for chain, _ in requests]
+        if dist is None or self.world == 1:
+            idx = torch.tensor([r for _, r in requests], device=ring.device)
+            return ring.index_select(0, idx).cpu().numpy()
+        pos, per_owner = [], [0] * self.world
+        for o in owners:
+            pos.append(per_owner[o])
+            per_owner[o] += 1
+        m = max(per_owner)
+        mine = [r for (_, r), o in zip(requests, owners) if o == self.rank]
+        block = torch.zeros(m, ring.shape[1], dtype=torch.uint8, device=ring.device)
+        if mine:
+            block[:len(mine)] = ring.index_select(0, torch.tensor(mine, device=ring.device))
+        allb = torch.empty(self.world * m, ring.shape[1], dtype=torch.uint8, device=ring.device)
+        dist.all_gather_into_tensor(allb, block)
+        index = torch.tensor([o * m + p for o, p in zip(owners, pos)], device=ring.device)
+        return allb.index_select(0, index).cpu().numpy()
+
+
 def swap_chains(chain_idx, ll, prior, chain_swaps, rng, statistics=None):
     """`MCMCGenerative.swap_chains` (mcmc_generative.py:242-280) on gathered scalars.  `chain_idx` (list, label ->
     chain) is permuted in place; `rng` is a numpy Generator every rank seeds identically, so all ranks agree."""

@@ -354,22 +354,24 @@ class ZoneMCMC(object):
                                           # were measured: no faster, and multi-GB allocations stall now and then)
 
     def _snapshot_samples(self, requests):
-        """The logged `Sample`s of a launch: `requests` = [(snapshot slot, GLOBAL chain)], each read from the ring of the
-        chain's owner; every rank gets all of them in one collective (`ChainShard.gather_states`)."""
+        """The logged `Sample`s of a launch: `requests` = [(snapshot slot, GLOBAL chain)], each taken from the ring of the
+        chain's owner; every rank gets all of them in one collective on device memory (`ChainShard.gather_records`)."""
         eng = self._engine
-
-        def local_arrays(key):
-            slot, chain = key
-            st = eng.read_snapshot(slot, self.shard.owner(chain)[1])
-            d = {'zones': st['zones'], 'weights': st['weights'], 'p_global': st['p_global'], 'p_zones': st['p_zones']}
-            if self.inheritance:
-                d['p_families'] = st['p_families']
-            return d
-
-        got = self.shard.gather_states([(chain, (slot, chain)) for slot, chain in requests], local_arrays,
-                                       self._template(False), self._dist_device)
-        return [Sample(a['zones'], a['weights'], a['p_global'], a['p_zones'], a.get('p_families'), source=None, chain=chain)
-                for a, (_, chain) in zip(got, requests)]
+        if not requests:
+            return []
+        ring = eng.snapshot_ring()
+        if ring is None:                     # a rank whose chains are never logged (no MC3) has no ring: it only receives
+            import torch
+            ring = torch.zeros(1, eng.ring_record_size, dtype=torch.uint8, device=torch.device('cuda', eng.device))
+        recs = self.shard.gather_records(
+            [(chain, slot * self.shard.counts[self.shard.owner(chain)[0]] + self.shard.owner(chain)[1])
+             for slot, chain in requests], ring)
+        out = []
+        for rec, (_, chain) in zip(recs, requests):
+            a = eng.unpack_record(rec)
+            out.append(Sample(a['zones'], a['weights'], a['p_global'], a['p_zones'], a['p_families'] if self.inheritance else None,
+                              source=None, chain=chain))
+        return out
 
     # evaluation API of the reference sampler (mcmc_generative.py:86-126)
     def prior(self, sample, chain):

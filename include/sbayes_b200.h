@@ -219,6 +219,14 @@ int sb_run_events(sb_ctx* ctx, int64_t n_steps, int n_events, const int32_t* eve
 int sb_read_event_scalars(sb_ctx* ctx, int n_events, double* ll, double* prior);   /* (n_events, n_chains) each */
 int sb_read_snapshot(sb_ctx* ctx, int slot, int chain, uint8_t* zones, double* weights, double* p_global,
                      double* p_zones, double* p_families /* any may be NULL */);
+/* DEVICE address and layout of the snapshot ring, for callers that move logged samples between GPUs without a host hop
+ * (contact_zones_b200/mc3.py:gather_records all-gathers the records with NCCL): record (slot, chain) is record_bytes
+ * bytes at index slot * n_chains + chain; field a of a record -- 0 zone ids int8[N] (-1 = no zone), 1 weights f64[F][3],
+ * 2 p_global f64[F][S], 3 p_zones f64[Z][F][S], 4 p_families f64[Fam][F][S] -- is lengths[a] bytes at offsets[a].  The
+ * address is valid until the next sb_run_events that names a larger slot (ring == NULL before the first one); the
+ * caller orders its reads behind the launch that wrote a slot (sb_read_event_scalars of that launch has returned).
+ * No reference counterpart (the reference logs Python objects, mcmc_generative.py:360-365). */
+int sb_snapshot_ring(sb_ctx* ctx, void** ring, int64_t* record_bytes, int64_t* n_records, int64_t offsets[5], int64_t lengths[5]);
 int sb_read_chain_scalars(sb_ctx* ctx, double* ll, double* prior);              /* (n_chains) each; SB_E_NUMERIC if flagged */
 /* DEVICE addresses of the running (ll, prior) arrays, n_chains doubles each, valid until sb_destroy: the MC3 exchange
  * (mcmc_generative.py:242-280) all-gathers them with NCCL on the context's stream without a host hop */
