@@ -56,9 +56,14 @@ def _worker(rank, world, port, out):
 
     reqs = [(c, 10 * c + i) for i, c in enumerate([0, 6, 3, 4, 6])]
     many = shard.gather_states(reqs, arrays_of, {'zones': ((3, 4), bool), 'weights': ((2, 3), float)})
+    # ... and its device form on raw ring records: rank r's ring holds 100 r + record index in every byte
+    import torch
+    ring = (torch.arange(6, dtype=torch.uint8)[:, None] + 100 * rank).repeat(1, 32)
+    rec_reqs = [(0, 2), (6, 1), (5, 5), (3, 0), (4, 3)]                     # (global chain, record index on its owner)
+    recs = shard.gather_records(rec_reqs, ring)
     out[rank] = dict(counts=shard.counts, offset=shard.offset, ll=g_ll, pr=g_pr, idx=chain_idx, stats=stats,
                      owner=shard.owner(chain_idx[0])[0], calls=calls, w=snap['weights'], z=snap['zones'],
-                     asked=asked, many=[(m['zones'], m['weights']) for m in many], reqs=reqs)
+                     asked=asked, many=[(m['zones'], m['weights']) for m in many], reqs=reqs, recs=recs, rec_reqs=rec_reqs)
     dist.destroy_process_group()
 
 
@@ -92,6 +97,9 @@ def test_mc3_exchange_world2():
         assert np.array_equal(z0, np.arange(12).reshape(3, 4) % 3 == (key % 3)) and z0.dtype == bool
         assert np.array_equal(w0, np.full((2, 3), -0.5 * key))
         assert np.array_equal(z0, z1) and np.array_equal(w0, w1)
+    # gather_records: request (chain, i) returns record i of the chain's owner, on both ranks
+    want = np.array([[100 * (c >= 4) + i] * 32 for c, i in r0['rec_reqs']], np.uint8)
+    assert np.array_equal(r0['recs'], want) and np.array_equal(r1['recs'], want)
 
 def test_swap_accepts_better_chain():
     """mcmc_generative.py:263-274: label 0 moves to a chain whose posterior is higher with probability 1."""
