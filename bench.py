@@ -242,11 +242,12 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------------
-def k1_traffic():
-    """DRAM bytes per launch of K1 at N=20000 from the committed `ncu --set full` summary (profiles/), or None."""
+def k1_traffic(pattern='r*_k1_ncu_full_N20000.txt'):
+    """DRAM bytes per launch of a kernel (default: K1 at N=20000) from the committed `ncu --set full` summary
+    (profiles/), or None."""
     import glob
     import re
-    files = sorted(glob.glob(os.path.join(ROOT, 'profiles', 'r*_k1_ncu_full_N20000.txt')))
+    files = sorted(glob.glob(os.path.join(ROOT, 'profiles', pattern)))
     if not files:
         return None
     tot, unit = 0.0, {'byte': 1.0, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}
@@ -572,8 +573,12 @@ def shape_d_kernel_leg(torch, data, device, stream, peak):
             ('k4', lambda: eng.recount_async(), 2 * d['N'] * d['F'] + 3 * d['N'] + 4 * table_bytes + 48 * d['F'])):
         us, us_min = time_launches(torch, fn, flush)
         nbytes = nc * per_chain
+        summary = {'k1': 'r*_k1_free_block_ncu_full_shapeD.txt', 'k1s': 'r*_k1s_source_block_ncu_full_shapeD.txt',
+                   'k4': 'r*_k4_count_block_ncu_full_shapeD.txt'}[key]
         out[key] = {'bound': 'hbm', 'achieved': nbytes / us / 1e3, 'peak': peak, 'unit': 'GB/s',
-                    'frac': nbytes / us / 1e3 / peak, 'traffic': None, 'bytes_per_launch': int(nbytes),
+                    'frac': nbytes / us / 1e3 / peak, 'traffic': k1_traffic(summary), 'bytes_per_launch': int(nbytes),
+                    'kernel': {'k1': 'lh_free_block_kernel (K1b, source-free)', 'k1s': 'lh_source_block_kernel (K1s)',
+                               'k4': 'count_block_kernel (K4)'}[key],
                     'us_per_launch': us, 'us_min': us_min, 'l2': 'flushed before every timed launch',
                     'shape': '64 chains x 2000 x 200 x 8, 7 zones, 20 families'}
     eng.close()
