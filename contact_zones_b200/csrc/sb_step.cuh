@@ -939,7 +939,8 @@ __device__ void gibbs_table_row(const DevData& d, const StepParams& sp, const Ch
 // Evaluated ONCE per CTA, by warp 0, and broadcast through shared memory: lanes 0 / 1 draw the two Gammas in lock-step,
 // then lane l takes one of the six lgamma terms and one of the four x log y terms.  (Every thread used to evaluate all of
 // it -- ~3000 instructions per warp and step, which is what an alter_* step cost whatever the number of sites.)
-// Ends in a CTA barrier; sh.dshare[0..2] is rewritten only after the caller's reduction barrier.
+// sh.dshare[0..1] are rewritten in the next alter_* step (after this step's reduction barrier), sh.dshare[2..3] behind that
+// step's first CTA barrier, i.e. after every thread has read this step's values.
 // log q(t -> v) - log q(v -> t) of the pair proposal; called by (at least) 8 consecutive lanes of a warp with
 // l = lane & 7, result valid in all of them
 __device__ __forceinline__ double pair_log_q_ratio(int l, double t0, double t1, double v0, double v1, double kappa) {
@@ -962,21 +963,29 @@ __global__ void pair_log_q_kernel(double c0, double c1, double n0, double n1, do
     const double term = pair_log_q_ratio(threadIdx.x & 7, c0 / mass, c1 / mass, n0 / mass, n1 / mass, kappa);
     if (threadIdx.x == 0) out[0] = term;
 }
+// Two phases: warp 0 draws the new pair and publishes it (CTA barrier); then warp 0 goes on with log q - log q_back (six
+// lgamma, four x log y: the longest dependent chain of an alter_* step) and leaves it in sh.dshare[2] WITHOUT a barrier,
+// while the other warps already walk the column (column_delta keeps warp 0 out of the site loop).  The caller reads
+// sh.dshare[2] after the barrier of its reduction.
 __device__ void pair_proposal(RngKey key, uint64_t step, double c0, double c1, double kappa, double& n0, double& n1,
-                              double& log_q_ratio, StepShared& sh) {
+                              StepShared& sh) {
+    double t0 = 0.0, t1 = 0.0, v0 = 0.0, v1 = 0.0;
     if (threadIdx.x < 32) {
-        const int lane = threadIdx.x, l = lane & 7;
+        const int lane = threadIdx.x;
         const double mass = c0 + c1;
-        const double t0 = c0 / mass, t1 = c1 / mass;
+        t0 = c0 / mass; t1 = c1 / mass;
         const double a0 = 1.0 + kappa * t0, a1 = 1.0 + kappa * t1;
         const double g = rng_gamma(key, step, RP_PROPOSAL, (uint32_t)(lane & 1), (lane & 1) ? a1 : a0);
         const double g0 = __shfl_sync(0xffffffffu, g, 0), g1 = __shfl_sync(0xffffffffu, g, 1);
-        const double v0 = g0 / (g0 + g1), v1 = g1 / (g0 + g1);
-        const double term = pair_log_q_ratio(l, t0, t1, v0, v1, kappa);
-        if (lane == 0) { sh.dshare[0] = v0 * mass; sh.dshare[1] = v1 * mass; sh.dshare[2] = term; }
+        v0 = g0 / (g0 + g1); v1 = g1 / (g0 + g1);
+        if (lane == 0) { sh.dshare[0] = v0 * mass; sh.dshare[1] = v1 * mass; }
     }
     __syncthreads();
-    n0 = sh.dshare[0]; n1 = sh.dshare[1]; log_q_ratio = sh.dshare[2];
+    n0 = sh.dshare[0]; n1 = sh.dshare[1];
+    if (threadIdx.x < 32) {
+        const double term = pair_log_q_ratio(threadIdx.x & 7, t0, t1, v0, v1, kappa);
+        if (threadIdx.x == 0) sh.dshare[2] = term;
+    }
 }
 
 // ordered pair of distinct indices out of n (== random.sample(list, 2))
@@ -1001,7 +1010,9 @@ __device__ double column_delta(const DevData& d, const Chain& k, int f, const in
     double acc = 0.0;
     int i_lo, i_hi;
     team_share(tm, n_sites, i_lo, i_hi);
-    for (int i = i_lo + threadIdx.x; i < i_hi; i += blockDim.x) {
+    // warp 0 is still busy with the proposal's log-density ratio (pair_proposal): the other warps take the sites
+    const int nthr = (int)blockDim.x - 32;
+    for (int i = i_lo + (int)threadIdx.x - 32; threadIdx.x >= 32 && i < i_hi; i += nthr) {
         const int n = sites ? sites[i] : i;
         const int xs = sites ? d.x[(size_t)n * d.ldx + f] : d.xT[(size_t)f * d.ldn + n];
         if (xs == SB_NA) continue;
@@ -1040,17 +1051,19 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
         int a = 0, b = 1;
         if (d.C == 3) pick_pair(ua, 3, a, b);                         // _random.sample([0,1,2], 2)  :423
         double* w = k.w + (size_t)f * 3;
-        pair_proposal(key, step, w[a], w[b], sp.prec_w, n0, n1, lqr, sh);
+        pair_proposal(key, step, w[a], w[b], sp.prec_w, n0, n1, sh);
         __shared__ double wrow_new[12];
-        if (threadIdx.x == 0) {
+        if (threadIdx.x == 32) {                                      // (warp 0 is busy, see pair_proposal)
             double v[3] = {w[0], w[1], w[2]};
             v[a] = n0; v[b] = n1;
             wnorm_row(v, wrow_new, d.C);
         }
-        __syncthreads();
+        // wrow_new is read by warps 1.. only (column_delta): a named barrier over them keeps warp 0 out of the wait
+        if (threadIdx.x >= 32) asm volatile("bar.sync 1, %0;" ::"r"((int)blockDim.x - 32) : "memory");
         // sample_from_prior: no likelihood term; the team barrier of the reduction is still needed
         if (sp.from_prior) { team_sync(tm); dll = 0.0; }
         else dll = column_delta(d, k, f, nullptr, d.N, wrow_new, -1, 0, 0, 0, 0.0, 0.0, sh, tm);
+        lqr = sh.dshare[2];
         const bool accept = flog(ua[UA_ACCEPT * SB_AHEAD], k.flt) < dll - lqr;
         synced = !accept;       // a rejected proposal wrote nothing after the reduction's barrier
         if (accept) {
@@ -1095,24 +1108,25 @@ __device__ bool op_alter(const DevData& d, const StepParams& sp, const Chain& k,
             pcache = k.ppf + (size_t)tab * d.F + f;
         }
     }
-    pair_proposal(key, step, row[s0], row[s1], kappa, n0, n1, lqr, sh);
+    pair_proposal(key, step, row[s0], row[s1], kappa, n0, n1, sh);
     double new_prior_term = 0.0;
-    if (alpha) {
+    if (alpha && (threadIdx.x >> 5) == 1) {
         // Dirichlet prior of the changed row with the two entries replaced (read before the reduction's barrier):
-        // warp 0, one state per lane
-        if (threadIdx.x < 32) {
-            double t = 0.0;
-            for (int s = threadIdx.x; s < d.S; s += 32)
-                if (mask >> s & 1u) t += xlogy_d(alpha[s] - 1.0, s == s0 ? n0 : (s == s1 ? n1 : row[s]));
-            t = warp_sum(t);
-            if (threadIdx.x == 0) sh.dshare[3] = *lnorm + t;
-        }
-        __syncthreads();
-        new_prior_term = sh.dshare[3];
-        dprior = new_prior_term - *pcache;
+        // warp 1, one state per lane (warp 0 is busy, see pair_proposal); published by the reduction's barrier
+        const int lane = threadIdx.x & 31;
+        double t = 0.0;
+        for (int s = lane; s < d.S; s += 32)
+            if (mask >> s & 1u) t += xlogy_d(alpha[s] - 1.0, s == s0 ? n0 : (s == s1 ? n1 : row[s]));
+        t = warp_sum(t);
+        if (lane == 0) sh.dshare[3] = *lnorm + t;
     }
     if (sp.from_prior) { team_sync(tm); dll = 0.0; }
     else dll = column_delta(d, k, f, sites, n_sites, nullptr, which, tab, s0, s1, n0, n1, sh, tm);
+    lqr = sh.dshare[2];
+    if (alpha) {
+        new_prior_term = sh.dshare[3];
+        dprior = new_prior_term - *pcache;
+    }
     const bool accept = flog(ua[UA_ACCEPT * SB_AHEAD], k.flt) < dll - lqr + dprior;
     synced = !accept;
     if (accept) {
