@@ -52,6 +52,7 @@ struct sb_ctx {
     int k1b_threads = LH_THREADS, k1s_threads = LH_THREADS;   // CTA sizes of the blocked likelihood kernels (SB_K1B_THREADS, SB_K1S_THREADS)
     int n_sms = 148;                 // cudaDevAttrMultiProcessorCount of the context's device
     int k1b_parts = 0;               // CTAs per chain of the blocked source-free kernel (0 = chosen per launch; SB_K1B_PARTS)
+    int k1c_max_n = 8192, k1c_min_chains = 96;   // one-CTA-per-chain table kernel: site and chain range (SB_K1C_MAX_N, SB_K1C_MIN_CHAINS)
     int k1_block_max_n = 1024;       // source-free launches over at most this many sites take the blocked kernel (SB_K1_BLOCK_MAX_N)
     long lt_want_compact = 148L * 7; // the same for shapes with one site per code byte (SB_K1_CTAS_COMPACT; 444..2072 measured)
     std::vector<int> h_gclass;       // host copy of lt.group_class (class span of a group range)
@@ -161,6 +162,8 @@ int sb_create(sb_ctx** out, int device, const sb_dims* dims) {
     if (const char* e = getenv("SB_K1_CTAS")) ctx->lt_want = std::max(1L, atol(e));
     if (const char* e = getenv("SB_K1_CTAS_COMPACT")) ctx->lt_want_compact = std::max(1L, atol(e));
     if (const char* e = getenv("SB_K1_BLOCK_MAX_N")) ctx->k1_block_max_n = atoi(e);
+    if (const char* e = getenv("SB_K1C_MAX_N")) ctx->k1c_max_n = atoi(e);
+    if (const char* e = getenv("SB_K1C_MIN_CHAINS")) ctx->k1c_min_chains = atoi(e);
     if (const char* e = getenv("SB_K1B_PARTS")) ctx->k1b_parts = atoi(e);
     if (const char* e = getenv("SB_K1B_THREADS")) ctx->k1b_threads = std::min(LH_THREADS, std::max(32, atoi(e) & ~31));
     if (const char* e = getenv("SB_K1S_THREADS")) ctx->k1s_threads = std::min(LH_THREADS, std::max(32, atoi(e) & ~31));
@@ -806,6 +809,23 @@ static int launch_likelihood(sb_ctx* ctx, int chain_begin, int n, int use_source
     const DevData& d = ctx->d;
     // table-driven K1: one launch (weights normalisation and the per-chain reduction are fused).  Its table rows hold
     // 32 codes, i.e. S + 1 <= 32 digits: S = 32 (SB_MAX_S) takes the tile-per-site kernel below
+    // one CTA per chain (sb_lhtab.cuh:lh_chain_kernel): launches of many chains over few sites, where the table
+    // kernel's per-chain prologue, repeated in each of its ~11 CTAs per chain, is most of the launch
+    if (!use_source && d.S + 1 <= LT_ROW && ctx->lt.cpb >= 2 && n >= ctx->k1c_min_chains && d.N <= ctx->k1c_max_n &&
+        n <= 65535 && blocked_kernels_allowed()) {
+        const LhTab& t = ctx->lt;
+        int fc = d.F;
+        while (fc > 1 && lc_layout(d.F, d.S, d.Z, fc, t.n_classes, t.n_groups, false).total > 96 * 1024) fc = (fc + 1) / 2;
+        const size_t smem = lc_layout(d.F, d.S, d.Z, fc, t.n_classes, t.n_groups, false).total;
+        if (smem <= 200 * 1024) {
+            auto kern = t.cpb == 2 ? lh_chain_kernel<2> : lh_chain_kernel<3>;
+            if (smem > 48 * 1024) CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            kern<<<n, LC_THREADS, smem, ctx->stream>>>(d, ctx->st, t, chain_begin, fc);
+            ++ctx->launches;
+            CK(cudaGetLastError());
+            return SB_OK;
+        }
+    }
     // blocked form (one CTA per 16-feature block and chain, sb_eval.cuh): shapes with one site per code byte (S + 1 > 5),
     // S = 32, and launches over few sites, where the table kernel's per-chain prologue dominates (SB_K1_BLOCK_MAX_N)
     const size_t fb_one = lh_free_block_smem(d.S, d.Z, d.Fam);

@@ -379,3 +379,318 @@ lh_table_kernel(DevData d, ChainArrays st, LhTab t, int chain_begin, double* __r
         }
     }
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// K1c: the table-driven likelihood with ONE CTA PER CHAIN, for launches of many chains over few sites.  Same tables,
+// same packed code stream and the same exact treatment of tiny values as lh_table_kernel, but a chain's fixed work is
+// done once instead of once per (feature chunk, correction part) CTA: at 256 chains x 2000 x 100 x 4 lh_table_kernel
+// executes 70 k warp instructions per chain of which 7 k are table values and member cells (ncu: most lanes of its
+// 11 CTAs per chain idle through prologue, reductions and the ticket).  Here
+//   * w~ rows of all features, p_global and p_zones (with a column of ones for NA) are staged in shared memory once;
+//   * the CTA walks the features in chunks of `fc`: builds the chunk's rows, then streams the chunk's (feature, group)
+//     units THREAD-STRIDED -- every thread has work whatever the number of groups -- with the next unit's 16 code bytes
+//     in flight;
+//   * the zone members are corrected by the same CTA, one warp per member, from the staged tables (only the state code
+//     is a global load);
+//   * one block reduction, one store: no partial sums, no ticket.
+// ---------------------------------------------------------------------------------------------------------------
+#define LC_THREADS 512
+struct LcLayout { size_t wn, pzg, tab, val, slow, gcls, total; };
+__host__ __device__ __forceinline__ LcLayout lc_layout(int F, int S, int Z, int fc, int ncls, int n_groups, bool compact) {
+    LcLayout L;
+    size_t o = 0;
+    L.wn = o;   o += (size_t)F * 12 * 8;
+    L.pzg = o;  o += (size_t)(1 + Z) * F * (S + 1) * 8;
+    o = (o + 255) & ~(size_t)255;
+    L.tab = o;  o += compact ? 0 : (size_t)ncls * fc * 2 * LT_ROW * 4;
+    L.val = o;  o += (size_t)ncls * fc * (S + 1) * 8;
+    L.slow = o; o += ((size_t)ncls * fc + 15) & ~(size_t)15;
+    L.gcls = o; o += ((size_t)n_groups * 2 + 15) & ~(size_t)15;
+    L.total = o;
+    return L;
+}
+
+template <int CPB>
+__global__ void __launch_bounds__(LC_THREADS)
+lh_chain_kernel(DevData d, ChainArrays st, LhTab t, int chain_begin, int fc) {
+    extern __shared__ __align__(256) unsigned char lc_smem[];
+    __shared__ double red[33];
+    __shared__ int zoff[SB_MAX_Z + 1];
+    constexpr bool COMPACT = CPB == 1;
+    const int chain = chain_begin + blockIdx.x;
+    const int S = d.S, S1 = S + 1, F = d.F, N = d.N, Z = d.Z, ncls = t.n_classes, ng = t.n_groups;
+    const size_t FS = (size_t)F * S;
+    const LcLayout L = lc_layout(F, S, Z, fc, ncls, ng, COMPACT);
+    double* wn = reinterpret_cast<double*>(lc_smem + L.wn);
+    double* pzg = reinterpret_cast<double*>(lc_smem + L.pzg);           // [1 + Z][F][S1]: p_global, then the zones
+    uint32_t* tab = reinterpret_cast<uint32_t*>(lc_smem + L.tab);
+    double* val = reinterpret_cast<double*>(lc_smem + L.val);
+    unsigned char* slow = lc_smem + L.slow;
+    int16_t* gcls = reinterpret_cast<int16_t*>(lc_smem + L.gcls);
+    const double* __restrict__ w = st.weights + chain * st.s_weights;
+    const double* __restrict__ pg = st.p_global + chain * st.s_p_global;
+    const double* __restrict__ pz = st.p_zones + chain * st.s_p_zones;
+    const double* __restrict__ pf = st.p_fam + chain * st.s_p_fam;
+    const int8_t* __restrict__ zone_id = st.zone_id + chain * st.s_zone_id;
+    const int T = blockDim.x, tid = threadIdx.x;
+
+    // ---- once per chain ----------------------------------------------------------------------------------------
+    {
+        // the first round of every thread's global loads is issued before anything is computed or stored (the loops
+        // below would otherwise pay one memory round trip each)
+        const int f_w = tid, i_s = tid;
+        double w3[3] = {1.0, 0.0, 0.0}, row0[4] = {1.0, 1.0, 1.0, 1.0};
+        if (f_w < F) { w3[0] = w[(size_t)f_w * 3]; w3[1] = w[(size_t)f_w * 3 + 1]; w3[2] = w[(size_t)f_w * 3 + 2]; }
+        const bool first_row = i_s < (1 + Z) * F && S <= 4;
+        if (first_row) {
+            const int tt = i_s / F, f = i_s - tt * F;
+            const double* src = (tt == 0 ? pg : pz + (size_t)(tt - 1) * FS) + (size_t)f * S;
+            for (int s = 0; s < S; ++s) row0[s] = src[s];
+        }
+        const int gc0 = tid < ng ? t.group_class[tid] : 0;
+        int zs = 0;
+        if (tid < Z) zs = st.zone_size[chain * st.s_zone_size + tid];
+        if (f_w < F) wnorm_row(w3, wn + (size_t)f_w * 12, d.C);
+        for (int f = tid + T; f < F; f += T) wnorm_row(w + (size_t)f * 3, wn + (size_t)f * 12, d.C);
+        for (int i = tid; i < (1 + Z) * F; i += T) {                    // one (table, feature) row per thread
+            double* dst = pzg + (size_t)i * S1;
+            if (i == i_s && first_row) {
+                for (int s = 0; s < S; ++s) dst[s] = row0[s];
+            } else {
+                const int tt = i / F, f = i - tt * F;
+                const double* src = (tt == 0 ? pg : pz + (size_t)(tt - 1) * FS) + (size_t)f * S;
+                for (int s = 0; s < S; ++s) dst[s] = src[s];
+            }
+            dst[S] = 1.0;
+        }
+        if (tid < ng) gcls[tid] = (int16_t)gc0;
+        for (int g = tid + T; g < ng; g += T) gcls[g] = (int16_t)t.group_class[g];
+        if (tid < Z) zoff[tid + 1] = zs;
+    }
+    __syncthreads();
+    if (tid == 0) {                                                     // sizes -> offsets
+        int o = 0;
+        for (int z = 0; z < Z; ++z) { const int sz = zoff[z + 1]; zoff[z] = o; o += sz; }
+        zoff[Z] = o;
+    }
+    // Without families a member's correction factor depends on (zone, feature, state) only: the staged zone tables are
+    // turned in place into RATIO tables  R[z][f][s] = mix_zone / v_free  (= mix_zone where the main pass left the cell
+    // out; -1 where mix_zone itself is tiny: those cells take the exact path), so that a member cell costs one look-up
+    // and one multiply.
+    const bool ratio = !d.inheritance;
+    if (ratio) {
+        __syncthreads();
+        for (int zf = tid; zf < Z * F; zf += T) {                               // one (zone, feature) row per thread
+            const int f = zf % F;
+            const double* wr = wn + (size_t)f * 12;
+            const double w0 = wr[0], w3 = wr[3], w4 = wr[4];                    // cfg 0 / cfg 1
+            double* rz = pzg + (size_t)(F + zf) * S1;
+            const double* rg = pzg + (size_t)f * S1;
+            for (int s = 0; s < S; ++s) {                                       // (the NA column stays 1)
+                const double mix = w3 * rg[s] + w4 * rz[s], vf = w0 * rg[s];
+                rz[s] = __double2hiint(mix) < LT_TINY_HI ? -1.0 : (__double2hiint(vf) >= LT_TINY_HI ? mix / vf : mix);
+            }
+        }
+    }
+    LogProd acc;
+    lp_init(acc);
+    const uint32_t tab_s = (uint32_t)__cvta_generic_to_shared(COMPACT ? (void*)val : (void*)tab);
+    const uint32_t row_b = COMPACT ? (uint32_t)S1 * 8u : 2u * LT_ROW * 4u;
+    const size_t xstride = (size_t)ng * 16;
+
+    for (int f0 = 0; f0 < F; f0 += fc) {
+        const int nf = min(fc, F - f0);
+        const uint32_t cls_rows = COMPACT ? (uint32_t)nf : (uint32_t)fc;
+        __syncthreads();                                                // staged tables ready / previous chunk streamed
+        for (int i = tid; i < ncls * nf; i += T) slow[i] = 0;
+        __syncthreads();
+        // ---- rows (class, feature) of the chunk ----
+        int tiny = 0;
+        for (int i = tid; i < ncls * nf * S1; i += T) {
+            const int r = i / S1, s = i - r * S1, ci = r / nf, fi = r - ci * nf;
+            double v = 1.0;                                                      // NA / padding digit
+            if (s < S) {
+                const int f = f0 + fi, fam = t.class_fam[ci];
+                const double pgv = pzg[(size_t)f * S1 + s];
+                v = fam >= 0 ? wn[(size_t)f * 12 + 6] * pgv + wn[(size_t)f * 12 + 8] * pf[(size_t)fam * FS + (size_t)f * S + s]
+                             : wn[(size_t)f * 12] * pgv;
+                // a tiny / zero value at a state that can occur sends the row to the exact cell-by-cell path
+                if ((t.chk_mask[f] >> s & 1u) && __double2hiint(v) < LT_TINY_HI) { slow[r] = 1; tiny = 1; }
+            }
+            val[i] = v;
+        }
+        const int any_slow = __syncthreads_or(tiny);
+        if (!COMPACT) {
+            // rows of 32 codes: lane = code (its digits are fixed for the thread), one row per warp and iteration
+            const int code = tid & 31;
+            int dig[CPB], c = code;
+#pragma unroll
+            for (int k = 0; k < CPB; ++k) { dig[k] = c % t.radix; c /= t.radix; }
+            if (code < t.row_entries) {
+                int ci = 0, fi2 = tid >> 5;
+                while (fi2 >= nf) { fi2 -= nf; ++ci; }
+                while (ci < ncls) {
+                    const double* vr = val + (size_t)(ci * nf + fi2) * S1;
+                    double v = 1.0;
+#pragma unroll
+                    for (int k = 0; k < CPB; ++k) v *= vr[dig[k]];
+                    uint32_t* row = tab + (size_t)(ci * fc + fi2) * 2 * LT_ROW;
+                    row[code] = (uint32_t)__double2hiint(v);
+                    row[LT_ROW + code] = (uint32_t)__double2loint(v);
+                    fi2 += T >> 5;
+                    while (fi2 >= nf && ci < ncls) { fi2 -= nf; ++ci; }
+                }
+            }
+            __syncthreads();
+        }
+        // ---- stream: (feature, group) units, thread-strided; consecutive threads read consecutive groups ----
+        int fi = tid / ng, g = tid - fi * ng;
+        const int step_f = T / ng, step_g = T - step_f * ng;            // a thread's next unit is T units further
+        uint4 xv = make_uint4(0, 0, 0, 0);
+        if (fi < nf) xv = __ldg(reinterpret_cast<const uint4*>(t.xcode + (size_t)(f0 + fi) * xstride + (size_t)g * 16));
+        double m = acc.m;
+        int e = acc.e;
+        while (fi < nf) {
+            const int ci = gcls[g];
+            const uint32_t row = tab_s + ((uint32_t)ci * cls_rows + (uint32_t)fi) * row_b;
+            const uint4 xc = xv;
+            const int fi_c = fi, g_c = g;
+            fi += step_f;
+            g += step_g;
+            if (g >= ng) { g -= ng; ++fi; }
+            if (fi < nf) xv = __ldg(reinterpret_cast<const uint4*>(t.xcode + (size_t)(f0 + fi) * xstride + (size_t)g * 16));
+            if (!any_slow || !slow[ci * nf + fi_c]) {
+                if (COMPACT) lt_unit_compact(xc, row, m, e);
+                else lt_unit<CPB>(xc, row, m, e);
+                continue;
+            }
+            // exact path (the row holds a tiny / zero value)
+            acc.m = m; acc.e = e;
+            for (int q = 0; q < t.G; ++q) {
+                const int n = t.perm[(size_t)g_c * t.G + q];
+                if (n < 0) continue;
+                const int xs = d.x[(size_t)n * d.ldx + f0 + fi_c];
+                if (xs == SB_NA) continue;
+                const double v = val[(size_t)(ci * nf + fi_c) * S1 + xs];
+                // a zone member with a tiny free value is left to the correction pass (no -inf - -inf)
+                if (zone_id[n] >= 0 && __double2hiint(v) < LT_TINY_HI) continue;
+                lp_mul(acc, v);
+            }
+            lp_renorm(acc);
+            m = acc.m; e = acc.e;
+        }
+        acc.m = m;
+        acc.e = e;
+    }
+
+    // ---- zone members: + log prod mix_zone - log prod v_free, one warp per member, lanes over the features ----
+    LogProd num, den;
+    lp_init(num);
+    lp_init(den);
+    {
+        const int* __restrict__ members = st.zone_members + chain * st.s_zone_members;
+        const int lane = tid & 31, wid = tid >> 5, nw = T >> 5, n_mem = zoff[Z];
+        int fill = 0;
+        double nm = num.m, dm = den.m;
+        // the warp's members: wid, wid + nw, ...; their ids are fetched by the lanes up front, and the state codes of
+        // the next member are in flight while the current one is processed
+        const int my_cnt = wid < n_mem ? (n_mem - wid + nw - 1) / nw : 0;
+        for (int j0 = 0; j0 < my_cnt; j0 += 32) {
+        int n_l = 0, z_l = 0, fam_l = -1;
+        {
+            const int mi_l = wid + (j0 + lane) * nw;
+            if (mi_l < n_mem) {
+                while (mi_l >= zoff[z_l + 1]) ++z_l;
+                n_l = members[(size_t)z_l * N + (mi_l - zoff[z_l])];
+                if (d.inheritance) fam_l = d.fam_id[n_l];
+            }
+        }
+        const int cnt = min(32, my_cnt - j0);
+        int xs_nxt[4];
+        {
+            const uint8_t* __restrict__ x0 = d.x + (size_t)__shfl_sync(0xffffffffu, n_l, 0) * d.ldx;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) xs_nxt[u] = lane + 32 * u < F ? (int)x0[lane + 32 * u] : SB_NA;
+        }
+        for (int j = 0; j < cnt; ++j) {
+            const int n = __shfl_sync(0xffffffffu, n_l, j), z = __shfl_sync(0xffffffffu, z_l, j);
+            const int fam = __shfl_sync(0xffffffffu, fam_l, j);
+            int xs_cur[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) xs_cur[u] = xs_nxt[u];
+            if (j + 1 < cnt) {
+                const uint8_t* __restrict__ x1 = d.x + (size_t)__shfl_sync(0xffffffffu, n_l, j + 1) * d.ldx;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) xs_nxt[u] = lane + 32 * u < F ? (int)x1[lane + 32 * u] : SB_NA;
+            }
+            const uint8_t* __restrict__ xr = d.x + (size_t)n * d.ldx;
+            const double* pzz = pzg + (size_t)(1 + z) * F * S1;
+            const double* pff = pf + (size_t)max(fam, 0) * FS;
+            for (int f_0 = lane; f_0 < F; f_0 += 128) {
+                int xs4[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    xs4[u] = f_0 == lane ? xs_cur[u] : (f_0 + 32 * u < F ? (int)xr[f_0 + 32 * u] : SB_NA);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (xs4[u] == SB_NA) continue;
+                    const int f = f_0 + 32 * u;
+                    const double* wr = wn + (size_t)f * 12;
+                    double pzv = pzz[(size_t)f * S1 + xs4[u]];
+                    if (ratio) {
+                        if (__double2hiint(pzv) >= LT_TINY_HI) {        // the staged ratio: factors in [2^-60, 2^60]
+                            nm *= pzv;
+                            if (++fill == 8) {                          // (dm too: exact cells may have used it)
+                                fill = 0;
+                                const int h0 = __double2hiint(nm), h1 = __double2hiint(dm);
+                                num.e += ((h0 >> 20) & 0x7ff) - 1023;
+                                den.e += ((h1 >> 20) & 0x7ff) - 1023;
+                                nm = __hiloint2double((h0 & 0x800fffff) | 0x3ff00000, __double2loint(nm));
+                                dm = __hiloint2double((h1 & 0x800fffff) | 0x3ff00000, __double2loint(dm));
+                            }
+                            continue;
+                        }
+                        pzv = pz[(size_t)z * FS + (size_t)f * S + xs4[u]];      // exact path below, from the chain's table
+                    }
+                    const double pgv = pzg[(size_t)f * S1 + xs4[u]];
+                    double mix, vf;
+                    if (fam >= 0) {
+                        const double pfv = pff[(size_t)f * S + xs4[u]];
+                        mix = wr[9] * pgv + wr[10] * pzv + wr[11] * pfv;       // cfg = 3
+                        vf = wr[6] * pgv + wr[8] * pfv;                          // cfg = 2
+                    } else {
+                        mix = wr[3] * pgv + wr[4] * pzv;                         // cfg = 1
+                        vf = wr[0] * pgv;                                        // cfg = 0
+                    }
+                    const bool vf_ok = __double2hiint(vf) >= LT_TINY_HI;   // else: the main pass skipped the cell
+                    if (__double2hiint(mix) < LT_TINY_HI) {
+                        num.side += log(mix);                                    // exact path (may be -inf)
+                        if (!vf_ok) continue;
+                    } else {
+                        nm *= mix;
+                    }
+                    if (vf_ok) dm *= vf;
+                    if (++fill == 8) {                 // factors in [2^-60, 1]: renormalise every 8
+                        fill = 0;
+                        const int h0 = __double2hiint(nm), h1 = __double2hiint(dm);
+                        num.e += ((h0 >> 20) & 0x7ff) - 1023;
+                        den.e += ((h1 >> 20) & 0x7ff) - 1023;
+                        nm = __hiloint2double((h0 & 0x800fffff) | 0x3ff00000, __double2loint(nm));
+                        dm = __hiloint2double((h1 & 0x800fffff) | 0x3ff00000, __double2loint(dm));
+                    }
+                }
+            }
+        }
+        }
+        num.m = nm;
+        den.m = dm;
+    }
+    // one log per warp: the lanes' mantissas (stream x member numerators / member denominators, each in [1/2, 8)) are
+    // multiplied across the warp first
+    lp_renorm(acc);
+    lp_renorm(num);
+    lp_renorm(den);
+    double v = lp_warp_value(acc.m * num.m / den.m, acc.e + num.e - den.e, acc.side + num.side - den.side);
+    v = block_sum(v, red);
+    if (tid == 0) st.ll[chain] = v;
+}

@@ -263,15 +263,20 @@ def test_fallback_evaluation_kernels(name, built_lib, monkeypatch):
             assert np.array_equal(fast[k], slow[k]), k
 
 
-@pytest.mark.parametrize('max_n', ['0', '1000000'])
+@pytest.mark.parametrize('max_n', ['0', '1000000', 'chain'])
 @pytest.mark.parametrize('name', golden_cases())
 def test_both_source_free_kernels_on_the_goldens(name, max_n, built_lib, monkeypatch):
-    """The source-free likelihood has two kernels: the table kernel (packed state codes, sb_lhtab.cuh) and the blocked
-    kernel (one CTA per range of 16-feature blocks, sb_eval.cuh), chosen by shape.  SB_K1_BLOCK_MAX_N = 0 keeps every
-    shape with two or more sites per code byte on the table kernel, 1000000 sends every shape to the blocked one (with
-    1 .. all blocks per CTA, SB_K1B_PARTS): both reproduce the reference's value."""
+    """The source-free likelihood has three kernels: the table kernel (packed state codes, sb_lhtab.cuh), its
+    one-CTA-per-chain form for many chains over few sites, and the blocked kernel (one CTA per range of 16-feature blocks,
+    sb_eval.cuh), chosen by shape.  SB_K1_BLOCK_MAX_N = 0 keeps every shape with two or more sites per code byte on the
+    table kernel, 1000000 sends every shape to the blocked one (with 1 .. all blocks per CTA, SB_K1B_PARTS), 'chain'
+    sends the shapes with two or more sites per code byte to the one-CTA-per-chain kernel: all reproduce the
+    reference's value."""
     c = load_case(name)
     g = c['g']
+    monkeypatch.setenv('SB_K1C_MIN_CHAINS', '1' if max_n == 'chain' else '1000000')
+    if max_n == 'chain':
+        max_n = '0'
     monkeypatch.setenv('SB_K1_BLOCK_MAX_N', max_n)
     for parts in (['0'] if max_n == '0' else ['0', '1', '2', '1000']):
         monkeypatch.setenv('SB_K1B_PARTS', parts)
