@@ -52,7 +52,7 @@ struct sb_ctx {
     int k1b_threads = LH_THREADS, k1s_threads = LH_THREADS;   // CTA sizes of the blocked likelihood kernels (SB_K1B_THREADS, SB_K1S_THREADS)
     int n_sms = 148;                 // cudaDevAttrMultiProcessorCount of the context's device
     int k1b_parts = 0;               // CTAs per chain of the blocked source-free kernel (0 = chosen per launch; SB_K1B_PARTS)
-    int k1c_max_n = 8192, k1c_min_chains = 96;   // one-CTA-per-chain table kernel: site and chain range (SB_K1C_MAX_N, SB_K1C_MIN_CHAINS)
+    int k1c_max_n = 12288, k1c_min_chains = 96;   // one-CTA-per-chain table kernel: site and chain range (SB_K1C_MAX_N, SB_K1C_MIN_CHAINS)
     int k1_block_max_n = 1024;       // source-free launches over at most this many sites take the blocked kernel (SB_K1_BLOCK_MAX_N)
     long lt_want_compact = 148L * 7; // the same for shapes with one site per code byte (SB_K1_CTAS_COMPACT; 444..2072 measured)
     std::vector<int> h_gclass;       // host copy of lt.group_class (class span of a group range)

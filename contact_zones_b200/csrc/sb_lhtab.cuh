@@ -631,6 +631,24 @@ lh_chain_kernel(DevData d, ChainArrays st, LhTab t, int chain_begin, int fc) {
 #pragma unroll
                 for (int u = 0; u < 4; ++u)
                     xs4[u] = f_0 == lane ? xs_cur[u] : (f_0 + 32 * u < F ? (int)xr[f_0 + 32 * u] : SB_NA);
+                if (ratio) {
+                    // four branch-free look-ups (NA, padding and columns beyond F read a ratio of 1); the exact code
+                    // below only runs if one of the four is flagged
+                    double r4[4];
+                    int lo_hi = 0x7fffffff;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        r4[u] = pzz[(size_t)min(f_0 + 32 * u, F - 1) * S1 + min(xs4[u], S)];
+                        lo_hi = min(lo_hi, __double2hiint(r4[u]));
+                    }
+                    if (lo_hi >= LT_TINY_HI) {
+                        nm *= (r4[0] * r4[1]) * (r4[2] * r4[3]);                // factors in [2^-60, 2^60]
+                        const int h0 = __double2hiint(nm);
+                        num.e += ((h0 >> 20) & 0x7ff) - 1023;
+                        nm = __hiloint2double((h0 & 0x800fffff) | 0x3ff00000, __double2loint(nm));
+                        continue;
+                    }
+                }
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     if (xs4[u] == SB_NA) continue;
