@@ -546,8 +546,10 @@ lh_chain_kernel(DevData d, ChainArrays st, LhTab t, int chain_begin, int fc) {
         // ---- stream: (feature, group) units, thread-strided; consecutive threads read consecutive groups ----
         int fi = tid / ng, g = tid - fi * ng;
         const int step_f = T / ng, step_g = T - step_f * ng;            // a thread's next unit is T units further
+        // (unit u = fi * ng + g is 16 bytes at xcode + (f0 * ng + u) * 16: the thread's pointer just advances by T units)
+        const uint4* xp = reinterpret_cast<const uint4*>(t.xcode + (size_t)f0 * xstride) + tid;
         uint4 xv = make_uint4(0, 0, 0, 0);
-        if (fi < nf) xv = __ldg(reinterpret_cast<const uint4*>(t.xcode + (size_t)(f0 + fi) * xstride + (size_t)g * 16));
+        if (fi < nf) xv = __ldg(xp);
         double m = acc.m;
         int e = acc.e;
         while (fi < nf) {
@@ -557,8 +559,9 @@ lh_chain_kernel(DevData d, ChainArrays st, LhTab t, int chain_begin, int fc) {
             const int fi_c = fi, g_c = g;
             fi += step_f;
             g += step_g;
+            xp += T;
             if (g >= ng) { g -= ng; ++fi; }
-            if (fi < nf) xv = __ldg(reinterpret_cast<const uint4*>(t.xcode + (size_t)(f0 + fi) * xstride + (size_t)g * 16));
+            if (fi < nf) xv = __ldg(xp);
             if (!any_slow || !slow[ci * nf + fi_c]) {
                 if (COMPACT) lt_unit_compact(xc, row, m, e);
                 else lt_unit<CPB>(xc, row, m, e);
